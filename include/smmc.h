@@ -1,0 +1,155 @@
+/*
+ * smmc.h -- C ABI of the B200-native Monte Carlo portfolio hot path.
+ *
+ * This is the drop-in boundary underneath the reference's C++ entry points
+ * (reference: include/stock_market_monte_carlo/simulations.h:69-86, gpu.h:1-2;
+ * definitions src/simulations.cu:269-341, :661-697, src/gpu.cu:17-47).  The C++
+ * symbols of the reference (`mc_simulations_gpu`, `mc_simulations_gpu_reduceBlock`,
+ * `reduce_mean_gpu`, `vector_add`, `vector_add_gpu`) are exported by the same
+ * shared library as thin marshalling wrappers over the functions declared here
+ * (see include/stock_market_monte_carlo/simulations.h in this repo).
+ *
+ * Plain pointers and sizes only: no C++ types, no torch types.  All functions
+ * return an smmc_status; none of them calls exit() or throws.
+ *
+ * There is NO CPU fallback: every compute entry point needs a CUDA device of
+ * compute capability 10.x and fails with SMMC_ERR_NO_DEVICE / SMMC_ERR_CUDA otherwise.
+ */
+#ifndef SMMC_H_
+#define SMMC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMMC_ABI_VERSION 1
+#define SMMC_BLOCK 256          /* logical block = THREADS_PER_BLOCK of the reference (src/simulations.cu:17) */
+#define SMMC_MAX_HIST_BINS 4096
+
+typedef enum smmc_status {
+  SMMC_OK = 0,
+  SMMC_ERR_INVALID_ARG = 1,   /* bad config (message via smmc_last_error) */
+  SMMC_ERR_NO_DEVICE = 2,     /* no CUDA device / wrong architecture */
+  SMMC_ERR_CUDA = 3,          /* a CUDA runtime call failed */
+  SMMC_ERR_UNSUPPORTED = 4    /* valid request this build cannot serve (e.g. table too large for shared memory) */
+} smmc_status;
+
+/* How each monthly return is produced. */
+typedef enum smmc_mode {
+  /* Reference stream, bit-for-bit: seed rand_pcg(path+1) (src/simulations.cu:62-67,:140), xorshift per month
+   * (:69-75,:146), float index map (:148), fmaf compounding (:149).  32-bit path ids: stream_offset+N < 2^31. */
+  SMMC_MODE_BOOTSTRAP_COMPAT = 0,
+  /* Philox4x32-10 counter stream, index = mulhi(u32, n_returns) (unbiased to n/2^32). */
+  SMMC_MODE_BOOTSTRAP = 1,
+  /* Philox4x32-10 counter stream + Box-Muller; r ~ N(gauss_mean, gauss_std) in percent
+   * (reference CPU semantics: sample_returns_gaussian, src/simulations.cpp:41-55). */
+  SMMC_MODE_GAUSSIAN = 2,
+  /* Sobol (Joe-Kuo direction numbers as vendored in reference include/sobol/sobol.cpp), point = path id + 1,
+   * dimension = month; optional Philox-keyed digital shift when seed != 0. */
+  SMMC_MODE_SOBOL_BOOTSTRAP = 3,
+  SMMC_MODE_SOBOL_GAUSSIAN = 4
+} smmc_mode;
+
+/* smmc_config.flags */
+#define SMMC_FLAG_DEVICE_POINTERS 1u   /* `returns` and every smmc_result buffer are DEVICE pointers on cfg->device;
+                                          the call is asynchronous on `stream` except for the scalar statistics,
+                                          which are only filled when SMMC_FLAG_NO_SYNC is absent */
+#define SMMC_FLAG_NO_SYNC 2u           /* with DEVICE_POINTERS: do not synchronise; scalars in smmc_result are left
+                                          untouched and the caller reads `stats_dev` (see below) itself */
+
+typedef struct smmc_config {
+  uint32_t abi_version;        /* SMMC_ABI_VERSION */
+  int32_t mode;                /* smmc_mode */
+  int64_t n_simulations;       /* N: paths simulated by this call (reference: max_n_simulations) */
+  int32_t n_periods;           /* P: compounding periods (months) per path */
+  int32_t n_returns;           /* n: length of `returns` (bootstrap modes), else 0 */
+  const float *returns;        /* historical monthly returns in PERCENT (reference units), bootstrap modes */
+  uint64_t seed;               /* Philox key (native modes); added to the PCG seed input in COMPAT (0 = reference) */
+  uint64_t stream_offset;      /* global id of path 0 of this call: path i uses RNG stream stream_offset + i.
+                                  Multi-GPU sharding = disjoint [offset, offset+N) ranges, multiples of 256 */
+  float initial_capital;       /* V0 */
+  float gauss_mean;            /* percent per period (GAUSSIAN modes) */
+  float gauss_std;             /* percent per period */
+  float target;                /* below_count = #{ final < target }  (strict, fp32 compare:
+                                  reference examples/benchmark_mc_gpu.cpp:30-41) */
+  float hist_lo, hist_hi;      /* histogram range [lo, hi); bins of equal width */
+  int32_t hist_bins;           /* 0 = no histogram; else 1..SMMC_MAX_HIST_BINS; output has hist_bins+2 counters:
+                                  [0] = underflow (x < lo or NaN), [1..bins] = bins, [bins+1] = overflow (x >= hi) */
+  int32_t device;              /* CUDA device ordinal */
+  uint32_t flags;
+  void *stream;                /* cudaStream_t (DEVICE_POINTERS only; NULL = legacy default stream) */
+} smmc_config;
+
+/* Device-side reduced statistics, laid out as doubles so that ONE sum-allreduce (ncclFloat64) over
+ * ranks merges every field exactly: the integer counters are < 2^53 and therefore exact in double.
+ *   [0] count   [1] below_count   [2] S1 = sum (x - V0)   [3] S2 = sum (x - V0)^2
+ *   [4] reserved (0)   [5] reserved (0)   [6 .. 6+hist_bins+2) histogram counters
+ * smmc_stats_len(bins) gives the length; smmc_stats_finalize() turns a (possibly all-reduced) vector into
+ * count / mean / M2 / below / hist. */
+#define SMMC_STATS_HEADER 6
+
+typedef struct smmc_result {
+  /* caller-owned output buffers (host pointers unless SMMC_FLAG_DEVICE_POINTERS); NULL = not requested */
+  float *finals;               /* [N]  final value of path i (reference `totals`, src/simulations.cu:151) */
+  float *block_means;          /* [ceil(N/256)] per-256-path-block mean (reference `totals[blockIdx.x]`, :244) */
+  float *block_vars;           /* [ceil(N/256)] per-block population variance (reference `variances`, :245) */
+  uint64_t *hist;              /* [hist_bins+2] (host pointer always; filled unless NO_SYNC) */
+  double *stats_dev;           /* DEVICE_POINTERS only: device buffer of smmc_stats_len(hist_bins) doubles */
+  /* scalars filled by the call */
+  uint64_t count;              /* N */
+  uint64_t below_count;
+  double mean;                 /* mean of the N finals */
+  double m2;                   /* sum (x - mean)^2   (population variance = m2 / count) */
+  float device_ms;             /* CUDA-event time of the kernel(s) of this call */
+  int32_t gpu_launches;        /* kernels launched by this call */
+} smmc_result;
+
+/* ---- run ---------------------------------------------------------------------------------------------- */
+
+/* One blocking simulation call on cfg->device.  Host buffers by default: the table is copied H2D, results D2H,
+ * device workspace comes from a per-device cache owned by the library (freed by smmc_shutdown).
+ * Replaces: mc_simulations_gpu_launcher / _reduceBlock_launcher / _multi_gpu_launcher_async
+ * (reference src/simulations.cu:345-473, :576-655). */
+smmc_status smmc_run(const smmc_config *cfg, smmc_result *out);
+
+/* Multi-GPU, single process, one host thread (the reference's driver model, src/simulations.cu:576-655): shards
+ * [0,N) into n_gpus contiguous 256-aligned path ranges by RNG offset, runs them concurrently on devices
+ * 0..n_gpus-1 and merges the partial statistics on the host.  Results are identical to a 1-GPU run of the same
+ * config (histogram / counts bit-identical; mean/M2 to fp64 rounding). Host pointers only. */
+smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out);
+
+int32_t smmc_stats_len(int32_t hist_bins);
+/* stats: HOST vector of smmc_stats_len(bins) doubles (e.g. after an allreduce). hist may be NULL. */
+smmc_status smmc_stats_finalize(const double *stats, int32_t hist_bins, float initial_capital,
+                                uint64_t *count, uint64_t *below_count, double *mean, double *m2, uint64_t *hist);
+
+/* ---- the remaining reference GPU entry points ------------------------------------------------------------ */
+
+/* mean of n host floats (reference reduce_mean_gpu, src/simulations.cu:269-341), single-pass fp64-accumulating
+ * device reduction; 64-bit indexing. */
+smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float *mean_out);
+/* out = a + b on the device (reference vector_add_gpu, src/gpu.cu:17-47). Host pointers. */
+smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device);
+
+/* ---- introspection used by the parity tests (device code paths, tiny outputs) ---------------------------------- */
+
+/* Raw per-month draws of `n_paths` paths starting at cfg->stream_offset, computed ON THE DEVICE with the same
+ * device functions the simulation kernel uses.  out[p * n_periods + m]:
+ *   bootstrap modes: table index drawn for month m;  GAUSSIAN modes: the raw 32-bit word behind month m. */
+smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *out);
+/* Philox4x32-10 block function on the device: out[4*i..] = philox(ctr[4*i..], key[0..1]) for i < n. */
+smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t n, int32_t device, uint32_t *out);
+
+/* ---- housekeeping ---------------------------------------------------------------------------------------- */
+
+const char *smmc_last_error(void);      /* thread-local message of the last failing call */
+const char *smmc_version(void);
+int32_t smmc_device_count(void);        /* number of usable (cc 10.x) CUDA devices; 0 if none */
+void smmc_shutdown(void);               /* free cached device workspaces */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMMC_H_ */

@@ -1,0 +1,195 @@
+"""ctypes binding of the CPU oracle (oracle/_build/liboracle.so) and of the compiled reference (oracle/_ref/*.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs.  Nothing under stock_market_monte_carlo_b200/ imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from stock_market_monte_carlo_b200 import _native as N
+from stock_market_monte_carlo_b200.data import sobol_directions
+from stock_market_monte_carlo_b200.simulations import Result, make_config
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(_HERE, "_build", "liboracle.so")
+REF_DIR = os.path.join(_HERE, "_ref")
+
+_lib = None
+_sobol_keep = None
+
+
+def build():
+    subprocess.run(["make", "-C", _HERE], check=True, capture_output=True)
+
+
+def load():
+    global _lib, _sobol_keep
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(ORACLE_SO):
+        build()
+    lib = C.CDLL(ORACLE_SO)
+    P = C.POINTER
+    lib.orc_rand_pcg.argtypes = [C.c_uint32]
+    lib.orc_rand_pcg.restype = C.c_uint32
+    lib.orc_xorshift.argtypes = [C.c_uint32]
+    lib.orc_xorshift.restype = C.c_uint32
+    lib.orc_compat_index.argtypes = [C.c_uint32, C.c_int32]
+    lib.orc_compat_index.restype = C.c_int32
+    lib.orc_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.orc_philox4x32_10.restype = None
+    lib.orc_sobol_set_table.argtypes = [C.c_void_p, C.c_int32]
+    lib.orc_sobol_point.argtypes = [C.c_uint64, C.c_int32]
+    lib.orc_sobol_point.restype = C.c_uint32
+    lib.orc_hist_bin.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int32]
+    lib.orc_hist_bin.restype = C.c_int32
+    lib.orc_hist_inv_width.argtypes = [C.c_float, C.c_float, C.c_int32]
+    lib.orc_hist_inv_width.restype = C.c_float
+    lib.orc_run.argtypes = [P(N.SmmcConfig), P(N.SmmcResult)]
+    lib.orc_run.restype = C.c_int
+    lib.orc_draws.argtypes = [P(N.SmmcConfig), C.c_int32, C.c_void_p]
+    lib.orc_draws.restype = C.c_int
+    lib.orc_reduce_mean.argtypes = [C.c_void_p, C.c_int64]
+    lib.orc_reduce_mean.restype = C.c_float
+    lib.orc_num_threads.restype = C.c_int
+    _sobol_keep = np.ascontiguousarray(sobol_directions())
+    lib.orc_sobol_set_table(_sobol_keep.ctypes.data, 1111)
+    _lib = lib
+    return lib
+
+
+def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+             gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
+             want_finals=False, want_block_partials=False) -> Result:
+    """Same signature and result as stock_market_monte_carlo_b200.simulate, computed by the CPU oracle."""
+    lib = load()
+    cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
+                            gauss_mean, gauss_std, target, hist_bins, hist_range)
+    res = N.SmmcResult()
+    out = Result()
+    nb = (int(n_simulations) + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
+    if want_finals:
+        out.finals = np.empty(int(n_simulations), dtype=np.float32)
+        res.finals = out.finals.ctypes.data
+    if want_block_partials:
+        out.block_means = np.zeros(nb, dtype=np.float32)
+        out.block_vars = np.zeros(nb, dtype=np.float32)
+        res.block_means = out.block_means.ctypes.data
+        res.block_vars = out.block_vars.ctypes.data
+    if hist_bins:
+        out.hist = np.zeros(int(hist_bins) + 2, dtype=np.uint64)
+        res.hist = out.hist.ctypes.data
+    rc = lib.orc_run(C.byref(cfg), C.byref(res))
+    if rc != 0:
+        raise ValueError("oracle rejected the configuration")
+    del keep
+    out.count, out.below_count = int(res.count), int(res.below_count)
+    out.mean, out.m2 = float(res.mean), float(res.m2)
+    return out
+
+
+def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0):
+    lib = load()
+    cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset)
+    out = np.zeros((int(n_paths), int(n_periods)), dtype=np.uint32)
+    if lib.orc_draws(C.byref(cfg), int(n_paths), out.ctypes.data) != 0:
+        raise ValueError("oracle rejected the configuration")
+    del keep
+    return out
+
+
+def philox(ctr, key):
+    lib = load()
+    ctr = np.ascontiguousarray(np.asarray(ctr, dtype=np.uint32).reshape(-1, 4))
+    key = np.ascontiguousarray(np.asarray(key, dtype=np.uint32).reshape(2))
+    out = np.zeros_like(ctr)
+    for i in range(ctr.shape[0]):
+        lib.orc_philox4x32_10(ctr[i].ctypes.data, key.ctypes.data, out[i].ctypes.data)
+    return out
+
+
+# ---- the compiled reference (oracle/_ref) ---------------------------------------------------------------------------
+
+def ref_available(name):
+    return os.path.exists(os.path.join(REF_DIR, name))
+
+
+_ref = {}
+
+
+def ref_lib(name):
+    if name not in _ref:
+        _ref[name] = C.CDLL(os.path.join(REF_DIR, name))
+    return _ref[name]
+
+
+def ref_mc_simulations(n, n_periods, initial_capital, returns, quiet=True):
+    """reference CPU v2 OpenMP bootstrap (src/simulations.cpp:204-266) -> (finals, threads)"""
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_mc_simulations.argtypes = [C.c_long, C.c_uint, C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.ref_mc_simulations.restype = C.c_int
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    out = np.empty(int(n), dtype=np.float32)
+    threads = lib.ref_mc_simulations(int(n), int(n_periods), float(initial_capital), r.ctypes.data, int(r.size),
+                                     out.ctypes.data, 1 if quiet else 0)
+    return out, threads
+
+
+def ref_gaussian_finals(n, n_periods, initial_capital, mean_pct, std_pct):
+    """reference sample_returns_gaussian + many_updates per path under OpenMP -> (finals, threads)"""
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_gaussian_finals.argtypes = [C.c_long, C.c_uint, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    lib.ref_gaussian_finals.restype = C.c_int
+    out = np.empty(int(n), dtype=np.float32)
+    threads = lib.ref_gaussian_finals(int(n), int(n_periods), float(initial_capital), float(mean_pct),
+                                      float(std_pct), out.ctypes.data)
+    return out, threads
+
+
+def ref_update_fund(fund, ret):
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_update_fund.argtypes = [C.c_float, C.c_float]
+    lib.ref_update_fund.restype = C.c_float
+    return float(lib.ref_update_fund(float(fund), float(ret)))
+
+
+def ref_i4_sobol(dim_num, point):
+    lib = ref_lib("libref_sobol.so")
+    lib.ref_i4_sobol.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_void_p]
+    q = np.zeros(int(dim_num), dtype=np.float32)
+    seed = C.c_int(int(point))
+    lib.ref_i4_sobol(int(dim_num), C.byref(seed), q.ctypes.data)
+    return q
+
+
+def ref_mc_simulations_gpu(n, n_periods, initial_capital, returns, n_gpus=1):
+    """the reference's own GPU library compiled for sm_100a (GPU box only) -> totals[N]"""
+    lib = ref_lib("libref_gpu.so")
+    lib.ref_mc_simulations_gpu.argtypes = [C.c_long, C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.ref_mc_simulations_gpu.restype = C.c_int
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    out = np.zeros(int(n), dtype=np.float32)
+    rc = lib.ref_mc_simulations_gpu(int(n), int(n_periods), float(initial_capital), r.ctypes.data, int(r.size),
+                                    out.ctypes.data, int(n_gpus))
+    if rc != 0:
+        raise RuntimeError(f"reference GPU run failed rc={rc}")
+    return out
+
+
+def ref_mc_simulations_gpu_reduceBlock(n, n_periods, initial_capital, returns):
+    lib = ref_lib("libref_gpu.so")
+    lib.ref_mc_simulations_gpu_reduceBlock.argtypes = [C.c_long, C.c_int, C.c_float, C.c_void_p, C.c_int,
+                                                       C.c_void_p, C.c_void_p]
+    lib.ref_mc_simulations_gpu_reduceBlock.restype = C.c_int
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    nb = (int(n) + 255) // 256
+    means = np.zeros(nb, dtype=np.float32)
+    variances = np.zeros(nb, dtype=np.float32)
+    rc = lib.ref_mc_simulations_gpu_reduceBlock(int(n), int(n_periods), float(initial_capital), r.ctypes.data,
+                                                int(r.size), means.ctypes.data, variances.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"reference GPU reduceBlock run failed rc={rc}")
+    return means, variances

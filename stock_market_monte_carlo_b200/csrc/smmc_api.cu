@@ -1,0 +1,548 @@
+// smmc_api.cu -- host side of the C ABI declared in include/smmc.h.
+//
+// Replaces the reference's launchers (src/simulations.cu:345-473 single GPU, :479-655 multi GPU plans): device
+// workspace is cached per device instead of being cudaMalloc'ed/freed on every call, the table upload and the
+// result download are the only host<->device copies, and multi-GPU runs shard the path-id range (RNG offset)
+// instead of re-running identical paths on every device (reference :621-622).
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/smmc.h"
+#include "smmc_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+smmc_status fail(smmc_status st, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return st;
+}
+
+#define CU(call)                                                                                       \
+  do {                                                                                                 \
+    cudaError_t e__ = (call);                                                                          \
+    if (e__ != cudaSuccess)                                                                            \
+      return fail(SMMC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+// grow-only device / pinned buffers
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct Context {
+  int device = -1;
+  bool ready = false;
+  int n_sms = 0;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  DevBuf returns, tbl, work, stats, finals, bmeans, bvars, scratch;
+  double *stats_host = nullptr;  // pinned
+  size_t stats_host_cap = 0;
+  std::mutex mu;
+};
+
+constexpr int kMaxDevices = 64;
+Context g_ctx[kMaxDevices];
+std::mutex g_ctx_mu;
+
+int g_device_count = -2;  // -2 = not probed
+
+int probe_devices() {
+  std::lock_guard<std::mutex> lk(g_ctx_mu);
+  if (g_device_count != -2) return g_device_count;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  int usable = 0;
+  for (int d = 0; d < n && d < kMaxDevices; d++) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major == 10) usable = d + 1;
+  }
+  g_device_count = usable;
+  return usable;
+}
+
+smmc_status get_context(int device, Context **out) {
+  const int n = probe_devices();
+  if (n <= 0) return fail(SMMC_ERR_NO_DEVICE, "no CUDA device of compute capability 10.x (sm_100a) is visible; this library has no CPU fallback");
+  if (device < 0 || device >= n) return fail(SMMC_ERR_INVALID_ARG, "device %d out of range [0,%d)", device, n);
+  Context &c = g_ctx[device];
+  std::lock_guard<std::mutex> lk(g_ctx_mu);
+  if (!c.ready) {
+    CU(cudaSetDevice(device));
+    int major = 0, sms = 0, optin = 0;
+    CU(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    if (major != 10) return fail(SMMC_ERR_NO_DEVICE, "device %d is not compute capability 10.x", device);
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    CU(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c.ev0));
+    CU(cudaEventCreate(&c.ev1));
+    c.device = device;
+    c.n_sms = sms;
+    c.smem_optin = (size_t)optin;
+    c.ready = true;
+  }
+  *out = &c;
+  return SMMC_OK;
+}
+
+bool is_bootstrap(int mode) {
+  return mode == SMMC_MODE_BOOTSTRAP_COMPAT || mode == SMMC_MODE_BOOTSTRAP || mode == SMMC_MODE_SOBOL_BOOTSTRAP;
+}
+bool is_sobol(int mode) { return mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN; }
+
+smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
+  if (!cfg || !out) return fail(SMMC_ERR_INVALID_ARG, "null config/result");
+  if (cfg->abi_version != SMMC_ABI_VERSION)
+    return fail(SMMC_ERR_INVALID_ARG, "abi_version %u != %u", cfg->abi_version, SMMC_ABI_VERSION);
+  if (cfg->mode < SMMC_MODE_BOOTSTRAP_COMPAT || cfg->mode > SMMC_MODE_SOBOL_GAUSSIAN)
+    return fail(SMMC_ERR_INVALID_ARG, "unknown mode %d", cfg->mode);
+  if (cfg->n_simulations < 0) return fail(SMMC_ERR_INVALID_ARG, "n_simulations < 0");
+  if (cfg->n_periods < 0) return fail(SMMC_ERR_INVALID_ARG, "n_periods < 0");
+  if (cfg->stream_offset % SMMC_BLOCK) return fail(SMMC_ERR_INVALID_ARG, "stream_offset must be a multiple of %d", SMMC_BLOCK);
+  if (is_bootstrap(cfg->mode)) {
+    if (!cfg->returns || cfg->n_returns < 1) return fail(SMMC_ERR_INVALID_ARG, "bootstrap modes need a non-empty returns table");
+    if (cfg->n_returns >= (1 << 24)) return fail(SMMC_ERR_INVALID_ARG, "n_returns must be < 2^24");
+  }
+  if (cfg->mode == SMMC_MODE_BOOTSTRAP_COMPAT && cfg->stream_offset + (uint64_t)cfg->n_simulations > 0x7fffffffull)
+    return fail(SMMC_ERR_INVALID_ARG, "BOOTSTRAP_COMPAT uses the reference's 32-bit path ids: stream_offset + N must be < 2^31");
+  if (is_sobol(cfg->mode)) {
+    if (cfg->n_periods > 1111) return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support at most 1111 periods (dimensions)");
+    if (cfg->stream_offset + (uint64_t)cfg->n_simulations + 256ull > 0x100000000ull)
+      return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support point indices < 2^32");
+  }
+  if (cfg->hist_bins < 0 || cfg->hist_bins > SMMC_MAX_HIST_BINS) return fail(SMMC_ERR_INVALID_ARG, "hist_bins out of range");
+  if (cfg->hist_bins > 0 && !(cfg->hist_hi > cfg->hist_lo)) return fail(SMMC_ERR_INVALID_ARG, "hist_hi must be > hist_lo");
+  if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !(cfg->flags & SMMC_FLAG_DEVICE_POINTERS))
+    return fail(SMMC_ERR_INVALID_ARG, "SMMC_FLAG_NO_SYNC requires SMMC_FLAG_DEVICE_POINTERS");
+  if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !out->stats_dev)
+    return fail(SMMC_ERR_INVALID_ARG, "SMMC_FLAG_NO_SYNC requires stats_dev");
+  return SMMC_OK;
+}
+
+int variant_from_env() {
+  const char *v = getenv("SMMC_ILP");
+  return v ? atoi(v) : 0;
+}
+
+smmc::PhiloxKeys make_keys(uint64_t seed) {
+  smmc::PhiloxKeys k;
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  for (int r = 0; r < 10; r++) {
+    k.k0[r] = k0;
+    k.k1[r] = k1;
+    k0 += smmc::kPhiloxW0;
+    k1 += smmc::kPhiloxW1;
+  }
+  return k;
+}
+
+// everything a launched shard needs to be collected later
+struct Pending {
+  Context *ctx = nullptr;
+  cudaStream_t stream = nullptr;
+  int64_t n = 0;
+  int64_t nb = 0;
+  int stats_len = 0;
+  bool device_ptrs = false;
+  float *finals_dev = nullptr, *bmeans_dev = nullptr, *bvars_dev = nullptr;
+  double *stats_dev = nullptr;
+  int launches = 0;
+};
+
+// Enqueue one shard [cfg->stream_offset, +N) on cfg->device.  Caller holds ctx->mu.
+smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx, Pending *pd) {
+  CU(cudaSetDevice(ctx->device));
+  const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
+  cudaStream_t st = devp ? (cudaStream_t)cfg->stream : ctx->stream;
+  const int64_t N = cfg->n_simulations;
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int bins = cfg->hist_bins;
+  const int slen = smmc_stats_len(bins);
+  const int variant = variant_from_env();
+
+  smmc::LaunchInfo li;
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, bins, ctx->n_sms, ctx->smem_optin, variant, &li))
+    return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %zu bytes of shared memory", cfg->n_returns, ctx->smem_optin);
+
+  smmc::KParams p;
+  memset(&p, 0, sizeof p);
+  p.n_paths = N;
+  p.path0 = cfg->stream_offset;
+  p.n_periods = cfg->n_periods;
+  p.n_returns = cfg->n_returns;
+  p.compat_seed = (uint32_t)cfg->seed;
+  p.keys = make_keys(cfg->seed);
+  {
+    const float mu = cfg->gauss_mean * 0.01f, sigma = cfg->gauss_std * 0.01f;
+    p.gc.a = 1.0f + mu;
+    p.gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
+    p.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)sigma);
+  }
+  p.v0 = cfg->initial_capital;
+  p.target = cfg->target;
+  p.hist_lo = cfg->hist_lo;
+  p.hist_inv_w = bins > 0 ? (float)((double)bins / ((double)cfg->hist_hi - (double)cfg->hist_lo)) : 0.0f;
+  p.hist_bins = bins;
+  pd->launches = 0;
+
+  // ---- table: upload (host pointers) and expand to the scaled, bank-private replicated layout
+  if (is_bootstrap(cfg->mode)) {
+    const int n = cfg->n_returns;
+    const float *src = cfg->returns;
+    if (!devp) {
+      CU(ctx->returns.reserve((size_t)n * 4));
+      CU(cudaMemcpyAsync(ctx->returns.p, cfg->returns, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+      src = (const float *)ctx->returns.p;
+    }
+    const uint32_t tbl_bytes = (uint32_t)((((size_t)(n + 1) * li.rep * 4) + 15) & ~(size_t)15);
+    CU(ctx->tbl.reserve(tbl_bytes));
+    smmc::launch_prep_table(src, n, li.rep, (float *)ctx->tbl.p, tbl_bytes / 4, st);
+    CU(cudaGetLastError());
+    pd->launches++;
+    p.tbl_rep = (const float *)ctx->tbl.p;
+    p.tbl_bytes = tbl_bytes;
+    p.rep4 = (uint32_t)li.rep * 4u;
+    p.nr4 = (uint32_t)n * (uint32_t)li.rep * 4u;
+    p.idx_scale = (float)n * 2.3283064365386963e-10f;  // exact: n < 2^24
+  } else {
+    p.rep4 = 4u;
+  }
+
+  // ---- workspace: [cta_partials grid*4 doubles][hist_g (bins+2) u64][ticket u32 (+pad)]
+  const size_t part_bytes = (size_t)li.grid * 4 * sizeof(double);
+  const size_t hist_bytes = (size_t)(bins + 2) * sizeof(unsigned long long);
+  CU(ctx->work.reserve(part_bytes + hist_bytes + 16));
+  char *w = (char *)ctx->work.p;
+  p.cta_partials = (double *)w;
+  p.hist_g = (unsigned long long *)(w + part_bytes);
+  p.ticket = (unsigned int *)(w + part_bytes + hist_bytes);
+  CU(cudaMemsetAsync(w + part_bytes, 0, hist_bytes + 16, st));
+
+  if (devp && out->stats_dev) {
+    p.stats = out->stats_dev;
+  } else {
+    CU(ctx->stats.reserve((size_t)slen * sizeof(double)));
+    p.stats = (double *)ctx->stats.p;
+  }
+
+  // ---- outputs
+  if (devp) {
+    p.finals = out->finals;
+    p.bmeans = out->block_means;
+    p.bvars = out->block_vars;
+  } else {
+    if (out->finals && N > 0) {
+      CU(ctx->finals.reserve((size_t)N * 4));
+      p.finals = (float *)ctx->finals.p;
+    }
+    if (out->block_means && nb > 0) {
+      CU(ctx->bmeans.reserve((size_t)nb * 4));
+      p.bmeans = (float *)ctx->bmeans.p;
+    }
+    if (out->block_vars && nb > 0) {
+      CU(ctx->bvars.reserve((size_t)nb * 4));
+      p.bvars = (float *)ctx->bvars.p;
+    }
+  }
+
+  if (is_sobol(cfg->mode)) return fail(SMMC_ERR_UNSUPPORTED, "Sobol modes are not built yet");
+
+  CU(cudaEventRecord(ctx->ev0, st));
+  CU(smmc::launch_mc(cfg->mode, p, li, variant, st));
+  CU(cudaEventRecord(ctx->ev1, st));
+  pd->launches++;
+
+  pd->ctx = ctx;
+  pd->stream = st;
+  pd->n = N;
+  pd->nb = nb;
+  pd->stats_len = slen;
+  pd->device_ptrs = devp;
+  pd->finals_dev = p.finals;
+  pd->bmeans_dev = p.bmeans;
+  pd->bvars_dev = p.bvars;
+  pd->stats_dev = p.stats;
+  return SMMC_OK;
+}
+
+// Download results of a shard into `out` (host pointers) and its statistics vector into stats_host.
+smmc_status collect(const Pending &pd, const smmc_result *out, double *stats_host, float *device_ms) {
+  Context *ctx = pd.ctx;
+  CU(cudaSetDevice(ctx->device));
+  if (ctx->stats_host_cap < (size_t)pd.stats_len) {
+    if (ctx->stats_host) cudaFreeHost(ctx->stats_host);
+    ctx->stats_host = nullptr;
+    CU(cudaMallocHost(&ctx->stats_host, (size_t)pd.stats_len * sizeof(double)));
+    ctx->stats_host_cap = (size_t)pd.stats_len;
+  }
+  CU(cudaMemcpyAsync(ctx->stats_host, pd.stats_dev, (size_t)pd.stats_len * sizeof(double), cudaMemcpyDeviceToHost, pd.stream));
+  if (!pd.device_ptrs) {
+    if (out->finals && pd.n > 0)
+      CU(cudaMemcpyAsync(out->finals, pd.finals_dev, (size_t)pd.n * 4, cudaMemcpyDeviceToHost, pd.stream));
+    if (out->block_means && pd.nb > 0)
+      CU(cudaMemcpyAsync(out->block_means, pd.bmeans_dev, (size_t)pd.nb * 4, cudaMemcpyDeviceToHost, pd.stream));
+    if (out->block_vars && pd.nb > 0)
+      CU(cudaMemcpyAsync(out->block_vars, pd.bvars_dev, (size_t)pd.nb * 4, cudaMemcpyDeviceToHost, pd.stream));
+  }
+  CU(cudaStreamSynchronize(pd.stream));
+  memcpy(stats_host, ctx->stats_host, (size_t)pd.stats_len * sizeof(double));
+  float ms = 0.0f;
+  CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  *device_ms = ms;
+  return SMMC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t smmc_stats_len(int32_t hist_bins) { return SMMC_STATS_HEADER + (hist_bins > 0 ? hist_bins : 0) + 2; }
+
+smmc_status smmc_stats_finalize(const double *stats, int32_t hist_bins, float initial_capital, uint64_t *count,
+                                uint64_t *below_count, double *mean, double *m2, uint64_t *hist) {
+  if (!stats) return fail(SMMC_ERR_INVALID_ARG, "null stats");
+  const double n = stats[0];
+  if (count) *count = (uint64_t)n;
+  if (below_count) *below_count = (uint64_t)stats[1];
+  if (n > 0.0) {
+    const double s1 = stats[2], s2 = stats[3];
+    if (mean) *mean = (double)initial_capital + s1 / n;
+    if (m2) {
+      const double v = s2 - s1 * s1 / n;
+      *m2 = v > 0.0 ? v : 0.0;
+    }
+  } else {
+    if (mean) *mean = 0.0;
+    if (m2) *m2 = 0.0;
+  }
+  if (hist && hist_bins > 0)
+    for (int i = 0; i < hist_bins + 2; i++) hist[i] = (uint64_t)stats[SMMC_STATS_HEADER + i];
+  return SMMC_OK;
+}
+
+smmc_status smmc_run(const smmc_config *cfg, smmc_result *out) {
+  smmc_status st = validate(cfg, out);
+  if (st != SMMC_OK) return st;
+  Context *ctx = nullptr;
+  st = get_context(cfg->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  Pending pd;
+  st = enqueue(cfg, out, ctx, &pd);
+  if (st != SMMC_OK) return st;
+  out->gpu_launches = pd.launches;
+  if (cfg->flags & SMMC_FLAG_NO_SYNC) return SMMC_OK;
+  std::vector<double> stats((size_t)pd.stats_len);
+  float ms = 0.0f;
+  st = collect(pd, out, stats.data(), &ms);
+  if (st != SMMC_OK) return st;
+  out->device_ms = ms;
+  return smmc_stats_finalize(stats.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count,
+                             &out->mean, &out->m2, out->hist);
+}
+
+smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out) {
+  smmc_status st = validate(cfg, out);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "smmc_run_multi takes host pointers");
+  const int ndev = probe_devices();
+  if (ndev <= 0) return fail(SMMC_ERR_NO_DEVICE, "no CUDA device of compute capability 10.x (sm_100a) is visible; this library has no CPU fallback");
+  if (n_gpus < 1 || n_gpus > ndev) return fail(SMMC_ERR_INVALID_ARG, "n_gpus %d out of range [1,%d]", n_gpus, ndev);
+  if (n_gpus == 1) return smmc_run(cfg, out);
+
+  const int64_t N = cfg->n_simulations;
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int64_t per = (nb + n_gpus - 1) / n_gpus;  // logical blocks per device
+  std::vector<Pending> pend((size_t)n_gpus);
+  std::vector<smmc_config> cfgs((size_t)n_gpus, *cfg);
+  std::vector<smmc_result> outs((size_t)n_gpus, *out);
+  std::vector<Context *> ctxs((size_t)n_gpus, nullptr);
+  for (int g = 0; g < n_gpus; g++) {
+    st = get_context(g, &ctxs[g]);
+    if (st != SMMC_OK) return st;
+  }
+  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.lock();
+  smmc_status rc = SMMC_OK;
+  int launched = 0;
+  for (int g = 0; g < n_gpus && rc == SMMC_OK; g++) {
+    int64_t b0 = per * g, b1 = per * (g + 1);
+    if (b0 > nb) b0 = nb;
+    if (b1 > nb) b1 = nb;
+    const int64_t p0 = b0 * SMMC_BLOCK;
+    int64_t p1 = b1 * SMMC_BLOCK;
+    if (p1 > N) p1 = N;
+    cfgs[g].device = g;
+    cfgs[g].stream_offset = cfg->stream_offset + (uint64_t)p0;
+    cfgs[g].n_simulations = p1 - p0;
+    outs[g].finals = out->finals ? out->finals + p0 : nullptr;
+    outs[g].block_means = out->block_means ? out->block_means + b0 : nullptr;
+    outs[g].block_vars = out->block_vars ? out->block_vars + b0 : nullptr;
+    rc = enqueue(&cfgs[g], &outs[g], ctxs[g], &pend[g]);
+    if (rc == SMMC_OK) launched++;
+  }
+  const int slen = smmc_stats_len(cfg->hist_bins);
+  std::vector<double> total((size_t)slen, 0.0), part((size_t)slen);
+  float ms_max = 0.0f;
+  int launches = 0;
+  for (int g = 0; g < launched; g++) {
+    float ms = 0.0f;
+    smmc_status s2 = collect(pend[g], &outs[g], part.data(), &ms);
+    if (s2 != SMMC_OK && rc == SMMC_OK) rc = s2;
+    for (int i = 0; i < slen; i++) total[i] += part[i];  // rank order: deterministic
+    if (ms > ms_max) ms_max = ms;
+    launches += pend[g].launches;
+  }
+  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.unlock();
+  if (rc != SMMC_OK) return rc;
+  out->device_ms = ms_max;
+  out->gpu_launches = launches;
+  return smmc_stats_finalize(total.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count,
+                             &out->mean, &out->m2, out->hist);
+}
+
+smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float *mean_out) {
+  if (!vec || !mean_out || n <= 0) return fail(SMMC_ERR_INVALID_ARG, "reduce_mean: need n > 0 and non-null pointers");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  const size_t part = (size_t)ctx->n_sms * 4 * sizeof(double);
+  CU(ctx->scratch.reserve((size_t)n * 4));
+  CU(ctx->work.reserve(part + 32));
+  char *w = (char *)ctx->work.p;
+  CU(cudaMemcpyAsync(ctx->scratch.p, vec, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaMemsetAsync(w + part, 0, 32, ctx->stream));
+  CU(smmc::launch_reduce_sum((const float *)ctx->scratch.p, n, (double *)w, (unsigned int *)(w + part + 16),
+                             (double *)(w + part), ctx->n_sms, ctx->stream));
+  double sum = 0.0;
+  CU(cudaMemcpyAsync(&sum, w + part, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *mean_out = (float)(sum / (double)n);
+  return SMMC_OK;
+}
+
+smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device) {
+  if (n < 0 || (n > 0 && (!out || !a || !b))) return fail(SMMC_ERR_INVALID_ARG, "vector_add: bad arguments");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  if (n == 0) return SMMC_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  CU(ctx->scratch.reserve((size_t)n * 12));
+  float *da = (float *)ctx->scratch.p, *db = da + n, *dout = db + n;
+  CU(cudaMemcpyAsync(da, a, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaMemcpyAsync(db, b, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(smmc::launch_vector_add(dout, da, db, n, ctx->stream));
+  CU(cudaMemcpyAsync(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return SMMC_OK;
+}
+
+smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  smmc_status st = validate(cfg, &dummy);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "debug_draws takes host pointers");
+  if (n_paths < 0 || !outbuf) return fail(SMMC_ERR_INVALID_ARG, "debug_draws: bad arguments");
+  if (is_sobol(cfg->mode)) return fail(SMMC_ERR_UNSUPPORTED, "Sobol modes are not built yet");
+  Context *ctx = nullptr;
+  st = get_context(cfg->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(cfg->device));
+  smmc::KParams p;
+  memset(&p, 0, sizeof p);
+  p.path0 = cfg->stream_offset;
+  p.n_periods = cfg->n_periods;
+  p.n_returns = cfg->n_returns;
+  p.compat_seed = (uint32_t)cfg->seed;
+  p.keys = make_keys(cfg->seed);
+  p.idx_scale = (float)cfg->n_returns * 2.3283064365386963e-10f;
+  const size_t bytes = (size_t)n_paths * (size_t)cfg->n_periods * 4;
+  if (bytes == 0) return SMMC_OK;
+  CU(ctx->scratch.reserve(bytes));
+  CU(smmc::launch_debug_draws(cfg->mode, p, n_paths, (uint32_t *)ctx->scratch.p, ctx->stream));
+  CU(cudaMemcpyAsync(outbuf, ctx->scratch.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return SMMC_OK;
+}
+
+smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t n, int32_t device, uint32_t *outbuf) {
+  if (!ctr || !key || !outbuf || n < 0) return fail(SMMC_ERR_INVALID_ARG, "debug_philox: bad arguments");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  if (n == 0) return SMMC_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  CU(ctx->scratch.reserve((size_t)n * 32));
+  uint32_t *dc = (uint32_t *)ctx->scratch.p, *dout = dc + (size_t)n * 4;
+  CU(cudaMemcpyAsync(dc, ctr, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  CU(smmc::launch_debug_philox(dc, make_keys((uint64_t)key[0] | ((uint64_t)key[1] << 32)), n, dout, ctx->stream));
+  CU(cudaMemcpyAsync(outbuf, dout, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return SMMC_OK;
+}
+
+const char *smmc_last_error(void) { return g_err; }
+const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 1)"; }
+int32_t smmc_device_count(void) { return probe_devices(); }
+
+void smmc_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g_ctx_mu);
+  for (int d = 0; d < kMaxDevices; d++) {
+    Context &c = g_ctx[d];
+    if (!c.ready) continue;
+    cudaSetDevice(d);
+    c.returns.release();
+    c.tbl.release();
+    c.work.release();
+    c.stats.release();
+    c.finals.release();
+    c.bmeans.release();
+    c.bvars.release();
+    c.scratch.release();
+    if (c.stats_host) cudaFreeHost(c.stats_host);
+    c.stats_host = nullptr;
+    c.stats_host_cap = 0;
+    cudaEventDestroy(c.ev0);
+    cudaEventDestroy(c.ev1);
+    cudaStreamDestroy(c.stream);
+    c.ready = false;
+  }
+}
+
+}  // extern "C"

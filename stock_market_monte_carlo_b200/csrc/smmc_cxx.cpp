@@ -1,0 +1,125 @@
+// smmc_cxx.cpp -- the reference's C++ entry points as marshalling wrappers over the C ABI (include/smmc.h).
+// Replaces the "CPP callable function" section of reference src/simulations.cu:657-697 and src/gpu.cpp.
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+#include "../../include/stock_market_monte_carlo/simulations.h"
+
+namespace {
+
+// reference error behaviour: message on stderr, then exit(code) (gpuErrchk, src/simulations.cu:23-30)
+void die_on(smmc_status st, const char *what) {
+  if (st == SMMC_OK) return;
+  std::fprintf(stderr, "SMMCassert: %s: %s\n", what, smmc_last_error());
+  std::exit((int)st);
+}
+
+smmc_config base_config(long N, int n_periods, float initial_capital, std::vector<float> &returns,
+                        const smmc::Options &opt) {
+  smmc_config c;
+  std::memset(&c, 0, sizeof c);
+  c.abi_version = SMMC_ABI_VERSION;
+  c.mode = opt.mode;
+  c.n_simulations = N;
+  c.n_periods = n_periods;
+  c.n_returns = (int)returns.size();  // the reference passes returns.size() as int (src/simulations.cu:670)
+  c.returns = returns.empty() ? nullptr : returns.data();
+  c.seed = opt.seed;
+  c.stream_offset = opt.stream_offset;
+  c.initial_capital = initial_capital;
+  c.gauss_mean = opt.gauss_mean;
+  c.gauss_std = opt.gauss_std;
+  c.target = opt.target < 0.0f ? initial_capital : opt.target;
+  c.hist_bins = opt.hist_bins;
+  c.hist_lo = opt.hist_lo;
+  c.hist_hi = opt.hist_hi;
+  return c;
+}
+
+void export_stats(const smmc_result &r, smmc::Statistics *s) {
+  if (!s) return;
+  s->count = r.count;
+  s->below_count = r.below_count;
+  s->mean = r.mean;
+  s->m2 = r.m2;
+  s->device_ms = r.device_ms;
+}
+
+}  // namespace
+
+void mc_simulations_gpu(std::atomic<long> &n_simulations, long N, int n_periods, float initial_capital,
+                        std::vector<float> &returns, std::vector<float> *totals, int n_gpus,
+                        const smmc::Options &opt, smmc::Statistics *stats) {
+  smmc_config c = base_config(N, n_periods, initial_capital, returns, opt);
+  smmc_result r;
+  std::memset(&r, 0, sizeof r);
+  std::vector<float> fresh;
+  if (totals) {
+    fresh.resize((size_t)(N > 0 ? N : 0));
+    r.finals = fresh.data();
+  }
+  if (stats && opt.hist_bins > 0) {
+    stats->hist.assign((size_t)opt.hist_bins + 2, 0);
+    r.hist = stats->hist.data();
+  }
+  die_on(smmc_run_multi(&c, n_gpus, &r), "mc_simulations_gpu");
+  if (totals) totals->swap(fresh);  // the reference swaps in a fresh N-element vector (src/simulations.cu:643-644)
+  export_stats(r, stats);
+  n_simulations.store(N, std::memory_order_release);  // results are visible before the progress counter moves
+}
+
+void mc_simulations_gpu(std::atomic<long> &n_simulations, long N, int n_periods, float initial_capital,
+                        std::vector<float> &returns, std::vector<float> &totals, int n_gpus) {
+  mc_simulations_gpu(n_simulations, N, n_periods, initial_capital, returns, &totals, n_gpus, smmc::Options{}, nullptr);
+}
+
+void mc_simulations_gpu_reduceBlock(std::atomic<long> &n_simulations, long N, int n_periods, float initial_capital,
+                                    std::vector<float> &returns, std::vector<float> *means,
+                                    std::vector<float> *variances, int n_gpus, const smmc::Options &opt,
+                                    smmc::Statistics *stats) {
+  if (n_gpus != 1) throw std::invalid_argument(">1 GPU not yet supported for reduceBlock version!!");
+  smmc_config c = base_config(N, n_periods, initial_capital, returns, opt);
+  smmc_result r;
+  std::memset(&r, 0, sizeof r);
+  const size_t nb = N > 0 ? (size_t)((N + SMMC_BLOCK - 1) / SMMC_BLOCK) : 0;
+  if (means) {
+    means->assign(nb, 0.0f);  // reference: resize + fill 0 (src/simulations.cu:429-432)
+    r.block_means = means->data();
+  }
+  if (variances) {
+    variances->assign(nb, 0.0f);
+    r.block_vars = variances->data();
+  }
+  if (stats && opt.hist_bins > 0) {
+    stats->hist.assign((size_t)opt.hist_bins + 2, 0);
+    r.hist = stats->hist.data();
+  }
+  die_on(smmc_run(&c, &r), "mc_simulations_gpu_reduceBlock");
+  export_stats(r, stats);
+  n_simulations.store(N, std::memory_order_release);
+}
+
+void mc_simulations_gpu_reduceBlock(std::atomic<long> &n_simulations, long N, int n_periods, float initial_capital,
+                                    std::vector<float> &returns, std::vector<float> &means,
+                                    std::vector<float> &variances, int n_gpus) {
+  mc_simulations_gpu_reduceBlock(n_simulations, N, n_periods, initial_capital, returns, &means, &variances, n_gpus,
+                                 smmc::Options{}, nullptr);
+}
+
+float reduce_mean_gpu(std::vector<float> &vec, long n) {
+  float mean = 0.0f;
+  die_on(smmc_reduce_mean(vec.data(), n, 0, &mean), "reduce_mean_gpu");
+  return mean;
+}
+
+void vector_add(float *out, float *a, float *b, int n) {
+  for (int i = 0; i < n; i++) out[i] = a[i] + b[i];
+}
+
+void vector_add_gpu(float *out, float *a, float *b, int n) {
+  die_on(smmc_vector_add(out, a, b, n, 0), "vector_add_gpu");
+}

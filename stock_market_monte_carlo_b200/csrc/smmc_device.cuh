@@ -1,0 +1,195 @@
+// smmc_device.cuh -- device building blocks of the Monte Carlo portfolio path (sm_100a).
+//
+// Arithmetic contracts are stated in DESIGN.md and restated on the CPU in oracle/smmc_oracle.c; reference
+// citations (/root/reference) are given per function.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace smmc {
+
+constexpr int kBlock = 256;          // logical block = THREADS_PER_BLOCK of the reference (src/simulations.cu:17)
+constexpr int kPathsPerLane = 8;     // one warp owns one logical block: lane l holds paths 32*j + l, j < 8
+
+// ---- reference stream (BOOTSTRAP_COMPAT) ----------------------------------------------------------------
+
+// PCG RXS-M-XS output hash used as per-path seed (reference src/simulations.cu:62-67; the LCG advance on its
+// line 64 acts on a by-value copy and is dead code)
+__device__ __forceinline__ uint32_t rand_pcg(uint32_t s) {
+  uint32_t word = ((s >> ((s >> 28u) + 4u)) ^ s) * 277803737u;
+  return (word >> 22u) ^ word;
+}
+
+// reference src/simulations.cu:69-75
+__device__ __forceinline__ uint32_t xorshift(uint32_t y) {
+  y ^= y << 11;
+  y ^= y >> 7;
+  return y ^ (y >> 12);
+}
+
+// ---- Philox4x32-10 ------------------------------------------------------------------------------------------
+// Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3" (SC'11).  Round keys are
+// precomputed on the host (they depend on the seed only) and live in the kernel parameter constant bank.
+struct PhiloxKeys {
+  uint32_t k0[10];
+  uint32_t k1[10];
+};
+
+constexpr uint32_t kPhiloxM0 = 0xD2511F53u;
+constexpr uint32_t kPhiloxM1 = 0xCD9E8D57u;
+constexpr uint32_t kPhiloxW0 = 0x9E3779B9u;
+constexpr uint32_t kPhiloxW1 = 0xBB67AE85u;
+
+__device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t k0,
+                                             uint32_t k1) {
+  const uint64_t p0 = (uint64_t)kPhiloxM0 * c0;  // IMAD.WIDE.U32
+  const uint64_t p1 = (uint64_t)kPhiloxM1 * c2;
+  const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;  // LOP3 (3-input xor)
+  const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+  c1 = (uint32_t)p1;
+  c3 = (uint32_t)p0;
+  c0 = n0;
+  c2 = n2;
+}
+
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              const PhiloxKeys &k, uint32_t (&out)[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) philox_round(c0, c1, c2, c3, k.k0[r], k.k1[r]);
+  out[0] = c0;
+  out[1] = c1;
+  out[2] = c2;
+  out[3] = c3;
+}
+
+// Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed.
+// Word j of call q serves month 4q + j.  The per-lane quantity (path_lo) sits in counter word 1 so that in
+// rounds 1-3 one of the two 32x32->64 multiplies has warp-uniform operands (q, tag, path_hi and the key are
+// uniform over a 256-path block): the compiler hoists those to once per call per warp, and only 16 of the
+// 20 multiplies of a call are per-lane work.
+constexpr uint32_t kTagBootstrap = 0x424F4F54u;   // "BOOT"
+constexpr uint32_t kTagGaussian = 0x47415553u;    // "GAUS"
+constexpr uint32_t kTagSobolShift = 0x534F424Cu;  // "SOBL"
+
+__device__ __forceinline__ void stream_words(uint32_t path_lo, uint32_t path_hi, uint32_t q, uint32_t tag,
+                                             const PhiloxKeys &k, uint32_t (&w)[4]) {
+  philox4x32_10(q, path_lo, tag, path_hi, k, w);
+}
+
+// ---- MUFU wrappers ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sin_approx(float x) {
+  float y;
+  asm("sin.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float cos_approx(float x) {
+  float y;
+  asm("cos.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// ---- Gaussian growth factors (Box-Muller on two 32-bit words) ----------------------------------------------
+// r ~ N(mean, std) percent, fund *= (100 + r)/100 (reference src/simulations.cpp:14-16, :41-55), evaluated as
+// g = (1 + mean/100) + (std/100) z with z = sqrt(-2 ln u) {cos,sin}(v):
+//   u = (wa + 1/2) 2^-32 in (0,1],  v = (int(wb) + 1/2) pi 2^-31 in (-pi, pi),
+//   (std/100) sqrt(-2 ln u) = sqrt(lg2(u) * k),  k = -2 ln2 (std/100)^2.
+struct GaussConsts {
+  float a;  // 1 + mean/100
+  float k;  // -2 ln2 sigma^2
+};
+
+__device__ __forceinline__ void gauss_pair(uint32_t wa, uint32_t wb, const GaussConsts gc, float &g0, float &g1) {
+  const float u = fmaf(__uint2float_rn(wa), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+  const float v = fmaf(__int2float_rn((int)wb), 1.4629180792671596e-09f, 7.3145903963357981e-10f);
+  const float t = lg2_approx(u) * gc.k;
+  const float rs = sqrt_approx(t);
+  g0 = fmaf(rs, cos_approx(v), gc.a);
+  g1 = fmaf(rs, sin_approx(v), gc.a);
+}
+
+// ---- inverse normal CDF (SOBOL_GAUSSIAN) ----------------------------------------------------------------------
+// Giles, "Approximating the erfinv function" (GPU Computing Gems, 2012), single-precision central/tail split.
+// Returns p*y with z = sqrt(2) * p * y; the caller folds sqrt(2)*sigma into its FFMA.
+__device__ __forceinline__ float erfinv_py(uint32_t x32) {
+  const float y = fmaf(__int2float_rn((int)(x32 ^ 0x80000000u)), 4.6566128730773926e-10f, 2.3283064365386963e-10f);
+  const float t = fmaxf(fmaf(-y, y, 1.0f), 5.9604645e-08f);
+  float w = lg2_approx(t) * -0.69314718055994530942f;
+  float p;
+  if (w < 5.0f) {
+    w = w - 2.5f;
+    p = 2.81022636e-08f;
+    p = fmaf(p, w, 3.43273939e-07f);
+    p = fmaf(p, w, -3.5233877e-06f);
+    p = fmaf(p, w, -4.39150654e-06f);
+    p = fmaf(p, w, 0.00021858087f);
+    p = fmaf(p, w, -0.00125372503f);
+    p = fmaf(p, w, -0.00417768164f);
+    p = fmaf(p, w, 0.246640727f);
+    p = fmaf(p, w, 1.50140941f);
+  } else {
+    w = sqrt_approx(w) - 3.0f;
+    p = -0.000200214257f;
+    p = fmaf(p, w, 0.000100950558f);
+    p = fmaf(p, w, 0.00134934322f);
+    p = fmaf(p, w, -0.00367342844f);
+    p = fmaf(p, w, 0.00573950773f);
+    p = fmaf(p, w, -0.0076224613f);
+    p = fmaf(p, w, 0.00943887047f);
+    p = fmaf(p, w, 1.00167406f);
+    p = fmaf(p, w, 2.83297682f);
+  }
+  return p * y;
+}
+
+// ---- histogram bin rule (DESIGN.md "Histogram") ------------------------------------------------------------
+__device__ __forceinline__ int hist_bin(float x, float lo, float inv_w, int bins) {
+  const float t = (x - lo) * inv_w;
+  if (!(t >= 0.0f)) return 0;
+  if (t >= (float)bins) return bins + 1;
+  return 1 + (int)t;
+}
+
+// ---- TMA bulk copy + mbarrier (table staging) ----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk async copy (UBLKCP), completion signalled on the mbarrier; bytes % 16 == 0, 16-B aligned
+__device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+}  // namespace smmc

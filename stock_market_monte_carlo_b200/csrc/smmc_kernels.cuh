@@ -1,0 +1,70 @@
+// smmc_kernels.cuh -- kernel parameter block and launch interface between smmc_kernels.cu (device code) and
+// smmc_api.cu (host side of the C ABI).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "smmc_device.cuh"
+
+namespace smmc {
+
+struct KParams {
+  int64_t n_paths;       // N of this launch
+  uint64_t path0;        // global id of path 0 (multiple of 256)
+  int32_t n_periods;     // P
+  int32_t n_returns;     // n
+  uint32_t compat_seed;  // added to the PCG seed input in BOOTSTRAP_COMPAT
+  // return table, scaled by 0.01f and replicated `rep` times per entry ([n+1][rep], entry n is a zero pad)
+  const float *tbl_rep;
+  uint32_t tbl_bytes;  // bytes to stage (multiple of 16)
+  uint32_t rep4;       // rep * 4: bytes per table row
+  uint32_t nr4;        // n * rep * 4: mulhi(word, nr4) = byte offset of the row + sub-row fraction
+  float idx_scale;     // compat: float(n) * 2^-32
+  PhiloxKeys keys;
+  GaussConsts gc;
+  float sigma_sqrt2;  // SOBOL_GAUSSIAN: sqrt(2) * std/100
+  float v0;
+  float target;
+  float hist_lo, hist_inv_w;
+  int32_t hist_bins;
+  // outputs (device pointers, nullable)
+  float *finals;
+  float *bmeans;
+  float *bvars;
+  // workspace
+  double *cta_partials;       // [grid][4] = n, mean, M2, below
+  unsigned long long *hist_g;  // [bins+2], zeroed before launch
+  unsigned int *ticket;        // zeroed before launch
+  double *stats;               // [SMMC_STATS_HEADER + bins + 2]
+  // Sobol
+  const uint32_t *sobol_lo;     // [P][8]      direction numbers of bits 0..7, month-major
+  const uint32_t *sobol_hi;     // [24][P_pad] direction numbers of bits 8..31, bit-major
+  const uint32_t *sobol_shift;  // [P_pad]     digital shift per month (0 = plain Sobol)
+  int32_t sobol_ppad;
+};
+
+struct LaunchInfo {
+  int grid;
+  int threads;
+  size_t smem_bytes;
+  int rep;  // table replication factor chosen
+};
+
+// Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
+bool plan_launch(int mode, int n_returns, int hist_bins, int n_sms, size_t smem_optin, int variant, LaunchInfo *li);
+
+// Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
+void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);
+
+cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
+
+// introspection kernels (parity tests)
+cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, uint32_t *out_dev, cudaStream_t s);
+cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n, uint32_t *out_dev, cudaStream_t s);
+
+// small reference entry points
+cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
+                              double *sum_dev, int n_sms, cudaStream_t s);
+cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, cudaStream_t s);
+
+}  // namespace smmc

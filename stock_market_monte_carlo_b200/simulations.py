@@ -1,0 +1,263 @@
+"""Host-side mirror of the reference's GPU entry points (reference include/stock_market_monte_carlo/simulations.h:69-86)
+over the C ABI of libsmmc.so.  Same names, argument order, argument meaning and error behaviour:
+
+    mc_simulations_gpu(n_simulations, max_n_simulations, n_periods, initial_capital, returns, totals, n_gpus)
+    mc_simulations_gpu_reduceBlock(n_simulations, max_n_simulations, n_periods, initial_capital, returns,
+                                   means, variances, n_gpus)
+    reduce_mean_gpu(vec, n)            vector_add(out, a, b, n)            vector_add_gpu(out, a, b, n)
+
+`std::atomic<long>&` becomes an `AtomicLong`, `std::vector<float>&` a `FloatVector` (a resizable wrapper around a
+float32 numpy array).  `simulate()` is the general entry point (seed, mode, fused statistics, histogram,
+P(target)); `simulate_device()` is the asynchronous variant over device pointers (torch tensors).
+"""
+import ctypes as C
+import threading
+from dataclasses import dataclass, field
+from typing import Optional
+
+import numpy as np
+
+from . import _native as N
+
+
+class AtomicLong:
+    """Mirror of the `std::atomic<long>& n_simulations` progress counter of the reference API."""
+
+    def __init__(self, value=0):
+        self._v = int(value)
+        self._lock = threading.Lock()
+
+    def load(self):
+        with self._lock:
+            return self._v
+
+    def store(self, v):
+        with self._lock:
+            self._v = int(v)
+
+    value = property(load, store)
+
+    def __int__(self):
+        return self.load()
+
+
+class FloatVector:
+    """Mirror of `std::vector<float>`: `.array` is the float32 storage, replaced/resized by the callee."""
+
+    def __init__(self, data=()):
+        self.array = np.ascontiguousarray(np.asarray(data, dtype=np.float32))
+
+    def size(self):
+        return int(self.array.size)
+
+    def resize(self, n, value=0.0):
+        old = self.array
+        self.array = np.full(int(n), value, dtype=np.float32)
+        k = min(old.size, int(n))
+        self.array[:k] = old[:k]
+
+    def __len__(self):
+        return self.size()
+
+    def __getitem__(self, i):
+        return self.array[i]
+
+
+def _as_f32(x):
+    if isinstance(x, FloatVector):
+        return x.array
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float32))
+
+
+@dataclass
+class Result:
+    count: int = 0
+    below_count: int = 0
+    mean: float = 0.0
+    m2: float = 0.0
+    finals: Optional[np.ndarray] = None
+    block_means: Optional[np.ndarray] = None
+    block_vars: Optional[np.ndarray] = None
+    hist: Optional[np.ndarray] = None
+    device_ms: float = 0.0
+    gpu_launches: int = 0
+
+    @property
+    def variance(self):
+        return self.m2 / self.count if self.count else 0.0
+
+    @property
+    def std(self):
+        return self.variance ** 0.5
+
+    @property
+    def p_below_target(self):
+        return self.below_count / self.count if self.count else 0.0
+
+
+def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+                gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None, device=0,
+                flags=0, stream=0, returns_ptr=None, n_returns=None):
+    cfg = N.SmmcConfig()
+    cfg.abi_version = N.SMMC_ABI_VERSION
+    cfg.mode = N.MODES[mode] if isinstance(mode, str) else int(mode)
+    cfg.n_simulations = int(n_simulations)
+    cfg.n_periods = int(n_periods)
+    keep = None
+    if returns_ptr is not None:
+        cfg.returns = int(returns_ptr)
+        cfg.n_returns = int(n_returns)
+    elif returns is not None:
+        keep = _as_f32(returns)
+        cfg.returns = keep.ctypes.data
+        cfg.n_returns = int(keep.size)
+    cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    cfg.stream_offset = int(stream_offset)
+    cfg.initial_capital = float(initial_capital)
+    cfg.gauss_mean = float(gauss_mean)
+    cfg.gauss_std = float(gauss_std)
+    cfg.target = float(initial_capital if target is None else target)
+    cfg.hist_bins = int(hist_bins)
+    if hist_bins:
+        lo, hi = hist_range if hist_range is not None else (0.0, 50.0 * float(initial_capital))
+        cfg.hist_lo, cfg.hist_hi = float(lo), float(hi)
+    cfg.device = int(device)
+    cfg.flags = int(flags)
+    cfg.stream = int(stream) if stream else None
+    return cfg, keep
+
+
+def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+             gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
+             want_finals=False, want_block_partials=False, device=0, n_gpus=1) -> Result:
+    """One blocking run through `smmc_run` / `smmc_run_multi` with HOST buffers (the call a user makes)."""
+    lib = N.load()
+    cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
+                            gauss_mean, gauss_std, target, hist_bins, hist_range, device)
+    res = N.SmmcResult()
+    out = Result()
+    nb = (int(n_simulations) + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
+    if want_finals:
+        out.finals = np.empty(int(n_simulations), dtype=np.float32)
+        res.finals = out.finals.ctypes.data
+    if want_block_partials:
+        out.block_means = np.zeros(nb, dtype=np.float32)
+        out.block_vars = np.zeros(nb, dtype=np.float32)
+        res.block_means = out.block_means.ctypes.data
+        res.block_vars = out.block_vars.ctypes.data
+    if hist_bins:
+        out.hist = np.zeros(int(hist_bins) + 2, dtype=np.uint64)
+        res.hist = out.hist.ctypes.data
+    if n_gpus == 1:
+        N.check(lib.smmc_run(C.byref(cfg), C.byref(res)))
+    else:
+        N.check(lib.smmc_run_multi(C.byref(cfg), int(n_gpus), C.byref(res)))
+    del keep
+    out.count, out.below_count = int(res.count), int(res.below_count)
+    out.mean, out.m2 = float(res.mean), float(res.m2)
+    out.device_ms, out.gpu_launches = float(res.device_ms), int(res.gpu_launches)
+    return out
+
+
+def stats_len(hist_bins):
+    return int(N.load().smmc_stats_len(int(hist_bins)))
+
+
+def simulate_device(mode, n_simulations, n_periods, stats_ptr, initial_capital=1000.0, returns_ptr=None,
+                    n_returns=0, seed=0, stream_offset=0, gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None,
+                    hist_bins=0, hist_range=None, finals_ptr=None, block_means_ptr=None, block_vars_ptr=None,
+                    device=0, stream=0):
+    """Asynchronous run over DEVICE pointers on `stream` (e.g. torch tensors' data_ptr() and torch's current
+    stream).  Nothing is synchronised; `stats_ptr` (stats_len(hist_bins) float64 on the device) receives the
+    allreduce-ready statistics vector described in include/smmc.h.  Returns the number of kernels launched."""
+    lib = N.load()
+    cfg, _ = make_config(mode, n_simulations, n_periods, initial_capital, None, seed, stream_offset, gauss_mean,
+                         gauss_std, target, hist_bins, hist_range, device,
+                         flags=N.FLAG_DEVICE_POINTERS | N.FLAG_NO_SYNC, stream=stream,
+                         returns_ptr=returns_ptr, n_returns=n_returns)
+    res = N.SmmcResult()
+    res.stats_dev = int(stats_ptr)
+    res.finals = int(finals_ptr) if finals_ptr else None
+    res.block_means = int(block_means_ptr) if block_means_ptr else None
+    res.block_vars = int(block_vars_ptr) if block_vars_ptr else None
+    N.check(lib.smmc_run(C.byref(cfg), C.byref(res)))
+    return int(res.gpu_launches)
+
+
+def finalize_stats(stats, hist_bins, initial_capital) -> Result:
+    """Turn a (possibly all-reduced) host statistics vector into count / mean / M2 / below / histogram."""
+    lib = N.load()
+    stats = np.ascontiguousarray(np.asarray(stats, dtype=np.float64))
+    assert stats.size == stats_len(hist_bins)
+    count, below = C.c_uint64(), C.c_uint64()
+    mean, m2 = C.c_double(), C.c_double()
+    hist = np.zeros(int(hist_bins) + 2, dtype=np.uint64) if hist_bins else None
+    N.check(lib.smmc_stats_finalize(stats.ctypes.data, int(hist_bins), float(initial_capital), C.byref(count),
+                                    C.byref(below), C.byref(mean), C.byref(m2),
+                                    hist.ctypes.data if hist is not None else None))
+    return Result(count=int(count.value), below_count=int(below.value), mean=float(mean.value), m2=float(m2.value),
+                  hist=hist)
+
+
+# ---- reference-named entry points ---------------------------------------------------------------------------------
+
+def mc_simulations_gpu(n_simulations, max_n_simulations, n_periods, initial_capital, returns, totals, n_gpus):
+    """reference src/simulations.cu:661-680: totals <- fresh vector of the N final values; n_simulations <- N."""
+    r = simulate("bootstrap_compat", max_n_simulations, n_periods, initial_capital, returns, want_finals=True,
+                 n_gpus=n_gpus)
+    totals.array = r.finals
+    n_simulations.store(max_n_simulations)
+
+
+def mc_simulations_gpu_reduceBlock(n_simulations, max_n_simulations, n_periods, initial_capital, returns, means,
+                                   variances, n_gpus):
+    """reference src/simulations.cu:682-697: per-256-path-block mean / population variance; 1 GPU only."""
+    if n_gpus != 1:
+        # the reference throws std::invalid_argument (src/simulations.cu:693)
+        raise ValueError(">1 GPU not yet supported for reduceBlock version!!")
+    r = simulate("bootstrap_compat", max_n_simulations, n_periods, initial_capital, returns,
+                 want_block_partials=True)
+    means.array = r.block_means
+    variances.array = r.block_vars
+    n_simulations.store(max_n_simulations)
+
+
+def reduce_mean_gpu(vec, n):
+    """reference src/simulations.cu:269-341."""
+    lib = N.load()
+    a = _as_f32(vec)
+    out = C.c_float()
+    N.check(lib.smmc_reduce_mean(a.ctypes.data, int(n), 0, C.byref(out)))
+    return float(out.value)
+
+
+def vector_add(out, a, b, n):
+    """reference src/gpu.cpp:7-15 (host loop)."""
+    out[:n] = np.asarray(a[:n], dtype=np.float32) + np.asarray(b[:n], dtype=np.float32)
+
+
+def vector_add_gpu(out, a, b, n):
+    """reference src/gpu.cu:17-47."""
+    lib = N.load()
+    a32, b32 = _as_f32(a), _as_f32(b)
+    assert isinstance(out, np.ndarray) and out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+    N.check(lib.smmc_vector_add(out.ctypes.data, a32.ctypes.data, b32.ctypes.data, int(n), 0))
+
+
+def debug_draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0, device=0):
+    lib = N.load()
+    cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset,
+                            device=device)
+    out = np.zeros((int(n_paths), int(n_periods)), dtype=np.uint32)
+    N.check(lib.smmc_debug_draws(C.byref(cfg), int(n_paths), out.ctypes.data))
+    del keep
+    return out
+
+
+def debug_philox(ctr, key, device=0):
+    lib = N.load()
+    ctr = np.ascontiguousarray(np.asarray(ctr, dtype=np.uint32).reshape(-1, 4))
+    key = np.ascontiguousarray(np.asarray(key, dtype=np.uint32).reshape(2))
+    out = np.zeros_like(ctr)
+    N.check(lib.smmc_debug_philox(ctr.ctypes.data, key.ctypes.data, int(ctr.shape[0]), int(device), out.ctypes.data))
+    return out
