@@ -85,7 +85,8 @@ void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t ou
 }
 
 /* stream contract of the native modes (DESIGN.md "RNG stream contract"):
- * counter = (month / 4, path_lo, domain tag, path_hi), key = (seed_lo, seed_hi); word j serves month 4q + j. */
+ * counter = (q, path_lo, domain tag, path_hi), key = (seed_lo, seed_hi); call q serves months 4q..4q+3
+ * (bootstrap, one word per month) or 6q..6q+5 (gaussian, see gauss_field). */
 #define TAG_BOOTSTRAP 0x424F4F54u /* "BOOT" */
 #define TAG_GAUSSIAN 0x47415553u  /* "GAUS" */
 #define TAG_SOBOL_SHIFT 0x534F424Cu /* "SOBL" */
@@ -113,16 +114,33 @@ static gauss_consts make_gauss_consts(float mean_pct, float std_pct) {
   return g;
 }
 
-#define BM_U_SCALE 2.3283064365386963e-10f /* 2^-32 */
-#define BM_U_BIAS 1.1641532182693481e-10f  /* 2^-33 */
-#define BM_V_SCALE 1.4629180792671596e-09f /* pi * 2^-31 */
-#define BM_V_BIAS 7.3145903963357981e-10f  /* pi * 2^-32 */
+/* One Philox call feeds six months (DESIGN.md "Gaussian draws"):
+ *   f0..f3 = low 21 bits of w0..w3; f4 = w0[31:21]:w1[31:21]; f5 = w2[31:21]:w3[31:21] (22 bits);
+ *   pair p = (radius field f_2p, angle field f_2p+1) -> months 6q+2p (cos), 6q+2p+1 (sin);
+ *   u = (f + 1/2)/2^bits, v = 2 pi u - pi.  The float constants are the device's, digit for digit. */
+static uint32_t gauss_field(const uint32_t w[4], int j) {
+  if (j < 4) return w[j] & 0x1FFFFFu;
+  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
+}
 
-/* (wa, wb) -> growth factors of two consecutive months.  The device uses MUFU lg2/sqrt/sin/cos approximations
+static float as_float(uint32_t bits) {
+  float f;
+  memcpy(&f, &bits, sizeof f);
+  return f;
+}
+
+/* (fr, fa) -> growth factors of two consecutive months.  The device uses MUFU lg2/sqrt/sin/cos approximations
  * where this uses libm, so Gaussian finals agree to a stated tolerance, not bit-for-bit (tests state it). */
-static void gauss_pair(uint32_t wa, uint32_t wb, gauss_consts gc, float *g0, float *g1) {
-  float u = fmaf((float)wa, BM_U_SCALE, BM_U_BIAS);
-  float v = fmaf((float)(int32_t)wb, BM_V_SCALE, BM_V_BIAS);
+static void gauss_pair(uint32_t fr, uint32_t fa, int bits, gauss_consts gc, float *g0, float *g1) {
+  float mr = as_float(fr | 0x3F800000u), ma = as_float(fa | 0x3F800000u);
+  float u, v;
+  if (bits == 21) {
+    u = fmaf(mr, 4.0f, -3.99999976158142089844f);
+    v = fmaf(ma, 25.132741928100585938f, -28.274332046508789062f);
+  } else {
+    u = fmaf(mr, 2.0f, -1.99999988079071044922f);
+    v = fmaf(ma, 12.566370964050292969f, -15.707962989807128906f);
+  }
   float t = log2f(u) * gc.k;
   float rs = sqrtf(t);
   float c = cosf(v), s = sinf(v);
@@ -167,7 +185,7 @@ static uint32_t sobol_shift(int32_t dim, uint64_t seed) {
 /* inverse normal CDF used by SOBOL_GAUSSIAN: single-precision restatement, see DESIGN.md "Sobol Gaussian".
  * Central/tail split of Giles' erfinv approximation ("Approximating the erfinv function", GPU Gems 2012),
  * evaluated with explicit fmaf so that host and device agree up to the log2/sqrt approximations. */
-static float normal_icdf(uint32_t x32) {
+static float normal_icdf(uint32_t x32) { /* returns z / sqrt(2) */
   /* u in (0,1), symmetric about 0.5:  u = (x + 0.5) * 2^-32;   z = sqrt(2) * erfinv(2u - 1) */
   float y = fmaf((float)(int32_t)(x32 ^ 0x80000000u), 4.6566128730773926e-10f, 2.3283064365386963e-10f); /* 2u-1 */
   float t = fmaxf(fmaf(-y, y, 1.0f), 5.9604645e-08f); /* 1 - y^2, clamped at 2^-24 so |y| = 1 stays finite */
@@ -196,7 +214,7 @@ static float normal_icdf(uint32_t x32) {
     p = fmaf(p, w, 1.00167406f);
     p = fmaf(p, w, 2.83297682f);
   }
-  return 1.41421356237309504880f * (p * y);
+  return p * y; /* z = sqrt(2) * p * y; the caller folds sqrt(2) * sigma into one constant, as the device does */
 }
 
 /* ------------------------------------------------------------------------------------------------------- */
@@ -206,7 +224,7 @@ typedef struct run_consts {
   const smmc_config *cfg;
   const float *tbl; /* returns * 0.01f, with one zero pad entry at [n] (compat one-past-the-end read) */
   gauss_consts gc;
-  float sigma;
+  float sigma_sqrt2; /* (float)(sqrt(2) * (double)(std * 0.01f)) */
   const uint32_t *shift; /* per-month Sobol digital shift */
 } run_consts;
 
@@ -239,10 +257,11 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
       uint32_t w[4];
       float g[2];
       for (int m = 0; m < P; m++) {
-        if ((m & 3) == 0) stream_words(path, (uint32_t)(m >> 2), TAG_GAUSSIAN, cfg->seed, w);
-        if ((m & 1) == 0) gauss_pair(w[m & 3], w[(m & 3) + 1], rc->gc, &g[0], &g[1]);
-        if (draws) draws[m] = w[m & 3];
-        total = total * g[m & 1];
+        int j = m % 6;
+        if (j == 0) stream_words(path, (uint32_t)(m / 6), TAG_GAUSSIAN, cfg->seed, w);
+        if ((j & 1) == 0) gauss_pair(gauss_field(w, j), gauss_field(w, j + 1), j < 4 ? 21 : 22, rc->gc, &g[0], &g[1]);
+        if (draws) draws[m] = gauss_field(w, j);
+        total = total * g[j & 1];
       }
     } break;
     case SMMC_MODE_SOBOL_BOOTSTRAP: {
@@ -257,8 +276,7 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
       for (int m = 0; m < P; m++) {
         uint32_t x = orc_sobol_point(path + SOBOL_SKIP, m) ^ rc->shift[m];
         if (draws) draws[m] = x;
-        float z = normal_icdf(x);
-        total = total * fmaf(rc->sigma, z, rc->gc.a);
+        total = total * fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
       }
     } break;
     default: break;
@@ -380,7 +398,7 @@ int orc_run(const smmc_config *cfg, smmc_result *out) {
   float *tbl = build_table(cfg);
   rc.tbl = tbl;
   rc.gc = make_gauss_consts(cfg->gauss_mean, cfg->gauss_std);
-  rc.sigma = cfg->gauss_std * 0.01f;
+  rc.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)(cfg->gauss_std * 0.01f));
   uint32_t *shift = (uint32_t *)calloc((size_t)(P > 0 ? P : 1), sizeof(uint32_t));
   if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
     for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);
@@ -457,7 +475,7 @@ int orc_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
   float *tbl = build_table(cfg);
   rc.tbl = tbl;
   rc.gc = make_gauss_consts(cfg->gauss_mean, cfg->gauss_std);
-  rc.sigma = cfg->gauss_std * 0.01f;
+  rc.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)(cfg->gauss_std * 0.01f));
   uint32_t *shift = (uint32_t *)calloc((size_t)(P > 0 ? P : 1), sizeof(uint32_t));
   if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
     for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);

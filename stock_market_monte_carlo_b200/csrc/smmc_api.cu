@@ -15,6 +15,11 @@
 #include "../../include/smmc.h"
 #include "smmc_kernels.cuh"
 
+namespace smmc {
+const uint32_t *sobol_table();  // smmc_sobol_data.cpp
+int sobol_table_dims();
+}  // namespace smmc
+
 namespace {
 
 thread_local char g_err[512] = "";
@@ -61,7 +66,10 @@ struct Context {
   size_t smem_optin = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  DevBuf returns, tbl, work, stats, finals, bmeans, bvars, scratch;
+  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift;
+  int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
+  uint64_t sobol_seed = 0;
+  bool sobol_full_ready = false;
   double *stats_host = nullptr;  // pinned
   size_t stats_host_cap = 0;
   std::mutex mu;
@@ -166,6 +174,65 @@ smmc::PhiloxKeys make_keys(uint64_t seed) {
   return k;
 }
 
+// host Philox4x32-10 (only for the per-month Sobol digital shift; same counter layout as the device stream)
+void philox_host(const uint32_t ctr[4], uint64_t seed, uint32_t out[4]) {
+  uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  for (int r = 0; r < 10; r++) {
+    const uint64_t p0 = (uint64_t)smmc::kPhiloxM0 * c0, p1 = (uint64_t)smmc::kPhiloxM1 * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1;
+    c3 = (uint32_t)p0;
+    c0 = n0;
+    c2 = n2;
+    k0 += smmc::kPhiloxW0;
+    k1 += smmc::kPhiloxW1;
+  }
+  out[0] = c0;
+  out[1] = c1;
+  out[2] = c2;
+  out[3] = c3;
+}
+
+// digital shift of Sobol dimension m: 0 for seed 0 (plain sequence), else word (m & 3) of the Philox call
+// (q = 0, path = m >> 2, tag "SOBL") keyed by the seed
+uint32_t sobol_shift_host(int m, uint64_t seed) {
+  if (seed == 0) return 0;
+  const uint32_t ctr[4] = {0u, (uint32_t)(m >> 2), smmc::kTagSobolShift, 0u};
+  uint32_t w[4];
+  philox_host(ctr, seed, w);
+  return w[m & 3];
+}
+
+// (Re)build the per-launch Sobol tables for (n_periods, seed) on `st`; cached per context.
+smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream_t st, smmc::KParams *p) {
+  const int ppad = (n_periods + 31) & ~31;
+  const uint32_t *V = smmc::sobol_table();
+  if (n_periods > smmc::sobol_table_dims()) return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support at most %d periods", smmc::sobol_table_dims());
+  if (ppad > 0 && (ctx->sobol_periods != n_periods || ctx->sobol_seed != seed)) {
+    std::vector<uint32_t> lo((size_t)ppad * 8, 0u), hi((size_t)26 * ppad, 0u);
+    for (int m = 0; m < n_periods; m++) {
+      for (int k = 0; k < 8; k++) lo[(size_t)m * 8 + k] = V[(size_t)m * 32 + k];
+      for (int k = 0; k < 24; k++) hi[(size_t)k * ppad + m] = V[(size_t)m * 32 + 8 + k];
+      hi[(size_t)24 * ppad + m] = V[(size_t)m * 32 + 7];
+      hi[(size_t)25 * ppad + m] = sobol_shift_host(m, seed);
+    }
+    CU(ctx->sobol_lo.reserve(lo.size() * 4));
+    CU(ctx->sobol_hi.reserve(hi.size() * 4));
+    CU(cudaStreamSynchronize(st));  // a previous launch on this stream may still read the cached tables
+    CU(cudaMemcpyAsync(ctx->sobol_lo.p, lo.data(), lo.size() * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->sobol_hi.p, hi.data(), hi.size() * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));  // lo/hi are stack-lifetime host vectors
+    ctx->sobol_periods = n_periods;
+    ctx->sobol_seed = seed;
+  }
+  p->sobol_lo = (const uint32_t *)ctx->sobol_lo.p;
+  p->sobol_hi = (const uint32_t *)ctx->sobol_hi.p;
+  p->sobol_ppad = ppad;
+  p->sobol_lo_bytes = (uint32_t)ppad * 32u;
+  return SMMC_OK;
+}
+
 // everything a launched shard needs to be collected later
 struct Pending {
   Context *ctx = nullptr;
@@ -191,7 +258,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   const int variant = variant_from_env();
 
   smmc::LaunchInfo li;
-  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, bins, ctx->n_sms, ctx->smem_optin, variant, &li))
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, ctx->n_sms, ctx->smem_optin, variant, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %zu bytes of shared memory", cfg->n_returns, ctx->smem_optin);
 
   smmc::KParams p;
@@ -223,6 +290,13 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
       CU(ctx->returns.reserve((size_t)n * 4));
       CU(cudaMemcpyAsync(ctx->returns.p, cfg->returns, (size_t)n * 4, cudaMemcpyHostToDevice, st));
       src = (const float *)ctx->returns.p;
+    }
+    if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP) {  // quasi-random draws sample the SORTED table (quantile function)
+      CU(ctx->sorted.reserve((size_t)n * 4));
+      smmc::launch_sort_table(src, n, (float *)ctx->sorted.p, st);
+      CU(cudaGetLastError());
+      pd->launches++;
+      src = (const float *)ctx->sorted.p;
     }
     const uint32_t tbl_bytes = (uint32_t)((((size_t)(n + 1) * li.rep * 4) + 15) & ~(size_t)15);
     CU(ctx->tbl.reserve(tbl_bytes));
@@ -275,7 +349,10 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     }
   }
 
-  if (is_sobol(cfg->mode)) return fail(SMMC_ERR_UNSUPPORTED, "Sobol modes are not built yet");
+  if (is_sobol(cfg->mode)) {
+    smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p);
+    if (sst != SMMC_OK) return sst;
+  }
 
   CU(cudaEventRecord(ctx->ev0, st));
   CU(smmc::launch_mc(cfg->mode, p, li, variant, st));
@@ -477,7 +554,6 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
   if (st != SMMC_OK) return st;
   if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "debug_draws takes host pointers");
   if (n_paths < 0 || !outbuf) return fail(SMMC_ERR_INVALID_ARG, "debug_draws: bad arguments");
-  if (is_sobol(cfg->mode)) return fail(SMMC_ERR_UNSUPPORTED, "Sobol modes are not built yet");
   Context *ctx = nullptr;
   st = get_context(cfg->device, &ctx);
   if (st != SMMC_OK) return st;
@@ -494,7 +570,23 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
   const size_t bytes = (size_t)n_paths * (size_t)cfg->n_periods * 4;
   if (bytes == 0) return SMMC_OK;
   CU(ctx->scratch.reserve(bytes));
-  CU(smmc::launch_debug_draws(cfg->mode, p, n_paths, (uint32_t *)ctx->scratch.p, ctx->stream));
+  const uint32_t *full_dev = nullptr, *shift_dev = nullptr;
+  if (is_sobol(cfg->mode)) {
+    const int dims = smmc::sobol_table_dims();
+    if (!ctx->sobol_full_ready) {
+      CU(ctx->sobol_full.reserve((size_t)dims * 32 * 4));
+      CU(cudaMemcpyAsync(ctx->sobol_full.p, smmc::sobol_table(), (size_t)dims * 32 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      ctx->sobol_full_ready = true;
+    }
+    std::vector<uint32_t> shift((size_t)cfg->n_periods);
+    for (int m = 0; m < cfg->n_periods; m++) shift[m] = sobol_shift_host(m, cfg->seed);
+    CU(ctx->sobol_shift.reserve(shift.size() * 4));
+    CU(cudaMemcpyAsync(ctx->sobol_shift.p, shift.data(), shift.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    full_dev = (const uint32_t *)ctx->sobol_full.p;
+    shift_dev = (const uint32_t *)ctx->sobol_shift.p;
+  }
+  CU(smmc::launch_debug_draws(cfg->mode, p, n_paths, full_dev, shift_dev, (uint32_t *)ctx->scratch.p, ctx->stream));
   CU(cudaMemcpyAsync(outbuf, ctx->scratch.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return SMMC_OK;
@@ -528,6 +620,13 @@ void smmc_shutdown(void) {
     if (!c.ready) continue;
     cudaSetDevice(d);
     c.returns.release();
+    c.sorted.release();
+    c.sobol_lo.release();
+    c.sobol_hi.release();
+    c.sobol_full.release();
+    c.sobol_shift.release();
+    c.sobol_periods = -1;
+    c.sobol_full_ready = false;
     c.tbl.release();
     c.work.release();
     c.stats.release();

@@ -62,8 +62,8 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
   out[3] = c3;
 }
 
-// Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed.
-// Word j of call q serves month 4q + j.  The per-lane quantity (path_lo) sits in counter word 1 so that in
+// Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed; call q serves months
+// 4q..4q+3 (BOOTSTRAP: one 32-bit word per month) or 6q..6q+5 (GAUSSIAN, see gauss_group).  The per-lane quantity (path_lo) sits in counter word 1 so that in
 // rounds 1-3 one of the two 32x32->64 multiplies has warp-uniform operands (q, tag, path_hi and the key are
 // uniform over a 256-path block): the compiler hoists those to once per call per warp, and only 16 of the
 // 20 multiplies of a call are per-lane work.
@@ -98,23 +98,56 @@ __device__ __forceinline__ float cos_approx(float x) {
   return y;
 }
 
-// ---- Gaussian growth factors (Box-Muller on two 32-bit words) ----------------------------------------------
+// ---- Gaussian growth factors (Box-Muller) -------------------------------------------------------------------
 // r ~ N(mean, std) percent, fund *= (100 + r)/100 (reference src/simulations.cpp:14-16, :41-55), evaluated as
-// g = (1 + mean/100) + (std/100) z with z = sqrt(-2 ln u) {cos,sin}(v):
-//   u = (wa + 1/2) 2^-32 in (0,1],  v = (int(wb) + 1/2) pi 2^-31 in (-pi, pi),
+// g = (1 + mean/100) + (std/100) z with (z0, z1) = sqrt(-2 ln u) (cos v, sin v).
+//
+// One Philox call (128 bits) feeds SIX months: the IMAD.WIDE multiplies of Philox run at a quarter of the issue
+// rate on sm_100a (profiles/r01_pipe_microbench.txt), so bits are not wasted.  Fields (f = integer value):
+//   f0..f3 = low 21 bits of w0..w3;  f4 = w0[31:21] : w1[31:21];  f5 = w2[31:21] : w3[31:21]  (22 bits)
+//   pair p = (radius field f_{2p}, angle field f_{2p+1}) serves months 6q + 2p (cos) and 6q + 2p + 1 (sin)
+//   u = (f + 1/2) / 2^bits  in (0,1)   (never 0 or 1: no special cases),   v = 2 pi u - pi  in (-pi, pi)
+// A field is turned into a float by OR-ing it into the mantissa of 1.0f (one LOP3, no I2F), then one exact FFMA.
 //   (std/100) sqrt(-2 ln u) = sqrt(lg2(u) * k),  k = -2 ln2 (std/100)^2.
 struct GaussConsts {
   float a;  // 1 + mean/100
   float k;  // -2 ln2 sigma^2
 };
 
-__device__ __forceinline__ void gauss_pair(uint32_t wa, uint32_t wb, const GaussConsts gc, float &g0, float &g1) {
-  const float u = fmaf(__uint2float_rn(wa), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
-  const float v = fmaf(__int2float_rn((int)wb), 1.4629180792671596e-09f, 7.3145903963357981e-10f);
+constexpr int kGaussMonthsPerCall = 6;
+
+template <int BITS>
+__device__ __forceinline__ void gauss_pair(uint32_t fr, uint32_t fa, const GaussConsts gc, float &g0, float &g1) {
+  static_assert(BITS == 21 || BITS == 22, "field width");
+  const float mr = __uint_as_float(fr | 0x3F800000u);  // 1 + f 2^-23
+  const float ma = __uint_as_float(fa | 0x3F800000u);
+  float u, v;
+  if (BITS == 21) {
+    u = fmaf(mr, 4.0f, -3.99999976158142089844f);               // (f + 1/2) 2^-21, exact
+    v = fmaf(ma, 25.132741928100585938f, -28.274332046508789062f);  // 8 pi m - (9 - 2^-21) pi
+  } else {
+    u = fmaf(mr, 2.0f, -1.99999988079071044922f);               // (f + 1/2) 2^-22, exact
+    v = fmaf(ma, 12.566370964050292969f, -15.707962989807128906f);  // 4 pi m - (5 - 2^-22) pi
+  }
   const float t = lg2_approx(u) * gc.k;
   const float rs = sqrt_approx(t);
   g0 = fmaf(rs, cos_approx(v), gc.a);
   g1 = fmaf(rs, sin_approx(v), gc.a);
+}
+
+// growth factors of the six months served by one Philox call
+__device__ __forceinline__ void gauss_group(const uint32_t (&w)[4], const GaussConsts gc, float (&g)[6]) {
+  const uint32_t f4 = ((w[0] >> 21) << 11) | (w[1] >> 21);
+  const uint32_t f5 = ((w[2] >> 21) << 11) | (w[3] >> 21);
+  gauss_pair<21>(w[0] & 0x1FFFFFu, w[1] & 0x1FFFFFu, gc, g[0], g[1]);
+  gauss_pair<21>(w[2] & 0x1FFFFFu, w[3] & 0x1FFFFFu, gc, g[2], g[3]);
+  gauss_pair<22>(f4, f5, gc, g[4], g[5]);
+}
+
+// field behind month j (0..5) of a call, for the draw-level parity test
+__device__ __forceinline__ uint32_t gauss_field(const uint32_t (&w)[4], int j) {
+  if (j < 4) return w[j] & 0x1FFFFFu;
+  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
 }
 
 // ---- inverse normal CDF (SOBOL_GAUSSIAN) ----------------------------------------------------------------------

@@ -22,15 +22,17 @@ namespace {
 constexpr int kThreads = 1024;
 constexpr int kWarps = kThreads / 32;
 
-// shared memory layout (dynamic): [0,8) mbarrier | [16, 16+8*(bins+2)) histogram | warp partials | table (128-B aligned)
+// shared memory layout (dynamic):
+// [0,8) mbarrier | [16, 16+8*(bins+2)) histogram | warp partials | Sobol low direction numbers | table (128-B aligned)
 struct SmemLayout {
-  uint32_t hist_off, wp_off, tbl_off, total;
+  uint32_t hist_off, wp_off, sob_off, tbl_off, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t tbl_bytes) {
+__host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sob_bytes, uint32_t tbl_bytes) {
   SmemLayout L;
   L.hist_off = 16;
   L.wp_off = L.hist_off + 8u * (uint32_t)(bins + 2);
-  L.tbl_off = (L.wp_off + 32u * kWarps + 127u) & ~127u;
+  L.sob_off = (L.wp_off + 32u * kWarps + 127u) & ~127u;
+  L.tbl_off = (L.sob_off + sob_bytes + 127u) & ~127u;
   L.total = L.tbl_off + tbl_bytes;
   return L;
 }
@@ -123,34 +125,82 @@ template <int ILP>
 __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&plo)[ILP], uint32_t phi,
                                              float (&tot)[ILP]) {
   const GaussConsts gc = p.gc;
-  const int nq = p.n_periods >> 2;
+  const int nq = p.n_periods / kGaussMonthsPerCall;
 #pragma unroll 1
   for (int q = 0; q < nq; q++) {
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
       stream_words(plo[i], phi, (uint32_t)q, kTagGaussian, p.keys, w);
-      float g0, g1, g2, g3;
-      gauss_pair(w[0], w[1], gc, g0, g1);
-      gauss_pair(w[2], w[3], gc, g2, g3);
-      tot[i] = __fmul_rn(tot[i], g0);
-      tot[i] = __fmul_rn(tot[i], g1);
-      tot[i] = __fmul_rn(tot[i], g2);
-      tot[i] = __fmul_rn(tot[i], g3);
+      float g[6];
+      gauss_group(w, gc, g);
+#pragma unroll
+      for (int j = 0; j < 6; j++) tot[i] = __fmul_rn(tot[i], g[j]);
     }
   }
-  const int rem = p.n_periods & 3;
+  const int rem = p.n_periods - nq * kGaussMonthsPerCall;
   if (rem) {
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
       stream_words(plo[i], phi, (uint32_t)nq, kTagGaussian, p.keys, w);
-      float g0, g1, g2, g3;
-      gauss_pair(w[0], w[1], gc, g0, g1);
-      gauss_pair(w[2], w[3], gc, g2, g3);
-      tot[i] = __fmul_rn(tot[i], g0);
-      if (rem > 1) tot[i] = __fmul_rn(tot[i], g1);
-      if (rem > 2) tot[i] = __fmul_rn(tot[i], g2);
+      float g[6];
+      gauss_group(w, gc, g);
+#pragma unroll
+      for (int j = 0; j < 5; j++)
+        if (j < rem) tot[i] = __fmul_rn(tot[i], g[j]);
+    }
+  }
+}
+
+// ---- Sobol modes: all 8 paths of the lane at once -------------------------------------------------------------------
+// Point i = path + 256 = 256 h + c with c = 32 j + lane (the block base is 256-aligned), x_m(i) = XOR over the set
+// bits k of gray(i) of V[m][k].  gray bits >= 8 depend on h only: that part (U_m, with the digital shift and the
+// h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
+// broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
+// eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
+template <int MODE>
+__device__ __forceinline__ void run_sobol(const KParams &p, const char *tbl, uint32_t lane_off, const uint4 *vlo,
+                                          uint32_t h, uint32_t lane, float (&tot)[8]) {
+  const uint32_t mk0 = ((lane ^ (lane >> 1)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk1 = (((lane >> 1) ^ (lane >> 2)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk2 = (((lane >> 2) ^ (lane >> 3)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk3 = (((lane >> 3) ^ (lane >> 4)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk4 = ((lane >> 4) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t gh = h ^ (h >> 1);
+  const int ppad = p.sobol_ppad;
+  const uint32_t nr4 = p.nr4, row_mask = ~(p.rep4 - 1u);
+  const float a = p.gc.a, s2 = p.sigma_sqrt2;
+#pragma unroll 1
+  for (int m0 = 0; m0 < p.n_periods; m0 += 32) {
+    const uint32_t *col = p.sobol_hi + m0 + lane;
+    uint32_t U = __ldg(col + 25 * ppad);
+    if (h & 1u) U ^= __ldg(col + 24 * ppad);
+    for (uint32_t g = gh; g; g &= g - 1u) U ^= __ldg(col + (__ffs((int)g) - 1) * ppad);
+    const int mend = (p.n_periods - m0) < 32 ? (p.n_periods - m0) : 32;
+#pragma unroll 2
+    for (int mi = 0; mi < mend; mi++) {
+      const uint32_t Um = __shfl_sync(0xffffffffu, U, mi);
+      const uint4 va = vlo[(m0 + mi) * 2], vb = vlo[(m0 + mi) * 2 + 1];
+      uint32_t base = Um ^ (va.x & mk0);
+      base ^= (va.y & mk1);
+      base ^= (va.z & mk2);
+      base ^= (va.w & mk3);
+      base ^= (vb.x & mk4);
+      uint32_t x[8];
+      x[0] = base;
+      x[1] = base ^ vb.x ^ vb.y;
+      x[2] = base ^ vb.y ^ vb.z;
+      x[3] = base ^ vb.x ^ vb.z;
+      x[4] = base ^ vb.z ^ vb.w;
+      x[5] = x[1] ^ vb.z ^ vb.w;
+      x[6] = base ^ vb.y ^ vb.w;
+      x[7] = base ^ vb.x ^ vb.w;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = boot_step(tot[j], x[j], tbl, nr4, row_mask, lane_off);
+        else tot[j] = __fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a));
+      }
     }
   }
 }
@@ -162,35 +212,40 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr bool kHasTable = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT || MODE == SMMC_MODE_BOOTSTRAP ||
                               MODE == SMMC_MODE_SOBOL_BOOTSTRAP);
-  const SmemLayout L = smem_layout(p.hist_bins, kHasTable ? p.tbl_bytes : 0u);
+  constexpr bool kSobol = (MODE == SMMC_MODE_SOBOL_BOOTSTRAP || MODE == SMMC_MODE_SOBOL_GAUSSIAN);
+  const SmemLayout L = smem_layout(p.hist_bins, kSobol ? p.sobol_lo_bytes : 0u, kHasTable ? p.tbl_bytes : 0u);
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
   unsigned long long *hist_s = reinterpret_cast<unsigned long long *>(smem + L.hist_off);
   double *wp = reinterpret_cast<double *>(smem + L.wp_off);
   const char *tbl = reinterpret_cast<const char *>(smem + L.tbl_off);
+  const uint4 *vlo = reinterpret_cast<const uint4 *>(smem + L.sob_off);
 
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
 
   // ---- stage the table: one thread arms the mbarrier and issues the bulk copies, everyone waits on the phase
-  if (kHasTable) {
+  if (kHasTable || kSobol) {
     if (tid == 0) {
       mbar_init(bar, 1);
       fence_mbar_init();
     }
     __syncthreads();
     if (tid == 0) {
-      mbar_arrive_expect_tx(bar, p.tbl_bytes);
+      const uint32_t tb = kHasTable ? p.tbl_bytes : 0u, sb = kSobol ? p.sobol_lo_bytes : 0u;
+      mbar_arrive_expect_tx(bar, tb + sb);
       constexpr uint32_t kChunk = 32768;
-      for (uint32_t o = 0; o < p.tbl_bytes; o += kChunk) {
-        const uint32_t nbytes = (p.tbl_bytes - o) < kChunk ? (p.tbl_bytes - o) : kChunk;
-        tma_bulk_g2s(smem + L.tbl_off + o, reinterpret_cast<const char *>(p.tbl_rep) + o, nbytes, bar);
-      }
+      for (uint32_t o = 0; o < tb; o += kChunk)
+        tma_bulk_g2s(smem + L.tbl_off + o, reinterpret_cast<const char *>(p.tbl_rep) + o,
+                     (tb - o) < kChunk ? (tb - o) : kChunk, bar);
+      for (uint32_t o = 0; o < sb; o += kChunk)
+        tma_bulk_g2s(smem + L.sob_off + o, reinterpret_cast<const char *>(p.sobol_lo) + o,
+                     (sb - o) < kChunk ? (sb - o) : kChunk, bar);
     }
   }
   for (int i = tid; i < p.hist_bins + 2; i += kThreads) hist_s[i] = 0ull;
   __syncthreads();
-  if (kHasTable) mbar_wait(bar, 0);
+  if (kHasTable || kSobol) mbar_wait(bar, 0);
 
   const int64_t N = p.n_paths;
   const int64_t nb = (N + kBlock - 1) / kBlock;
@@ -209,8 +264,13 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     const int live = rem_paths < kBlock ? (int)rem_paths : kBlock;
 
     float x[kPathsPerLane];
+    if (kSobol) {
 #pragma unroll
-    for (int s = 0; s < kPathsPerLane; s += ILP) {
+      for (int j = 0; j < kPathsPerLane; j++) x[j] = p.v0;
+      run_sobol<MODE>(p, tbl, lane_off, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
+    }
+#pragma unroll
+    for (int s = 0; s < (kSobol ? 0 : kPathsPerLane); s += ILP) {
       uint32_t plo[ILP];
       float tot[ILP];
 #pragma unroll
@@ -362,8 +422,23 @@ __global__ void prep_table_kernel(const float *__restrict__ src, int n, int rep,
   }
 }
 
+// stable rank sort, O(n^2): n is a table length (~1e3), once per call
+__global__ void sort_table_kernel(const float *__restrict__ src, int n, float *__restrict__ dst) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float v = src[i];
+    int rank = 0;
+    for (int j = 0; j < n; j++) {
+      const float u = __ldg(src + j);
+      rank += (u < v || (u == v && j < i)) ? 1 : 0;
+    }
+    dst[rank] = v;
+  }
+}
+
 // ---- introspection kernels ----------------------------------------------------------------------------------------
-__global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, int n_paths, uint32_t *out) {
+__global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, int n_paths,
+                                   const uint32_t *__restrict__ sobol_full, const uint32_t *__restrict__ shift,
+                                   uint32_t *out) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_paths) return;
   const uint64_t path = p.path0 + (uint64_t)t;
@@ -375,13 +450,25 @@ __global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, 
       st = xorshift(st);
       o[m] = (uint32_t)(int)(__uint2float_rn(st) * p.idx_scale);
     }
-  } else if (mode == SMMC_MODE_BOOTSTRAP || mode == SMMC_MODE_GAUSSIAN) {
-    const uint32_t tag = mode == SMMC_MODE_BOOTSTRAP ? kTagBootstrap : kTagGaussian;
+  } else if (mode == SMMC_MODE_BOOTSTRAP) {
     uint32_t w[4];
     for (int m = 0; m < p.n_periods; m++) {
-      if ((m & 3) == 0) stream_words(plo, phi, (uint32_t)(m >> 2), tag, p.keys, w);
-      const uint32_t word = w[m & 3];
-      o[m] = mode == SMMC_MODE_BOOTSTRAP ? __umulhi(word, (uint32_t)p.n_returns) : word;
+      if ((m & 3) == 0) stream_words(plo, phi, (uint32_t)(m >> 2), kTagBootstrap, p.keys, w);
+      o[m] = __umulhi(w[m & 3], (uint32_t)p.n_returns);
+    }
+  } else if (mode == SMMC_MODE_GAUSSIAN) {
+    uint32_t w[4];
+    for (int m = 0; m < p.n_periods; m++) {
+      if (m % 6 == 0) stream_words(plo, phi, (uint32_t)(m / 6), kTagGaussian, p.keys, w);
+      o[m] = gauss_field(w, m % 6);
+    }
+  } else {  // Sobol modes: plain Gray-code evaluation over all 32 direction numbers of dimension m
+    const uint64_t i = path + kSobolSkip;
+    const uint32_t g = (uint32_t)(i ^ (i >> 1));
+    for (int m = 0; m < p.n_periods; m++) {
+      uint32_t x = shift[m];
+      for (uint32_t gg = g; gg; gg &= gg - 1u) x ^= sobol_full[m * 32 + (__ffs((int)gg) - 1)];
+      o[m] = mode == SMMC_MODE_SOBOL_BOOTSTRAP ? __umulhi(x, (uint32_t)p.n_returns) : x;
     }
   }
 }
@@ -457,8 +544,11 @@ cudaError_t launch_mode(const KParams &p, const LaunchInfo &li, int variant, cud
 
 }  // namespace
 
-bool plan_launch(int mode, int n_returns, int hist_bins, int n_sms, size_t smem_optin, int variant, LaunchInfo *li) {
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int n_sms, size_t smem_optin, int variant,
+                 LaunchInfo *li) {
   (void)variant;
+  const bool sobol = (mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN);
+  const uint32_t sob_bytes = sobol ? (uint32_t)(((n_periods + 31) & ~31) * 32) : 0u;
   const bool has_table = (mode == SMMC_MODE_BOOTSTRAP_COMPAT || mode == SMMC_MODE_BOOTSTRAP ||
                           mode == SMMC_MODE_SOBOL_BOOTSTRAP);
   li->grid = n_sms;
@@ -469,12 +559,12 @@ bool plan_launch(int mode, int n_returns, int hist_bins, int n_sms, size_t smem_
     int rep = 32;
     for (; rep >= 1; rep >>= 1) {
       tbl_bytes = (uint32_t)((((size_t)(n_returns + 1) * rep * 4) + 15) & ~(size_t)15);
-      if (smem_layout(hist_bins, tbl_bytes).total <= smem_optin) break;
+      if (smem_layout(hist_bins, sob_bytes, tbl_bytes).total <= smem_optin) break;
     }
     if (rep < 1) return false;
     li->rep = rep;
   }
-  li->smem_bytes = smem_layout(hist_bins, tbl_bytes).total;
+  li->smem_bytes = smem_layout(hist_bins, sob_bytes, tbl_bytes).total;
   return li->smem_bytes <= smem_optin;
 }
 
@@ -484,8 +574,14 @@ void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uin
   prep_table_kernel<<<blocks > 1184 ? 1184 : blocks, threads, 0, s>>>(returns_dev, n, rep, dst, dst_floats);
 }
 
+void launch_sort_table(const float *src, int n, float *dst, cudaStream_t s) {
+  sort_table_kernel<<<(n + 127) / 128 > 1184 ? 1184 : (n + 127) / 128, 128, 0, s>>>(src, n, dst);
+}
+
 cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s) {
   switch (mode) {
+    case SMMC_MODE_SOBOL_BOOTSTRAP: return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8>(p, li, s);
+    case SMMC_MODE_SOBOL_GAUSSIAN: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8>(p, li, s);
     case SMMC_MODE_BOOTSTRAP_COMPAT: return launch_mode<SMMC_MODE_BOOTSTRAP_COMPAT>(p, li, variant, s);
     case SMMC_MODE_BOOTSTRAP: return launch_mode<SMMC_MODE_BOOTSTRAP>(p, li, variant, s);
     case SMMC_MODE_GAUSSIAN: return launch_mode<SMMC_MODE_GAUSSIAN>(p, li, variant, s);
@@ -493,9 +589,10 @@ cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int vari
   }
 }
 
-cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, uint32_t *out_dev, cudaStream_t s) {
+cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, const uint32_t *sobol_full,
+                               const uint32_t *shift, uint32_t *out_dev, cudaStream_t s) {
   if (n_paths <= 0) return cudaSuccess;
-  debug_draws_kernel<<<(n_paths + 127) / 128, 128, 0, s>>>(mode, p, n_paths, out_dev);
+  debug_draws_kernel<<<(n_paths + 127) / 128, 128, 0, s>>>(mode, p, n_paths, sobol_full, shift, out_dev);
   return cudaGetLastError();
 }
 

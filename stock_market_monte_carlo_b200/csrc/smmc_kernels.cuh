@@ -36,12 +36,15 @@ struct KParams {
   unsigned long long *hist_g;  // [bins+2], zeroed before launch
   unsigned int *ticket;        // zeroed before launch
   double *stats;               // [SMMC_STATS_HEADER + bins + 2]
-  // Sobol
-  const uint32_t *sobol_lo;     // [P][8]      direction numbers of bits 0..7, month-major
-  const uint32_t *sobol_hi;     // [24][P_pad] direction numbers of bits 8..31, bit-major
-  const uint32_t *sobol_shift;  // [P_pad]     digital shift per month (0 = plain Sobol)
-  int32_t sobol_ppad;
+  // Sobol (DESIGN.md "Sobol"): point index of path p is p + 256; month m is dimension m
+  const uint32_t *sobol_lo;  // [P_pad][8]   direction numbers of index bits 0..7, month-major (staged to smem)
+  const uint32_t *sobol_hi;  // [26][P_pad]  rows 0..23: direction numbers of index bits 8..31 (bit-major);
+                             //              row 24: bit 7 again; row 25: digital shift per month (0 = plain)
+  int32_t sobol_ppad;        // P rounded up to a multiple of 32
+  uint32_t sobol_lo_bytes;   // P_pad * 32
 };
+
+constexpr uint32_t kSobolSkip = 256;  // first Sobol point used; keeps 256-path blocks aligned to 256-point blocks
 
 struct LaunchInfo {
   int grid;
@@ -51,15 +54,20 @@ struct LaunchInfo {
 };
 
 // Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
-bool plan_launch(int mode, int n_returns, int hist_bins, int n_sms, size_t smem_optin, int variant, LaunchInfo *li);
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int n_sms, size_t smem_optin, int variant,
+                 LaunchInfo *li);
 
 // Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
 void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);
+// dst = src sorted ascending (stable rank sort; SOBOL_BOOTSTRAP samples the empirical quantile function)
+void launch_sort_table(const float *src, int n, float *dst, cudaStream_t s);
 
 cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
 
 // introspection kernels (parity tests)
-cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, uint32_t *out_dev, cudaStream_t s);
+// sobol_full: [n_dims][32] direction numbers (device), only read in the Sobol modes
+cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, const uint32_t *sobol_full,
+                               const uint32_t *shift, uint32_t *out_dev, cudaStream_t s);
 cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n, uint32_t *out_dev, cudaStream_t s);
 
 // small reference entry points

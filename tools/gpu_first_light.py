@@ -51,3 +51,20 @@ for mode, kw in (("gaussian", dict(seed=1234)), ("bootstrap", dict(returns=tbl, 
             r = S.simulate(mode, N, P, hist_bins=100, want_block_partials=True, **kw)
             best = min(best, r.device_ms)
         print(f"{mode:18s} ILP={ilp} {best:8.3f} ms  {N*P/best/1e9:8.2f} G path-months/s  mean={r.mean:.3f} std={r.std:.3f}")
+
+print("---- sobol")
+for mode, kw in (("sobol_bootstrap", dict(returns=tbl, seed=0)), ("sobol_bootstrap", dict(returns=tbl, seed=99)),
+                 ("sobol_gaussian", dict(seed=0)), ("sobol_gaussian", dict(seed=99))):
+    for N, P in ((0, 360), (1, 1), (255, 7), (256, 360), (1000, 361), (65536 + 77, 360), (20000, 1000)):
+        cmp(mode, N, P, **kw)
+    d = S.debug_draws(mode, 300, 50, returns=kw.get("returns"), seed=kw.get("seed", 0))
+    o = O.draws(mode, 300, 50, returns=kw.get("returns"), seed=kw.get("seed", 0))
+    print(mode, "draws equal:", np.array_equal(d, o))
+for mode, kw in (("sobol_bootstrap", dict(returns=tbl, seed=0)), ("sobol_gaussian", dict(seed=0))):
+    N, P = 5_000_000, 1000
+    S.simulate(mode, 100000, P, **kw)
+    best = 1e9
+    for _ in range(3):
+        r = S.simulate(mode, N, P, hist_bins=100, **kw)
+        best = min(best, r.device_ms)
+    print(f"{mode:18s} {best:8.3f} ms  {N*P/best/1e9:8.3f} T path-months/s  mean={r.mean:.3f} std={r.std:.3f} p_below={r.p_below_target:.6f}")
