@@ -1,0 +1,389 @@
+#!/usr/bin/env python
+"""bench.py -- path-months/s of the Monte Carlo portfolio hot path on N B200s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3compat|c4|c4boot] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+A "step" is one pass of the hot path over one batch of synthetic paths on every GPU: the fused kernel (RNG ->
+compounding in registers -> per-block mean/variance partials -> warp/CTA/grid reduction -> histogram + P(target))
+followed, for N > 1, by the ONE all-reduce of the O(KB) statistics vector (NCCL over NVLink).  Per-GPU work is fixed
+as N grows (weak scaling); rank r of step s simulates path ids [(s*N + r) * B, +B) -- disjoint RNG streams, never a
+cached result.
+
+Workloads (BASELINE.json configs):
+  c2        360 months x 100 M paths per GPU, Gaussian(0.5 %, 10/12 %), per-256-path-block mean/variance partials,
+            100-bin histogram, P(final < V0)                     <- default; the config the metric is quoted on
+  c3        360 x 100 M bootstrap (Philox) from the synthetic 1200-month S&P-500-shaped table (shared-memory resident)
+  c3compat  same through the reference's own RNG stream (bit-exact drop-in of src/simulations.cu)
+  c4        1000 x 5 M Sobol (Joe-Kuo) Gaussian, histogram + P(target);  c4boot: Sobol bootstrap
+
+Printed: ONE JSON line (rank 0).  `value` is device-timed (CUDA events on the launching stream, summed over the K
+steps, max over ranks) with everything resident in HBM; `e2e` is the same metric through the public host-buffer
+entry point (smmc_run via simulate(): table H2D, results D2H inside the timed region); `roofline` is the simulation
+kernel against the instruction-issue roofline (this path is ALU/RNG-bound: SURVEY 8(d)); `cpu_baseline` is the
+reference's own CPU implementation (oracle/_ref, compiled from the reference sources) on this box's host cores.
+
+`--impl reference` times that CPU implementation alone (all host threads it uses, bounded sample per step).
+oracle/ is only ever the checker / the CPU baseline here, never the thing measured as the product.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "path-months/sec (device-timed)"
+UNIT = "path-months/s"
+
+# algorithmic thread-instructions per path-month (restated in DESIGN.md "Roofline")
+I_ALG = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": 6, "sobol_gaussian": 12}
+
+WORKLOADS = {
+    "c2": dict(mode="gaussian", paths=100_000_000, periods=360, block_partials=True, hist_range=(0.0, 50_000.0),
+               desc="360 months x 100M paths Gaussian(0.5%,0.8333%) per-block mean/variance partials + histogram + P(target)"),
+    "c3": dict(mode="bootstrap", paths=100_000_000, periods=360, block_partials=True, hist_range=(0.0, 200_000.0),
+               desc="360 months x 100M paths Philox bootstrap from synthetic 1200-month S&P500-shaped table (smem-resident)"),
+    "c3compat": dict(mode="bootstrap_compat", paths=100_000_000, periods=360, block_partials=True,
+                     hist_range=(0.0, 200_000.0),
+                     desc="360 months x 100M paths bootstrap, reference RNG stream (drop-in of src/simulations.cu)"),
+    "c4": dict(mode="sobol_gaussian", paths=5_000_000, periods=1000, block_partials=False, hist_range=(0.0, 500_000.0),
+               desc="1000 months x 5M paths Sobol (Joe-Kuo) Gaussian, histogram + P(target)"),
+    "c4boot": dict(mode="sobol_bootstrap", paths=5_000_000, periods=1000, block_partials=False,
+                   hist_range=(0.0, 1.0e8),
+                   desc="1000 months x 5M paths Sobol (Joe-Kuo) bootstrap, histogram + P(target)"),
+}
+HIST_BINS = 100
+V0 = 1000.0
+GAUSS = dict(gauss_mean=0.5, gauss_std=10.0 / 12.0)
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+# ---- clocks ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi sampled every 100 ms while the timed region runs (B200_PROFILING.md 'clocks' recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_indices):
+        self.rows = []
+        self.proc = None
+        self.mark0 = self.mark1 = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", ",".join(str(i) for i in gpu_indices)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def begin(self):
+        self.mark0 = time.perf_counter()
+
+    def end(self):
+        self.mark1 = time.perf_counter()
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        for t, line in self.rows:
+            if self.mark0 is None or not (self.mark0 <= t <= (self.mark1 or t) + 0.1):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm), "power_w_max": max(power) if power else None}
+
+
+# ---- CPU baseline: the reference's own CPU implementation (oracle/_ref) or, failing that, the oracle port -----------
+class CpuReference:
+    def __init__(self, mode, periods):
+        from oracle import binding as O
+        import stock_market_monte_carlo_b200 as S
+        self.O, self.mode, self.periods = O, mode, periods
+        self.table = S.synthetic_sp500_table(1200)
+        self.kind = "reference" if O.ref_available("libref_cpu.so") else "port"
+        self.cores = None
+        self.desc = None
+
+    def run(self, n_paths):
+        """simulate n_paths paths x periods months on the host cores; returns seconds"""
+        O = self.O
+        n_paths = max(int(n_paths), 10_000)  # the reference divides by n_blocks/10 (src/simulations.cpp:255)
+        t0 = time.perf_counter()
+        if self.kind == "reference":
+            if "gaussian" in self.mode:
+                _, self.cores = O.ref_gaussian_finals(n_paths, self.periods, V0, GAUSS["gauss_mean"], GAUSS["gauss_std"])
+                self.desc = "reference sample_returns_gaussian+many_updates (src/simulations.cpp:41-55,:24-39) under OpenMP"
+            else:
+                _, self.cores = O.ref_mc_simulations(n_paths, self.periods, V0, self.table)
+                self.desc = "reference CPU v2 mc_simulations (src/simulations.cpp:204-266), OpenMP"
+        else:
+            kw = dict(returns=self.table) if "bootstrap" in self.mode else {}
+            O.simulate(self.mode, n_paths, self.periods, seed=1, **kw)
+            self.cores = int(O.load().orc_num_threads())
+            self.desc = "oracle/smmc_oracle.c port (OpenMP)"
+        return time.perf_counter() - t0, n_paths
+
+    def sized_sample(self, target_seconds):
+        dt, n = self.run(20_000)
+        rate = n / max(dt, 1e-6)
+        return int(min(max(rate * target_seconds, 20_000), 50_000_000))
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cpu = CpuReference(wl["mode"], wl["periods"])
+    sample = cpu.sized_sample(1.0)  # ~1 s of host work per step
+    for _ in range(args.warmup):
+        cpu.run(sample)
+    total = 0.0
+    for _ in range(args.steps):
+        dt, n = cpu.run(sample)
+        total += dt
+    value = args.steps * sample * wl["periods"] / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "mode": wl["mode"], "periods": wl["periods"],
+                   "paths_per_step": sample, "note": "bounded sample of the workload per step, host cores only"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
+                         "sample": f"{sample} paths x {wl['periods']} months per step; {cpu.desc}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---- the GPU arm --------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--paths", type=int, default=0, help="override paths per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.paths:
+        wl["paths"] = args.paths
+    if args.impl == "reference":
+        return run_reference_arm(args, wl)
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: >= 3 warm-up steps
+
+    import torch
+    import torch.distributed as dist
+    import stock_market_monte_carlo_b200 as S
+    from stock_market_monte_carlo_b200.distributed import allreduce_stats
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if S.load().smmc_device_count() <= local:
+        raise SystemExit("bench.py needs a B200 per rank: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    mode, B, P = wl["mode"], wl["paths"], wl["periods"]
+    nb = (B + 255) // 256
+    table = S.synthetic_sp500_table(1200) if "bootstrap" in mode else None
+    seed = 0 if mode == "bootstrap_compat" else 1234
+    sobol = mode.startswith("sobol")
+    slen = S.stats_len(HIST_BINS)
+
+    # device-resident inputs / outputs of the timed region
+    table_dev = torch.from_numpy(table).to(dev) if table is not None else None
+    stats = torch.zeros(slen, dtype=torch.float64, device=dev)
+    bmeans = torch.empty(nb, dtype=torch.float32, device=dev) if wl["block_partials"] else None
+    bvars = torch.empty(nb, dtype=torch.float32, device=dev) if wl["block_partials"] else None
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream(dev)
+
+    def offset_of(step):
+        if sobol or mode == "bootstrap_compat":  # 32-bit point / path ids: wrap the offsets, still disjoint per rank
+            span = (1 << 31) - 256 - B if mode == "bootstrap_compat" else (1 << 32) - 512 - B
+            return (((step * world + rank) * B) % max(span, 1)) // 256 * 256
+        return (step * world + rank) * B
+
+    def device_step(step):
+        n = S.simulate_device(mode, B, P, stats.data_ptr(), initial_capital=V0, seed=seed, stream_offset=offset_of(step),
+                              returns_ptr=table_dev.data_ptr() if table_dev is not None else None,
+                              n_returns=table.size if table is not None else 0, hist_bins=HIST_BINS,
+                              hist_range=wl["hist_range"], block_means_ptr=bmeans.data_ptr() if bmeans is not None else None,
+                              block_vars_ptr=bvars.data_ptr() if bvars is not None else None, device=local,
+                              stream=stream.cuda_stream, **GAUSS)
+        allreduce_stats(stats)
+        return n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    sampler = ClockSampler(list(range(world))) if rank == 0 else None
+    for s in range(args.warmup):
+        device_step(s)
+        flush.zero_()
+    barrier()
+
+    # ---- timed region: exactly K steps; CUDA events on the launching stream around every step; the L2 flush
+    # between steps sits outside the event pairs
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches = 0
+    if sampler:
+        sampler.begin()
+    t_wall0 = time.perf_counter()
+    for s in range(args.steps):
+        ev[s][0].record(stream)
+        launches += device_step(args.warmup + s)
+        ev[s][1].record(stream)
+        flush.zero_()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    if sampler:
+        sampler.end()
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    kernel_ms = S.kernel_times(local, args.steps)  # the simulation kernel alone, same launches
+    final = S.finalize_stats(stats.cpu().numpy(), HIST_BINS, V0)  # result of the last step (all ranks merged)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- e2e: the public host-buffer entry point, H2D of the table and D2H of every result inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        k_e2e = min(args.steps, 50)
+
+        def host_step(step):
+            r = S.simulate(mode, B, P, initial_capital=V0, returns=table, seed=seed, stream_offset=offset_of(step),
+                           hist_bins=HIST_BINS, hist_range=wl["hist_range"], want_block_partials=wl["block_partials"],
+                           device=local, **GAUSS)
+            if world > 1:  # merge the ranks' results: count / S1 / S2 / below / histogram through the same all-reduce
+                v = np.concatenate([[r.count, r.below_count, (r.mean - V0) * r.count,
+                                     r.m2 + r.count * (r.mean - V0) ** 2, 0.0, 0.0], r.hist.astype(np.float64)])
+                t = torch.from_numpy(v).to(dev)
+                allreduce_stats(t)
+                t.cpu()
+            return r
+
+        for s in range(3):
+            host_step(10_000 + s)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(k_e2e):
+            host_step(20_000 + s)
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * B * P * k_e2e / float(dt.item()), "unit": UNIT,
+               "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
+               "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
+               "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ---- derived numbers
+    peaks = measured_peaks()
+    props = torch.cuda.get_device_properties(dev)
+    n_sm = props.multi_processor_count
+    f_max = float(peaks.get("sm_max_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6
+    peak = n_sm * 128 * f_max  # thread-instructions/s: 4 schedulers x 32 lanes per SM per clock
+    k_ms = float(np.mean(kernel_ms)) if len(kernel_ms) else total_ms / args.steps
+    achieved = B * P * I_ALG[mode] / (k_ms * 1e-3)
+    roofline = {
+        "bound": "issue", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tinstr/s", "frac": achieved / peak,
+        "traffic": None, "kernel": "smmc::mc_kernel<%s>" % mode, "kernel_ms": k_ms,
+        "i_alg": I_ALG[mode],
+        "peak_source": f"{n_sm} SMs x 128 thread-instr/clk x sm_max_mhz {f_max / 1e6:.0f} "
+                       f"({'MEASURED_PEAKS.json' if peaks.get('sm_max_mhz') else 'nvidia-smi'}); HBM/tensor peaks do not bound this path",
+    }
+    if clocks and clocks.get("sm_mhz"):
+        roofline["frac_at_sampled_clock"] = achieved / (n_sm * 128 * clocks["sm_mhz"] * 1e6)
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        cpu = CpuReference(mode, P)
+        sample = cpu.sized_sample(12.0)
+        dt, n = cpu.run(sample)
+        cpu_baseline = {"value": n * P / dt, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
+                        "sample": f"{n} paths x {P} months in {dt:.1f} s; {cpu.desc}"}
+
+    value = world * B * P * args.steps / (total_ms * 1e-3)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "mode": mode, "paths_per_gpu_per_step": B, "periods": P, "seed": seed,
+                   "hist_bins": HIST_BINS, "block_partials": wl["block_partials"], "parallelism": f"paths sharded by RNG offset x{world}",
+                   "collective": "1 all_reduce(SUM) of %d float64 per step (NCCL)" % slen if world > 1 else "none",
+                   "l2": "flushed between timed steps (256 MiB memset outside the event pairs); the path has no HBM input larger than 4.8 KB"},
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,
+        "result": {"count": final.count, "mean": final.mean, "std": final.std, "p_below_target": final.p_below_target},
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -120,6 +120,11 @@ smmc_status smmc_run(const smmc_config *cfg, smmc_result *out);
  * config (histogram / counts bit-identical; mean/M2 to fp64 rounding). Host pointers only. */
 smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out);
 
+/* CUDA-event durations (ms) of the simulation kernel of the most recent launches on `device` (oldest first, at
+ * most 256 are kept), whichever entry point or flags enqueued them.  Blocks until those kernels have finished.
+ * This is how an asynchronous caller (SMMC_FLAG_NO_SYNC) times the kernel on the stream it was launched on. */
+smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int32_t *n_out);
+
 int32_t smmc_stats_len(int32_t hist_bins);
 /* stats: HOST vector of smmc_stats_len(bins) doubles (e.g. after an allreduce). hist may be NULL. */
 smmc_status smmc_stats_finalize(const double *stats, int32_t hist_bins, float initial_capital,

@@ -82,7 +82,7 @@ class SmmcError(RuntimeError):
 # every symbol include/smmc.h declares (tests check the library exports exactly these)
 C_ABI_SYMBOLS = [
     "smmc_run", "smmc_run_multi", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_vector_add",
-    "smmc_debug_draws", "smmc_debug_philox", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
+    "smmc_debug_draws", "smmc_debug_philox", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
 ]
 
 _lib = None
@@ -116,6 +116,8 @@ def load():
     lib.smmc_debug_draws.restype = C.c_int
     lib.smmc_debug_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     lib.smmc_debug_philox.restype = C.c_int
+    lib.smmc_kernel_times.argtypes = [C.c_int32, C.c_void_p, C.c_int32, P(C.c_int32)]
+    lib.smmc_kernel_times.restype = C.c_int
     lib.smmc_last_error.restype = C.c_char_p
     lib.smmc_version.restype = C.c_char_p
     lib.smmc_device_count.restype = C.c_int32

@@ -59,13 +59,17 @@ struct DevBuf {
   }
 };
 
+constexpr int kEventRing = 256;
+
 struct Context {
   int device = -1;
   bool ready = false;
   int n_sms = 0;
   size_t smem_optin = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // ring of event pairs around the simulation kernel of the last kEventRing launches (smmc_kernel_times)
+  cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
+  uint64_t ev_head = 0;  // launches recorded so far
   DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift;
   int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
   uint64_t sobol_seed = 0;
@@ -112,8 +116,10 @@ smmc_status get_context(int device, Context **out) {
     CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     CU(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
     CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&c.ev0));
-    CU(cudaEventCreate(&c.ev1));
+    for (int i = 0; i < kEventRing; i++) {
+      CU(cudaEventCreate(&c.ev0[i]));
+      CU(cudaEventCreate(&c.ev1[i]));
+    }
     c.device = device;
     c.n_sms = sms;
     c.smem_optin = (size_t)optin;
@@ -244,6 +250,7 @@ struct Pending {
   float *finals_dev = nullptr, *bmeans_dev = nullptr, *bvars_dev = nullptr;
   double *stats_dev = nullptr;
   int launches = 0;
+  int ev_slot = 0;
 };
 
 // Enqueue one shard [cfg->stream_offset, +N) on cfg->device.  Caller holds ctx->mu.
@@ -354,9 +361,12 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     if (sst != SMMC_OK) return sst;
   }
 
-  CU(cudaEventRecord(ctx->ev0, st));
+  const int slot = (int)(ctx->ev_head % kEventRing);
+  CU(cudaEventRecord(ctx->ev0[slot], st));
   CU(smmc::launch_mc(cfg->mode, p, li, variant, st));
-  CU(cudaEventRecord(ctx->ev1, st));
+  CU(cudaEventRecord(ctx->ev1[slot], st));
+  ctx->ev_head++;
+  pd->ev_slot = slot;
   pd->launches++;
 
   pd->ctx = ctx;
@@ -394,7 +404,7 @@ smmc_status collect(const Pending &pd, const smmc_result *out, double *stats_hos
   CU(cudaStreamSynchronize(pd.stream));
   memcpy(stats_host, ctx->stats_host, (size_t)pd.stats_len * sizeof(double));
   float ms = 0.0f;
-  CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  CU(cudaEventElapsedTime(&ms, ctx->ev0[pd.ev_slot], ctx->ev1[pd.ev_slot]));
   *device_ms = ms;
   return SMMC_OK;
 }
@@ -609,6 +619,24 @@ smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t 
   return SMMC_OK;
 }
 
+smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int32_t *n_out) {
+  if (!ms_out || !n_out || max_n < 0) return fail(SMMC_ERR_INVALID_ARG, "kernel_times: bad arguments");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  uint64_t have = ctx->ev_head < (uint64_t)kEventRing ? ctx->ev_head : (uint64_t)kEventRing;
+  if (have > (uint64_t)max_n) have = (uint64_t)max_n;
+  for (uint64_t i = 0; i < have; i++) {  // oldest first
+    const int slot = (int)((ctx->ev_head - have + i) % kEventRing);
+    CU(cudaEventSynchronize(ctx->ev1[slot]));
+    CU(cudaEventElapsedTime(&ms_out[i], ctx->ev0[slot], ctx->ev1[slot]));
+  }
+  *n_out = (int32_t)have;
+  return SMMC_OK;
+}
+
 const char *smmc_last_error(void) { return g_err; }
 const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 1)"; }
 int32_t smmc_device_count(void) { return probe_devices(); }
@@ -637,8 +665,11 @@ void smmc_shutdown(void) {
     if (c.stats_host) cudaFreeHost(c.stats_host);
     c.stats_host = nullptr;
     c.stats_host_cap = 0;
-    cudaEventDestroy(c.ev0);
-    cudaEventDestroy(c.ev1);
+    for (int i = 0; i < kEventRing; i++) {
+      cudaEventDestroy(c.ev0[i]);
+      cudaEventDestroy(c.ev1[i]);
+    }
+    c.ev_head = 0;
     cudaStreamDestroy(c.stream);
     c.ready = false;
   }

@@ -1,0 +1,61 @@
+"""Multi-GPU host logic: one process per GPU, paths sharded by RNG offset, ONE sum-allreduce of the statistics vector.
+
+The reference's multi-GPU launcher re-runs the same paths on every device and gathers all finals over PCIe
+(reference src/simulations.cu:576-655, :621-622).  Here rank r simulates the contiguous, 256-aligned path-id
+range `shard_range(N, r, G)`; the path id IS the RNG stream offset, so the union over ranks is exactly the
+1-GPU run.  Each rank's kernel emits the allreduce-ready statistics vector of include/smmc.h
+(count, below, S1, S2, histogram -- all sum-reducible, integer fields exact in fp64), and a single
+`all_reduce(SUM)` (NCCL over NVLink on GPUs, gloo in the CPU tests) merges them.
+
+Nothing here touches per-path data, and nothing here computes paths: the simulation itself is `simulate_device`
+(CUDA only).
+"""
+from . import _native as N
+
+
+def shard_range(n_simulations, rank, world_size, stream_offset=0):
+    """(first_path_id, n_paths) of `rank`: contiguous ranges in units of whole 256-path logical blocks, the
+    remainder blocks going to the lowest ranks.  Same partition rule family as smmc_run_multi
+    (csrc/smmc_api.cu), restated for the one-process-per-GPU launch."""
+    n = int(n_simulations)
+    if n < 0 or world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad shard request")
+    nb = (n + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
+    base, extra = divmod(nb, world_size)
+    b0 = rank * base + min(rank, extra)
+    b1 = b0 + base + (1 if rank < extra else 0)
+    p0 = b0 * N.SMMC_BLOCK
+    p1 = min(b1 * N.SMMC_BLOCK, n)
+    return int(stream_offset) + p0, max(p1 - p0, 0)
+
+
+def allreduce_stats(stats, group=None):
+    """In-place SUM all-reduce of a statistics vector (torch float64 tensor; CUDA for NCCL, CPU for gloo).
+    This is the only collective of the path: O(KB), latency-bound."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
+    return stats
+
+
+def simulate_sharded(mode, n_simulations, n_periods, *, device, stream=None, group=None, hist_bins=0, **kw):
+    """Rank-local shard of a global run of `n_simulations` paths + the allreduce.  Must be called by every rank
+    of `group`.  Returns (Result of the GLOBAL run, launches on this rank).  Needs torch + a CUDA device."""
+    import torch
+    import torch.distributed as dist
+
+    from .simulations import finalize_stats, simulate_device, stats_len
+
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    off, n_local = shard_range(n_simulations, rank, world, kw.pop("stream_offset", 0))
+    dev = torch.device("cuda", device)
+    stats = torch.empty(stats_len(hist_bins), dtype=torch.float64, device=dev)
+    st = stream if stream is not None else torch.cuda.current_stream(dev)
+    with torch.cuda.stream(st):
+        launches = simulate_device(mode, n_local, n_periods, stats.data_ptr(), stream_offset=off,
+                                   hist_bins=hist_bins, device=device, stream=st.cuda_stream, **kw)
+        allreduce_stats(stats, group)
+        host = stats.cpu()
+    return finalize_stats(host.numpy(), hist_bins, kw.get("initial_capital", 1000.0)), launches

@@ -184,6 +184,15 @@ def simulate_device(mode, n_simulations, n_periods, stats_ptr, initial_capital=1
     return int(res.gpu_launches)
 
 
+def kernel_times(device=0, max_n=256):
+    """CUDA-event durations (ms, oldest first) of the simulation kernel of the most recent launches on `device`."""
+    lib = N.load()
+    out = np.zeros(int(max_n), dtype=np.float32)
+    n = C.c_int32()
+    N.check(lib.smmc_kernel_times(int(device), out.ctypes.data, int(max_n), C.byref(n)))
+    return out[:int(n.value)].copy()
+
+
 def finalize_stats(stats, hist_bins, initial_capital) -> Result:
     """Turn a (possibly all-reduced) host statistics vector into count / mean / M2 / below / histogram."""
     lib = N.load()

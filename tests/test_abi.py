@@ -1,0 +1,142 @@
+"""The drop-in boundary: libsmmc.so loads, exports every symbol include/smmc.h declares plus the reference's five
+C++ entry points under their Itanium-mangled names, the ctypes mirrors match the C structs, and
+the library fails loudly without a device (no CPU fallback).  No compute happens here."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "smmc.h")
+
+# reference include/stock_market_monte_carlo/simulations.h:69-86 and gpu.h:1-2, mangled (probed with nm on the
+# reference's own objects)
+REFERENCE_CXX_SYMBOLS = [
+    "_Z18mc_simulations_gpuRSt6atomicIlElifRSt6vectorIfSaIfEES5_i",
+    "_Z30mc_simulations_gpu_reduceBlockRSt6atomicIlElifRSt6vectorIfSaIfEES5_S5_i",
+    "_Z15reduce_mean_gpuRSt6vectorIfSaIfEEl",
+    "_Z10vector_addPfS_S_i",
+    "_Z14vector_add_gpuPfS_S_i",
+]
+
+
+def _declared_functions():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(smmc_[a-z_0-9]+)\s*\(", text)))
+
+
+def _exported(S):
+    from stock_market_monte_carlo_b200 import _native
+    out = subprocess.run(["nm", "-D", "--defined-only", _native.LIB_PATH], capture_output=True, text=True, check=True)
+    return {line.split()[-1] for line in out.stdout.splitlines() if line.strip()}
+
+
+def test_library_exports_every_declared_symbol(S):
+    from stock_market_monte_carlo_b200 import _native
+    declared = _declared_functions()
+    assert declared == sorted(_native.C_ABI_SYMBOLS)
+    exported = _exported(S)
+    missing = [s for s in declared if s not in exported]
+    assert not missing, missing
+    lib = S.load()
+    for s in declared:
+        getattr(lib, s)
+
+
+def test_reference_cxx_entry_points_exported(S):
+    exported = _exported(S)
+    missing = [s for s in REFERENCE_CXX_SYMBOLS if s not in exported]
+    assert not missing, missing
+
+
+def test_struct_layout_matches_header(S, tmp_path):
+    """compile a C probe against include/smmc.h and compare sizeof/offsetof with the ctypes mirrors"""
+    from stock_market_monte_carlo_b200 import _native as N
+    fields_cfg = [f[0] for f in N.SmmcConfig._fields_]
+    fields_res = [f[0] for f in N.SmmcResult._fields_]
+    src = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', "int main(void){",
+           'printf("%zu %zu\\n", sizeof(smmc_config), sizeof(smmc_result));']
+    for f in fields_cfg:
+        src.append(f'printf("c {f} %zu\\n", offsetof(smmc_config, {f}));')
+    for f in fields_res:
+        src.append(f'printf("r {f} %zu\\n", offsetof(smmc_result, {f}));')
+    src.append('printf("k %d %d %d %d\\n", SMMC_ABI_VERSION, SMMC_BLOCK, SMMC_STATS_HEADER, SMMC_MAX_HIST_BINS);')
+    src.append("return 0;}")
+    c = tmp_path / "probe.c"
+    c.write_text("\n".join(src))
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-o", str(exe), str(c)], check=True)
+    lines = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
+    assert lines[0].split() == [str(C.sizeof(N.SmmcConfig)), str(C.sizeof(N.SmmcResult))]
+    for line in lines[1:-1]:
+        kind, name, off = line.split()
+        struct = N.SmmcConfig if kind == "c" else N.SmmcResult
+        assert getattr(struct, name).offset == int(off), line
+    assert lines[-1].split()[1:] == [str(N.SMMC_ABI_VERSION), str(N.SMMC_BLOCK), str(N.SMMC_STATS_HEADER),
+                                     str(N.SMMC_MAX_HIST_BINS)]
+
+
+def test_header_is_plain_c(tmp_path):
+    c = tmp_path / "plain.c"
+    c.write_text(f'#include "{HEADER}"\nint main(void) {{ return smmc_stats_len(0) - 8; }}\n')
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-c", "-o", str(tmp_path / "plain.o"), str(c)],
+                   check=True)
+
+
+def test_cxx_header_compiles_like_the_reference_callers(tmp_path):
+    """a caller written against the reference's signatures compiles against our drop-in header"""
+    cpp = tmp_path / "caller.cpp"
+    cpp.write_text(f'''
+#include "{ROOT}/include/stock_market_monte_carlo/simulations.h"
+#include "{ROOT}/include/stock_market_monte_carlo/gpu.h"
+int main() {{
+  std::atomic<long> n{{0}};
+  std::vector<float> returns{{1.f, -2.f}}, totals, means, variances;
+  if (false) {{
+    mc_simulations_gpu(n, 100L, 360, 1000.f, returns, totals, 1);
+    mc_simulations_gpu_reduceBlock(n, 100L, 360, 1000.f, returns, means, variances, 1);
+    (void)reduce_mean_gpu(totals, 10L);
+    vector_add_gpu(nullptr, nullptr, nullptr, 0);
+  }}
+  return 0;
+}}''')
+    from stock_market_monte_carlo_b200 import _native
+    libdir = os.path.dirname(_native.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-o", str(tmp_path / "caller"), str(cpp), f"-L{libdir}", "-lsmmc",
+                    f"-Wl,-rpath,{libdir}"], check=True)
+    subprocess.run([str(tmp_path / "caller")], check=True)
+
+
+def test_no_device_fails_loudly(S):
+    lib = S.load()
+    if lib.smmc_device_count() > 0:
+        pytest.skip("a device is visible")
+    with pytest.raises(S.SmmcError) as e:
+        S.simulate("gaussian", 1000, 12)
+    assert e.value.status == 2 and "no CPU fallback" in str(e.value)
+    with pytest.raises(S.SmmcError):
+        S.reduce_mean_gpu([1.0, 2.0], 2)
+
+
+def test_validation_precedes_device_probe(S, table):
+    """argument errors are reported as such with or without a GPU (reference behaviour for bad input is UB/abort;
+    the C ABI returns status codes instead, include/smmc.h)"""
+    bad = [
+        dict(mode="bootstrap", n_simulations=10, n_periods=10),                      # no table
+        dict(mode="gaussian", n_simulations=-1, n_periods=10),
+        dict(mode="gaussian", n_simulations=10, n_periods=-1),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, stream_offset=100),    # not a multiple of 256
+        dict(mode="gaussian", n_simulations=10, n_periods=10, hist_bins=5000),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, hist_bins=10, hist_range=(5.0, 5.0)),
+        dict(mode="sobol_gaussian", n_simulations=10, n_periods=1112),
+        dict(mode="bootstrap_compat", n_simulations=2 ** 31, n_periods=1, returns=table),
+        dict(mode="sobol_bootstrap", n_simulations=2 ** 32, n_periods=1, returns=table),
+        dict(mode=17, n_simulations=10, n_periods=10),
+    ]
+    for kw in bad:
+        with pytest.raises(S.SmmcError) as e:
+            S.simulate(**kw)
+        assert e.value.status == 1, kw
