@@ -279,11 +279,11 @@ def test_full_size_gaussian_100m(S, O):
     pooled = r.block_vars.astype(np.float64).mean() + r.block_means.astype(np.float64).var()
     assert abs(pooled / r.variance - 1.0) < 1e-5
     # sharded by RNG offset: two halves == whole, bit-identical integer partials
-    h = N // 2
+    h = (N // 2) // 256 * 256  # shard boundaries are whole 256-path logical blocks
     a = S.simulate("gaussian", h, P, seed=1234, hist_bins=100)
     b = S.simulate("gaussian", N - h, P, seed=1234, hist_bins=100, stream_offset=h)
     assert np.array_equal(a.hist + b.hist, r.hist) and a.below_count + b.below_count == r.below_count
-    assert abs((a.mean + b.mean) / 2 - r.mean) < 1e-12 * r.mean
+    assert abs((a.mean * a.count + b.mean * b.count) / N - r.mean) < 1e-12 * r.mean
     # spot-check far blocks against the oracle
     for off in (256 * 390_000, 256 * 200_001):
         g = S.simulate("gaussian", 512, P, seed=1234, want_finals=True, stream_offset=off)
