@@ -41,9 +41,10 @@ typedef enum smmc_mode {
   /* Reference stream, bit-for-bit: seed rand_pcg(path+1) (src/simulations.cu:62-67,:140), xorshift per month
    * (:69-75,:146), float index map (:148), fmaf compounding (:149).  32-bit path ids: stream_offset+N < 2^31. */
   SMMC_MODE_BOOTSTRAP_COMPAT = 0,
-  /* Philox4x32-10 counter stream, index = mulhi(u32, n_returns) (unbiased to n/2^32). */
+  /* Philox4x32-10 counter stream, six 21/22-bit fields per call, index = floor(field * n_returns / 2^bits)
+   * (unbiased to n/2^21; n_returns < 2^21). */
   SMMC_MODE_BOOTSTRAP = 1,
-  /* Philox4x32-10 counter stream + Box-Muller; r ~ N(gauss_mean, gauss_std) in percent
+  /* Philox4x32-10 counter stream + Box-Muller (one 32-bit word per pair); r ~ N(gauss_mean, gauss_std) in percent
    * (reference CPU semantics: sample_returns_gaussian, src/simulations.cpp:41-55). */
   SMMC_MODE_GAUSSIAN = 2,
   /* Sobol (Joe-Kuo direction numbers as vendored in reference include/sobol/sobol.cpp), point = path id + 1,
@@ -142,7 +143,8 @@ smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t 
 
 /* Raw per-month draws of `n_paths` paths starting at cfg->stream_offset, computed ON THE DEVICE with the same
  * device functions the simulation kernel uses.  out[p * n_periods + m]:
- *   bootstrap modes: table index drawn for month m;  GAUSSIAN modes: the raw 32-bit word behind month m. */
+ *   bootstrap modes: table index drawn for month m;  GAUSSIAN: radius field (even m) / hashed angle word (odd m)
+ *   of the Box-Muller pair behind months m, m+1;  SOBOL_GAUSSIAN: the (shifted) Sobol word of month m. */
 smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *out);
 /* Philox4x32-10 block function on the device: out[4*i..] = philox(ctr[4*i..], key[0..1]) for i < n. */
 smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t n, int32_t device, uint32_t *out);

@@ -55,6 +55,8 @@ def load():
     lib.orc_reduce_mean.argtypes = [C.c_void_p, C.c_int64]
     lib.orc_reduce_mean.restype = C.c_float
     lib.orc_num_threads.restype = C.c_int
+    lib.orc_gauss_pairs.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p]
+    lib.orc_gauss_pairs.restype = None
     _sobol_keep = np.ascontiguousarray(sobol_directions())
     lib.orc_sobol_set_table(_sobol_keep.ctypes.data, 1111)
     _lib = lib
@@ -99,6 +101,15 @@ def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0):
         raise ValueError("oracle rejected the configuration")
     del keep
     return out
+
+
+def gauss_pairs(words, mean_pct=0.0, std_pct=100.0):
+    """growth factors (g0, g1) of each 32-bit word; with mean 0 % and std 100 % they are the normals (z0, z1)"""
+    lib = load()
+    w = np.ascontiguousarray(np.asarray(words, dtype=np.uint32))
+    g = np.zeros((w.size, 2), dtype=np.float32)
+    lib.orc_gauss_pairs(w.ctypes.data, int(w.size), float(mean_pct), float(std_pct), g.ctypes.data)
+    return g
 
 
 def philox(ctr, key):

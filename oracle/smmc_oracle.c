@@ -84,9 +84,9 @@ void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t ou
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-/* stream contract of the native modes (DESIGN.md "RNG stream contract"):
- * counter = (q, path_lo, domain tag, path_hi), key = (seed_lo, seed_hi); call q serves months 4q..4q+3
- * (bootstrap, one word per month) or 6q..6q+5 (gaussian, see gauss_field). */
+/* stream contract of the native modes:
+ * counter = (q, path_lo, domain tag, path_hi), key = (seed_lo, seed_hi); call q serves months 6q..6q+5
+ * (bootstrap: one 21/22-bit field per month) or 8q..8q+7 (gaussian: one 32-bit word per Box-Muller pair). */
 #define TAG_BOOTSTRAP 0x424F4F54u /* "BOOT" */
 #define TAG_GAUSSIAN 0x47415553u  /* "GAUS" */
 #define TAG_SOBOL_SHIFT 0x534F424Cu /* "SOBL" */
@@ -97,8 +97,20 @@ static void stream_words(uint64_t path, uint32_t q, uint32_t tag, uint64_t seed,
   orc_philox4x32_10(ctr, key, w);
 }
 
+/* six bit fields of one call: f0..f3 = low 21 bits of w0..w3; f4 = w0[31:21]:w1[31:21]; f5 = w2[31:21]:w3[31:21] */
+static uint32_t field_of(const uint32_t w[4], int j) {
+  if (j < 4) return w[j] & 0x1FFFFFu;
+  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
+}
+
+/* bootstrap index of field j: floor(f n / 2^bits) in exact integer arithmetic.  (The device gets the same
+ * integer from one round-toward-zero FMA; see boot_load in csrc/smmc_device.cuh.) */
+static uint32_t boot_index(const uint32_t w[4], int j, uint32_t n) {
+  return (uint32_t)(((uint64_t)field_of(w, j) * n) >> (j < 4 ? 21 : 22));
+}
+
 /* ------------------------------------------------------------------------------------------------------- */
-/* Gaussian growth factors from two 32-bit words (Box-Muller)                                                */
+/* Gaussian growth factors from one 32-bit word (Box-Muller pair)                                            */
 
 typedef struct gauss_consts {
   float a;  /* 1 + mean/100                         */
@@ -114,38 +126,32 @@ static gauss_consts make_gauss_consts(float mean_pct, float std_pct) {
   return g;
 }
 
-/* One Philox call feeds six months (DESIGN.md "Gaussian draws"):
- *   f0..f3 = low 21 bits of w0..w3; f4 = w0[31:21]:w1[31:21]; f5 = w2[31:21]:w3[31:21] (22 bits);
- *   pair p = (radius field f_2p, angle field f_2p+1) -> months 6q+2p (cos), 6q+2p+1 (sin);
- *   u = (f + 1/2)/2^bits, v = 2 pi u - pi.  The float constants are the device's, digit for digit. */
-static uint32_t gauss_field(const uint32_t w[4], int j) {
-  if (j < 4) return w[j] & 0x1FFFFFu;
-  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
-}
-
 static float as_float(uint32_t bits) {
   float f;
   memcpy(&f, &bits, sizeof f);
   return f;
 }
 
-/* (fr, fa) -> growth factors of two consecutive months.  The device uses MUFU lg2/sqrt/sin/cos approximations
- * where this uses libm, so Gaussian finals agree to a stated tolerance, not bit-for-bit (tests state it). */
-static void gauss_pair(uint32_t fr, uint32_t fa, int bits, gauss_consts gc, float *g0, float *g1) {
-  float mr = as_float(fr | 0x3F800000u), ma = as_float(fa | 0x3F800000u);
-  float u, v;
-  if (bits == 21) {
-    u = fmaf(mr, 4.0f, -3.99999976158142089844f);
-    v = fmaf(ma, 25.132741928100585938f, -28.274332046508789062f);
-  } else {
-    u = fmaf(mr, 2.0f, -1.99999988079071044922f);
-    v = fmaf(ma, 12.566370964050292969f, -15.707962989807128906f);
-  }
+/* word w -> growth factors of two consecutive months (DESIGN.md "Gaussian draws"):
+ *   radius u = (f + 1/2)/2^20, f = w[19:0];  angle v = 2 pi int32(w K)/2^32, K = 0x9E3779B1 (bijective hash, so
+ *   that the offset of the 4096-direction grid behind each radius is equidistributed).  The float constants are the device's,
+ * digit for digit.  The device uses MUFU lg2/sqrt/sin/cos approximations where this uses libm, so Gaussian
+ * finals agree to a stated tolerance, not bit-for-bit (tests state it). */
+static void gauss_pair(uint32_t w, gauss_consts gc, float *g0, float *g1) {
+  float mr = as_float((w & 0xFFFFFu) | 0x3F800000u);
+  float u = fmaf(mr, 8.0f, -7.99999952316284179688f);
+  float v = (float)(int32_t)(w * 0x9E3779B1u) * 1.4629180792671596e-09f;
   float t = log2f(u) * gc.k;
   float rs = sqrtf(t);
   float c = cosf(v), s = sinf(v);
   *g0 = fmaf(rs, c, gc.a);
   *g1 = fmaf(rs, s, gc.a);
+}
+
+/* test hook: growth factors of n words (g[2i], g[2i+1]) */
+void orc_gauss_pairs(const uint32_t *w, int64_t n, float mean_pct, float std_pct, float *g) {
+  gauss_consts gc = make_gauss_consts(mean_pct, std_pct);
+  for (int64_t i = 0; i < n; i++) gauss_pair(w[i], gc, &g[2 * i], &g[2 * i + 1]);
 }
 
 /* ------------------------------------------------------------------------------------------------------- */
@@ -247,8 +253,9 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
     case SMMC_MODE_BOOTSTRAP: {
       uint32_t w[4];
       for (int m = 0; m < P; m++) {
-        if ((m & 3) == 0) stream_words(path, (uint32_t)(m >> 2), TAG_BOOTSTRAP, cfg->seed, w);
-        uint32_t idx = (uint32_t)(((uint64_t)w[m & 3] * (uint32_t)n) >> 32);
+        int j = m % 6;
+        if (j == 0) stream_words(path, (uint32_t)(m / 6), TAG_BOOTSTRAP, cfg->seed, w);
+        uint32_t idx = boot_index(w, j, (uint32_t)n);
         if (draws) draws[m] = idx;
         total = fmaf(total, rc->tbl[idx], total);
       }
@@ -257,10 +264,10 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
       uint32_t w[4];
       float g[2];
       for (int m = 0; m < P; m++) {
-        int j = m % 6;
-        if (j == 0) stream_words(path, (uint32_t)(m / 6), TAG_GAUSSIAN, cfg->seed, w);
-        if ((j & 1) == 0) gauss_pair(gauss_field(w, j), gauss_field(w, j + 1), j < 4 ? 21 : 22, rc->gc, &g[0], &g[1]);
-        if (draws) draws[m] = gauss_field(w, j);
+        int j = m % 8;
+        if (j == 0) stream_words(path, (uint32_t)(m / 8), TAG_GAUSSIAN, cfg->seed, w);
+        if ((j & 1) == 0) gauss_pair(w[j >> 1], rc->gc, &g[0], &g[1]);
+        if (draws) draws[m] = (j & 1) ? w[j >> 1] * 0x9E3779B1u : (w[j >> 1] & 0xFFFFFu); /* radius field | hashed angle word */
         total = total * g[j & 1];
       }
     } break;

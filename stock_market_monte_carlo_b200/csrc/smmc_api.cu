@@ -145,7 +145,7 @@ smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
   if (cfg->stream_offset % SMMC_BLOCK) return fail(SMMC_ERR_INVALID_ARG, "stream_offset must be a multiple of %d", SMMC_BLOCK);
   if (is_bootstrap(cfg->mode)) {
     if (!cfg->returns || cfg->n_returns < 1) return fail(SMMC_ERR_INVALID_ARG, "bootstrap modes need a non-empty returns table");
-    if (cfg->n_returns >= (1 << 24)) return fail(SMMC_ERR_INVALID_ARG, "n_returns must be < 2^24");
+    if (cfg->n_returns >= (1 << 21)) return fail(SMMC_ERR_INVALID_ARG, "n_returns must be < 2^21");
   }
   if (cfg->mode == SMMC_MODE_BOOTSTRAP_COMPAT && cfg->stream_offset + (uint64_t)cfg->n_simulations > 0x7fffffffull)
     return fail(SMMC_ERR_INVALID_ARG, "BOOTSTRAP_COMPAT uses the reference's 32-bit path ids: stream_offset + N must be < 2^31");
@@ -282,6 +282,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
     p.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)sigma);
   }
+  p.one = 0x3F800000u;
   p.v0 = cfg->initial_capital;
   p.target = cfg->target;
   p.hist_lo = cfg->hist_lo;
@@ -315,6 +316,12 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.rep4 = (uint32_t)li.rep * 4u;
     p.nr4 = (uint32_t)n * (uint32_t)li.rep * 4u;
     p.idx_scale = (float)n * 2.3283064365386963e-10f;  // exact: n < 2^24
+    p.bc.c21 = (float)(4 * n);                          // exact: n < 2^21 (validated)
+    p.bc.k21 = (float)(8388608 - 4 * n);
+    p.bc.c22 = (float)(2 * n);
+    p.bc.k22 = (float)(8388608 - 2 * n);
+    p.bc.row_shift = 2;
+    while ((1u << p.bc.row_shift) < (uint32_t)li.rep * 4u) p.bc.row_shift++;
   } else {
     p.rep4 = 4u;
   }
@@ -577,6 +584,11 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
   p.compat_seed = (uint32_t)cfg->seed;
   p.keys = make_keys(cfg->seed);
   p.idx_scale = (float)cfg->n_returns * 2.3283064365386963e-10f;
+  p.one = 0x3F800000u;
+  p.bc.c21 = (float)(4 * cfg->n_returns);
+  p.bc.k21 = (float)(8388608 - 4 * cfg->n_returns);
+  p.bc.c22 = (float)(2 * cfg->n_returns);
+  p.bc.k22 = (float)(8388608 - 2 * cfg->n_returns);
   const size_t bytes = (size_t)n_paths * (size_t)cfg->n_periods * 4;
   if (bytes == 0) return SMMC_OK;
   CU(ctx->scratch.reserve(bytes));

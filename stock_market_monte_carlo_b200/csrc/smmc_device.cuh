@@ -62,11 +62,13 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
   out[3] = c3;
 }
 
-// Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed; call q serves months
-// 4q..4q+3 (BOOTSTRAP: one 32-bit word per month) or 6q..6q+5 (GAUSSIAN, see gauss_group).  The per-lane quantity (path_lo) sits in counter word 1 so that in
-// rounds 1-3 one of the two 32x32->64 multiplies has warp-uniform operands (q, tag, path_hi and the key are
-// uniform over a 256-path block): the compiler hoists those to once per call per warp, and only 16 of the
-// 20 multiplies of a call are per-lane work.
+// Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed.
+// One Philox call = 128 bits serves SIX bootstrap months (call q -> months 6q..6q+5, one 21/22-bit field each)
+// or EIGHT Gaussian months (call q -> months 8q..8q+7, one 32-bit word per Box-Muller pair).  The wide
+// multiplies of Philox run at a quarter of the issue rate on sm_100a (profiles/r01_pipe_microbench.txt), so no
+// bits are wasted.  The per-lane quantity (path_lo) sits in counter word 1 so that in rounds 1-3 one of the two
+// 32x32->64 multiplies has warp-uniform operands (q, tag, path_hi and the key are uniform over a 256-path block):
+// only 16 of the 20 multiplies of a call are per-lane work.
 constexpr uint32_t kTagBootstrap = 0x424F4F54u;   // "BOOT"
 constexpr uint32_t kTagGaussian = 0x47415553u;    // "GAUS"
 constexpr uint32_t kTagSobolShift = 0x534F424Cu;  // "SOBL"
@@ -98,56 +100,76 @@ __device__ __forceinline__ float cos_approx(float x) {
   return y;
 }
 
+// ---- six bit fields of one Philox call ------------------------------------------------------------------------
+//   f0..f3 = low 21 bits of w0..w3;  f4 = w0[31:21] : w1[31:21];  f5 = w2[31:21] : w3[31:21]  (22 bits)
+// A field is used as the mantissa of a float in [1,2): m = 1 + f 2^-23 (one LOP3: (w & mask) | 0x3F800000).
+constexpr int kFieldsPerCall = 6;
+constexpr uint32_t kOne = 0x3F800000u;
+
+__device__ __forceinline__ uint32_t field_of(const uint32_t (&w)[4], int j) {
+  if (j < 4) return w[j] & 0x1FFFFFu;
+  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
+}
+// mantissa form of the six fields; `one` is 0x3F800000 held in a register so that (w & mask) | one is ONE LOP3
+__device__ __forceinline__ void field_mantissas(const uint32_t (&w)[4], uint32_t one, uint32_t (&m)[6]) {
+#pragma unroll
+  for (int j = 0; j < 4; j++) m[j] = (w[j] & 0x1FFFFFu) | one;
+  m[4] = (((w[0] >> 10) & 0x3FF800u) | (w[1] >> 21)) | one;
+  m[5] = (((w[2] >> 10) & 0x3FF800u) | (w[3] >> 21)) | one;
+}
+
+// ---- bootstrap index (native modes) ---------------------------------------------------------------------------
+// idx = floor(f * n / 2^bits), f a `bits`-wide field: unbiased to n / 2^21.  Computed without an integer multiply:
+//   y = fma.rz(m, c, 2^23 - c),  m = 1 + f 2^-23,  c = n * 2^(23 - bits)   (c and 2^23 - c are exact: n < 2^21)
+// m * c is exact inside the FMA and the sum lands in [2^23, 2^24), where the float spacing is 1, so round-toward-
+// zero IS the floor: the bit pattern of y is 0x4B000000 + idx.  The byte address of the bank-private table row is
+// then one shift-add (LEA): (bits(y) << log2(row bytes)) + base, with the shifted-out exponent folded into `base`.
+struct BootConsts {
+  float c21, k21;      // 4n, 2^23 - 4n
+  float c22, k22;      // 2n, 2^23 - 2n
+  uint32_t row_shift;  // log2(rep * 4)
+};
+
+template <int SHIFT>
+__device__ __forceinline__ float boot_load(uint32_t m, float c, float k, uint32_t base, uint32_t row_shift) {
+  const float y = __fmaf_rz(__uint_as_float(m), c, k);
+  const uint32_t sh = SHIFT >= 0 ? (uint32_t)SHIFT : row_shift;
+  const uint32_t addr = (__float_as_uint(y) << sh) + base;
+  float r;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(addr));
+  return r;
+}
+
 // ---- Gaussian growth factors (Box-Muller) -------------------------------------------------------------------
 // r ~ N(mean, std) percent, fund *= (100 + r)/100 (reference src/simulations.cpp:14-16, :41-55), evaluated as
 // g = (1 + mean/100) + (std/100) z with (z0, z1) = sqrt(-2 ln u) (cos v, sin v).
 //
-// One Philox call (128 bits) feeds SIX months: the IMAD.WIDE multiplies of Philox run at a quarter of the issue
-// rate on sm_100a (profiles/r01_pipe_microbench.txt), so bits are not wasted.  Fields (f = integer value):
-//   f0..f3 = low 21 bits of w0..w3;  f4 = w0[31:21] : w1[31:21];  f5 = w2[31:21] : w3[31:21]  (22 bits)
-//   pair p = (radius field f_{2p}, angle field f_{2p+1}) serves months 6q + 2p (cos) and 6q + 2p + 1 (sin)
-//   u = (f + 1/2) / 2^bits  in (0,1)   (never 0 or 1: no special cases),   v = 2 pi u - pi  in (-pi, pi)
-// A field is turned into a float by OR-ing it into the mantissa of 1.0f (one LOP3, no I2F), then one exact FFMA.
+// One 32-bit word w serves one Box-Muller pair = two months:
+//   radius  u = (f + 1/2) / 2^20  in (0,1),  f = w[19:0]        (never 0 or 1: no special cases)
+//   angle   v = 2 pi * int32(w * K) / 2^32  in [-pi, pi],  K = 0x9E3779B1 (odd: w -> w K is a bijection mod 2^32)
+// For a given radius field the 4096 words that share it map to a uniform grid of 4096 directions whose offset is
+// frac(K f / 2^20): a hash of the radius bits, equidistributed over any radius interval.  Averages of a
+// trigonometric polynomial of degree < 4096 over each grid equal the continuous average (all joint moments of
+// (z0, z1) up to that order are those of independent normals), and the hashed offsets make the angle effectively
+// continuous for non-smooth functionals (2-D chi-square and polar-bin tests in tests/test_oracle_pins.py; taking
+// the angle from the raw word, or from its top 12 bits only, fails them).
 //   (std/100) sqrt(-2 ln u) = sqrt(lg2(u) * k),  k = -2 ln2 (std/100)^2.
 struct GaussConsts {
   float a;  // 1 + mean/100
   float k;  // -2 ln2 sigma^2
 };
 
-constexpr int kGaussMonthsPerCall = 6;
+constexpr int kGaussMonthsPerCall = 8;
+constexpr uint32_t kAngleHash = 0x9E3779B1u;
 
-template <int BITS>
-__device__ __forceinline__ void gauss_pair(uint32_t fr, uint32_t fa, const GaussConsts gc, float &g0, float &g1) {
-  static_assert(BITS == 21 || BITS == 22, "field width");
-  const float mr = __uint_as_float(fr | 0x3F800000u);  // 1 + f 2^-23
-  const float ma = __uint_as_float(fa | 0x3F800000u);
-  float u, v;
-  if (BITS == 21) {
-    u = fmaf(mr, 4.0f, -3.99999976158142089844f);               // (f + 1/2) 2^-21, exact
-    v = fmaf(ma, 25.132741928100585938f, -28.274332046508789062f);  // 8 pi m - (9 - 2^-21) pi
-  } else {
-    u = fmaf(mr, 2.0f, -1.99999988079071044922f);               // (f + 1/2) 2^-22, exact
-    v = fmaf(ma, 12.566370964050292969f, -15.707962989807128906f);  // 4 pi m - (5 - 2^-22) pi
-  }
+__device__ __forceinline__ void gauss_pair(uint32_t w, uint32_t one, const GaussConsts gc, float &g0, float &g1) {
+  const float mr = __uint_as_float((w & 0xFFFFFu) | one);            // 1 + f 2^-23
+  const float u = fmaf(mr, 8.0f, -7.99999952316284179688f);          // (f + 1/2) 2^-20, exact
+  const float v = __int2float_rn((int)(w * kAngleHash)) * 1.4629180792671596e-09f;  // 2 pi 2^-32
   const float t = lg2_approx(u) * gc.k;
   const float rs = sqrt_approx(t);
   g0 = fmaf(rs, cos_approx(v), gc.a);
   g1 = fmaf(rs, sin_approx(v), gc.a);
-}
-
-// growth factors of the six months served by one Philox call
-__device__ __forceinline__ void gauss_group(const uint32_t (&w)[4], const GaussConsts gc, float (&g)[6]) {
-  const uint32_t f4 = ((w[0] >> 21) << 11) | (w[1] >> 21);
-  const uint32_t f5 = ((w[2] >> 21) << 11) | (w[3] >> 21);
-  gauss_pair<21>(w[0] & 0x1FFFFFu, w[1] & 0x1FFFFFu, gc, g[0], g[1]);
-  gauss_pair<21>(w[2] & 0x1FFFFFu, w[3] & 0x1FFFFFu, gc, g[2], g[3]);
-  gauss_pair<22>(f4, f5, gc, g[4], g[5]);
-}
-
-// field behind month j (0..5) of a call, for the draw-level parity test
-__device__ __forceinline__ uint32_t gauss_field(const uint32_t (&w)[4], int j) {
-  if (j < 4) return w[j] & 0x1FFFFFu;
-  return j == 4 ? (((w[0] >> 21) << 11) | (w[1] >> 21)) : (((w[2] >> 21) << 11) | (w[3] >> 21));
 }
 
 // ---- inverse normal CDF (SOBOL_GAUSSIAN) ----------------------------------------------------------------------

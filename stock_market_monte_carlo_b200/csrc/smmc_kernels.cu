@@ -92,39 +92,50 @@ __device__ __forceinline__ float boot_step(float tot, uint32_t w, const char *tb
   return fmaf(tot, r, tot);
 }
 
-template <int ILP>
-__device__ __forceinline__ void run_bootstrap(const KParams &p, const char *tbl, uint32_t lane_off,
-                                              const uint32_t (&plo)[ILP], uint32_t phi, float (&tot)[ILP]) {
-  const uint32_t nr4 = p.nr4;
-  const uint32_t row_mask = ~(p.rep4 - 1u);
-  const int nq = p.n_periods >> 2;
+// months 6q..6q+5 of ILP paths: one Philox call each, six table gathers, six FFMAs
+template <int ILP, int SHIFT>
+__device__ __forceinline__ void run_bootstrap(const KParams &p, uint32_t base, const uint32_t (&plo)[ILP],
+                                              uint32_t phi, float (&tot)[ILP]) {
+  const BootConsts bc = p.bc;
+  const uint32_t one = p.one;
+  const int nq = p.n_periods / kFieldsPerCall;
 #pragma unroll 1
   for (int q = 0; q < nq; q++) {
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
-      uint32_t w[4];
+      uint32_t w[4], m[6];
       stream_words(plo[i], phi, (uint32_t)q, kTagBootstrap, p.keys, w);
+      field_mantissas(w, one, m);
 #pragma unroll
-      for (int j = 0; j < 4; j++) tot[i] = boot_step(tot[i], w[j], tbl, nr4, row_mask, lane_off);
+      for (int j = 0; j < 6; j++) {
+        const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
+        tot[i] = fmaf(tot[i], r, tot[i]);
+      }
     }
   }
-  const int rem = p.n_periods & 3;
+  const int rem = p.n_periods - nq * kFieldsPerCall;
   if (rem) {
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
-      uint32_t w[4];
+      uint32_t w[4], m[6];
       stream_words(plo[i], phi, (uint32_t)nq, kTagBootstrap, p.keys, w);
+      field_mantissas(w, one, m);
 #pragma unroll
-      for (int j = 0; j < 3; j++)
-        if (j < rem) tot[i] = boot_step(tot[i], w[j], tbl, nr4, row_mask, lane_off);
+      for (int j = 0; j < 5; j++)
+        if (j < rem) {
+          const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
+          tot[i] = fmaf(tot[i], r, tot[i]);
+        }
     }
   }
 }
 
+// months 8q..8q+7 of ILP paths: one Philox call each, four Box-Muller pairs
 template <int ILP>
 __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&plo)[ILP], uint32_t phi,
                                              float (&tot)[ILP]) {
   const GaussConsts gc = p.gc;
+  const uint32_t one = p.one;
   const int nq = p.n_periods / kGaussMonthsPerCall;
 #pragma unroll 1
   for (int q = 0; q < nq; q++) {
@@ -132,10 +143,12 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
       stream_words(plo[i], phi, (uint32_t)q, kTagGaussian, p.keys, w);
-      float g[6];
-      gauss_group(w, gc, g);
 #pragma unroll
-      for (int j = 0; j < 6; j++) tot[i] = __fmul_rn(tot[i], g[j]);
+      for (int j = 0; j < 4; j++) {
+        float g0, g1;
+        gauss_pair(w[j], one, gc, g0, g1);
+        tot[i] = __fmul_rn(__fmul_rn(tot[i], g0), g1);
+      }
     }
   }
   const int rem = p.n_periods - nq * kGaussMonthsPerCall;
@@ -144,11 +157,13 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
       stream_words(plo[i], phi, (uint32_t)nq, kTagGaussian, p.keys, w);
-      float g[6];
-      gauss_group(w, gc, g);
 #pragma unroll
-      for (int j = 0; j < 5; j++)
-        if (j < rem) tot[i] = __fmul_rn(tot[i], g[j]);
+      for (int j = 0; j < 4; j++) {
+        float g0, g1;
+        gauss_pair(w[j], one, gc, g0, g1);
+        if (2 * j < rem) tot[i] = __fmul_rn(tot[i], g0);
+        if (2 * j + 1 < rem) tot[i] = __fmul_rn(tot[i], g1);
+      }
     }
   }
 }
@@ -207,7 +222,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const char *tbl, uin
 
 // ---- the fused persistent kernel ---------------------------------------------------------------------------------
 
-template <int MODE, int ILP>
+template <int MODE, int ILP, int SHIFT>
 __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr bool kHasTable = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT || MODE == SMMC_MODE_BOOTSTRAP ||
@@ -252,6 +267,8 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   const int64_t total_warps = (int64_t)gridDim.x * kWarps;
   const uint32_t lane_off = (lane * 4u) & (p.rep4 - 1u);
   constexpr bool kCompat = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT);
+  // BOOTSTRAP: shared-window address of this lane's column, minus the float exponent bits that boot_load shifts out
+  const uint32_t boot_base = smem_u32(tbl) + lane_off - (0x4B000000u << (SHIFT >= 0 ? (uint32_t)SHIFT : p.bc.row_shift));
 
   Moments acc = {0.0, 0.0, 0.0};
   unsigned int below_lane = 0;
@@ -279,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
         tot[i] = p.v0;
       }
       if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP>(p, tbl, lane_off, plo, tot);
-      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP>(p, tbl, lane_off, plo, phi, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT>(p, boot_base, plo, phi, tot);
       if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP>(p, plo, phi, tot);
 #pragma unroll
       for (int i = 0; i < ILP; i++) x[s + i] = tot[i];
@@ -450,17 +467,23 @@ __global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, 
       st = xorshift(st);
       o[m] = (uint32_t)(int)(__uint2float_rn(st) * p.idx_scale);
     }
-  } else if (mode == SMMC_MODE_BOOTSTRAP) {
-    uint32_t w[4];
+  } else if (mode == SMMC_MODE_BOOTSTRAP) {  // the index as the simulation kernel computes it (fma.rz floor)
+    uint32_t w[4], mt[6];
     for (int m = 0; m < p.n_periods; m++) {
-      if ((m & 3) == 0) stream_words(plo, phi, (uint32_t)(m >> 2), kTagBootstrap, p.keys, w);
-      o[m] = __umulhi(w[m & 3], (uint32_t)p.n_returns);
+      const int j = m % 6;
+      if (j == 0) {
+        stream_words(plo, phi, (uint32_t)(m / 6), kTagBootstrap, p.keys, w);
+        field_mantissas(w, p.one, mt);
+      }
+      const float y = __fmaf_rz(__uint_as_float(mt[j]), j < 4 ? p.bc.c21 : p.bc.c22, j < 4 ? p.bc.k21 : p.bc.k22);
+      o[m] = __float_as_uint(y) - 0x4B000000u;
     }
-  } else if (mode == SMMC_MODE_GAUSSIAN) {
+  } else if (mode == SMMC_MODE_GAUSSIAN) {  // even month: radius field, odd month: the hashed angle word
     uint32_t w[4];
     for (int m = 0; m < p.n_periods; m++) {
-      if (m % 6 == 0) stream_words(plo, phi, (uint32_t)(m / 6), kTagGaussian, p.keys, w);
-      o[m] = gauss_field(w, m % 6);
+      const int j = m % 8;
+      if (j == 0) stream_words(plo, phi, (uint32_t)(m / 8), kTagGaussian, p.keys, w);
+      o[m] = (j & 1) ? w[j >> 1] * kAngleHash : (w[j >> 1] & 0xFFFFFu);
     }
   } else {  // Sobol modes: plain Gray-code evaluation over all 32 direction numbers of dimension m
     const uint64_t i = path + kSobolSkip;
@@ -522,12 +545,12 @@ __global__ void vector_add_kernel(float *__restrict__ out, const float *__restri
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = a[i] + b[i];
 }
 
-template <int MODE, int ILP>
+template <int MODE, int ILP, int SHIFT = -1>
 cudaError_t launch_one(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP, SHIFT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)li.smem_bytes);
   if (e != cudaSuccess) return e;
-  mc_kernel<MODE, ILP><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
+  mc_kernel<MODE, ILP, SHIFT><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
   return cudaGetLastError();
 }
 
@@ -539,6 +562,18 @@ cudaError_t launch_mode(const KParams &p, const LaunchInfo &li, int variant, cud
     case 8: return launch_one<MODE, 8>(p, li, s);
     case 4:
     default: return launch_one<MODE, 4>(p, li, s);
+  }
+}
+
+// BOOTSTRAP: the common case (32 bank-private copies per row: 128-byte rows) gets the row shift as an immediate
+cudaError_t launch_bootstrap(const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s) {
+  if (li.rep != 32) return launch_mode<SMMC_MODE_BOOTSTRAP>(p, li, variant, s);
+  switch (variant) {
+    case 1: return launch_one<SMMC_MODE_BOOTSTRAP, 1, 7>(p, li, s);
+    case 2: return launch_one<SMMC_MODE_BOOTSTRAP, 2, 7>(p, li, s);
+    case 8: return launch_one<SMMC_MODE_BOOTSTRAP, 8, 7>(p, li, s);
+    case 4:
+    default: return launch_one<SMMC_MODE_BOOTSTRAP, 4, 7>(p, li, s);
   }
 }
 
@@ -583,7 +618,7 @@ cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int vari
     case SMMC_MODE_SOBOL_BOOTSTRAP: return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8>(p, li, s);
     case SMMC_MODE_SOBOL_GAUSSIAN: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8>(p, li, s);
     case SMMC_MODE_BOOTSTRAP_COMPAT: return launch_mode<SMMC_MODE_BOOTSTRAP_COMPAT>(p, li, variant, s);
-    case SMMC_MODE_BOOTSTRAP: return launch_mode<SMMC_MODE_BOOTSTRAP>(p, li, variant, s);
+    case SMMC_MODE_BOOTSTRAP: return launch_bootstrap(p, li, variant, s);
     case SMMC_MODE_GAUSSIAN: return launch_mode<SMMC_MODE_GAUSSIAN>(p, li, variant, s);
     default: return cudaErrorInvalidValue;
   }

@@ -339,6 +339,7 @@ def test_distribution_vs_reference_cpu_generators(S, table):
 # ---- the C++ drop-in boundary -------------------------------------------------------------------------------------
 CALLER = r'''
 #include <cstdio>
+#include <stdexcept>
 #include "stock_market_monte_carlo/simulations.h"
 int main(int argc, char **argv) {
   std::vector<float> returns;

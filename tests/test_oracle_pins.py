@@ -215,6 +215,51 @@ def test_closed_form_gaussian(O):
     assert abs(q.mean - mean) < 1.0 * std / np.sqrt(1 << 17)
 
 
+def test_box_muller_pairs_are_jointly_normal(O):
+    """One 32-bit word -> (z0, z1): radius from w[19:0], angle from the hashed word.  Marginals,
+    joint moments, a 2-D chi-square on quantile cells and a polar-bin chi-square with a non-dyadic number of angle
+    bins (which a raw 12-bit angle grid fails)."""
+    from scipy import stats
+    n = 8_000_000
+    w = np.random.default_rng(3).integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    z = O.gauss_pairs(w, 0.0, 100.0).astype(np.float64) - 1.0
+    z0, z1 = z[:, 0], z[:, 1]
+    se = 1.0 / np.sqrt(n)
+    assert abs(z0.mean()) < 5 * se and abs(z1.mean()) < 5 * se
+    assert abs(z0.var() - 1) < 5 * np.sqrt(2) * se and abs(z1.var() - 1) < 5 * np.sqrt(2) * se
+    assert abs((z0 * z1).mean()) < 5 * se
+    assert abs((z0 ** 4).mean() - 3) < 5 * np.sqrt(96) * se and abs((z0 ** 2 * z1 ** 2).mean() - 1) < 5 * np.sqrt(8) * se
+    assert 5.0 < np.abs(z).max() < 5.45  # radius field is 20 bits: |z| <= sqrt(2 ln 2^21) = 5.40
+    assert stats.kstest(z0[:2_000_000], "norm").pvalue > 1e-3 and stats.kstest(z1[:2_000_000], "norm").pvalue > 1e-3
+    k = 32
+    edges = stats.norm.ppf(np.linspace(0, 1, k + 1)[1:-1])
+    cells = np.bincount(np.searchsorted(edges, z0) * k + np.searchsorted(edges, z1), minlength=k * k)
+    chi = ((cells - n / k ** 2) ** 2 / (n / k ** 2)).sum()
+    assert stats.chi2.sf(chi, k * k - 1) > 1e-4
+    ang = np.floor((np.arctan2(z1, z0) + np.pi) / (2 * np.pi) * 1000).astype(np.int64).clip(0, 999)
+    rad = np.searchsorted(np.sqrt(-2 * np.log(1 - np.linspace(0, 1, 11)[1:-1])), np.hypot(z0, z1))
+    cells = np.bincount(ang * 10 + rad, minlength=10_000)
+    chi = ((cells - n / 1e4) ** 2 / (n / 1e4)).sum()
+    assert stats.chi2.sf(chi, 9999) > 1e-4
+
+
+def test_bootstrap_index_is_the_exact_floor(O, table):
+    """idx = floor(f n / 2^bits) for the six fields of a call; every index < n; near-uniform over the table"""
+    d = O.draws("bootstrap", 2000, 600, returns=table, seed=9)
+    assert d.max() < table.size
+    counts = np.bincount(d.ravel(), minlength=table.size)
+    from scipy import stats
+    chi = ((counts - d.size / table.size) ** 2 / (d.size / table.size)).sum()
+    assert stats.chi2.sf(chi, table.size - 1) > 1e-4
+    # restate the contract in Python for one path
+    lib = O.load()
+    w = O.philox([[0, 5, 0x424F4F54, 0]], [9, 0])[0]
+    f = [int(x) & 0x1FFFFF for x in w] + [((int(w[0]) >> 21) << 11) | (int(w[1]) >> 21), ((int(w[2]) >> 21) << 11) | (int(w[3]) >> 21)]
+    want = [(f[j] * table.size) >> (21 if j < 4 else 22) for j in range(6)]
+    got = O.draws("bootstrap", 6, 6, returns=table, seed=9)[5]
+    assert list(got) == want
+
+
 # ---- contract freeze ----------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("mode", ALL_MODES)
 def test_oracle_regression_fixture(O, table, mode):
