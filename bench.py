@@ -45,8 +45,13 @@ import numpy as np  # noqa: E402
 METRIC = "path-months/sec (device-timed)"
 UNIT = "path-months/s"
 
-# algorithmic thread-instructions per path-month (restated in DESIGN.md "Roofline")
-I_ALG = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": 6, "sobol_gaussian": 12}
+# Algorithmic thread-instructions per path-month of the IMPLEMENTED recipes (minimal SASS-level count, DESIGN.md
+# section 4; restates SURVEY 8(d) for the stream contract actually shipped).  SURVEY 8(d) budgeted 19 (bootstrap:
+# 4 draws per Philox call + IMAD.HI index) and 22 (gaussian: 2 normals per 2 words); the shipped recipes draw 6
+# fields / 8 normals per call and need 12, so the fraction below stays an issue-slot utilisation (<= 1).  The
+# SURVEY-budget fraction is reported next to it as `frac_survey_budget`.
+I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 24}
+I_ALG_SURVEY = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": None, "sobol_gaussian": None}
 
 WORKLOADS = {
     "c2": dict(mode="gaussian", paths=100_000_000, periods=360, block_partials=True, hist_range=(0.0, 50_000.0),
@@ -232,6 +237,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if not os.environ.get("SMMC_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout: keep the JSON line alone there
         dist.init_process_group("nccl", device_id=dev)
 
     mode, B, P = wl["mode"], wl["paths"], wl["periods"]
@@ -350,7 +357,8 @@ def main():
     roofline = {
         "bound": "issue", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tinstr/s", "frac": achieved / peak,
         "traffic": None, "kernel": "smmc::mc_kernel<%s>" % mode, "kernel_ms": k_ms,
-        "i_alg": I_ALG[mode],
+        "i_alg": I_ALG[mode], "survey_i_alg": I_ALG_SURVEY[mode],
+        "frac_survey_budget": (achieved / I_ALG[mode] * I_ALG_SURVEY[mode] / peak) if I_ALG_SURVEY[mode] else None,
         "peak_source": f"{n_sm} SMs x 128 thread-instr/clk x sm_max_mhz {f_max / 1e6:.0f} "
                        f"({'MEASURED_PEAKS.json' if peaks.get('sm_max_mhz') else 'nvidia-smi'}); HBM/tensor peaks do not bound this path",
     }

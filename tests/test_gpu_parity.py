@@ -380,3 +380,48 @@ def test_cxx_drop_in_program(S, O, table1127, tmp_path):
     o = O.simulate("bootstrap_compat", 5000, 36, returns=table1127, want_finals=True, want_block_partials=True)
     assert np.array_equal(out[:5000], o.finals)
     assert np.array_equal(out[5000:5020], o.block_means) and np.array_equal(out[5020:], o.block_vars)
+
+
+def _run_relinked(tmp_path, exe, args, table):
+    """run one of the reference's own example programs (unmodified source, relinked against libsmmc.so by
+    `make -C oracle relink`) in a scratch directory holding the CSV it expects"""
+    import shutil
+    (tmp_path / "data").mkdir(exist_ok=True)
+    with open(tmp_path / "data" / "SP500_monthly_returns.csv", "w") as f:  # reference src/simulations.cpp:83-93
+        f.write("Date,returns\n")
+        for x in table:
+            f.write(f"1900-01-01,{float(x)!r}\n")
+    env = dict(os.environ)
+    if os.path.isdir("/usr/lib/locale/C.utf8"):  # the examples ask for en_US.UTF-8, which this image does not ship
+        loc = tmp_path / "locale"
+        if not loc.exists():
+            shutil.copytree("/usr/lib/locale/C.utf8", loc / "en_US.UTF-8")
+        env["LOCPATH"] = str(loc)
+    p = subprocess.run([exe] + [str(a) for a in args], cwd=tmp_path, env=env, capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr[-2000:]
+    return p.stdout
+
+
+def test_reference_examples_relinked_against_libsmmc(S, O, table1127, tmp_path):
+    """the reference's benchmark_mc_gpu / benchmark_mc_gpu_reduceBlock, sources untouched,
+    linked to the product library instead of the reference's src/simulations.cu"""
+    import re
+    exe = os.path.join(ROOT, "oracle", "_ref", "benchmark_mc_gpu")
+    exe_rb = os.path.join(ROOT, "oracle", "_ref", "benchmark_mc_gpu_reduceBlock")
+    if not (os.path.exists(exe) and os.path.exists(exe_rb)):
+        pytest.skip("relinked reference examples did not travel with the snapshot (make -C oracle relink)")
+    N, P = 200_000, 360
+    out = _run_relinked(tmp_path, exe, [1, P, N], table1127)
+    o = O.simulate("bootstrap_compat", N, P, returns=table1127, want_finals=True)
+    mean, std = map(float, re.search(r"mean: ([\d.]+) \| std: ([\d.]+)", out).groups())
+    fin = o.finals.astype(np.float64)
+    # the example's own host statistics (examples/benchmark_mc_gpu.cpp:7-41) over the finals we returned
+    assert abs(mean - fin.mean()) <= 0.02 + 1e-6 * fin.mean() and abs(std - fin.std()) <= 0.02 + 1e-5 * fin.std()
+    below = int(re.search(r"count_below [\d.,]+: ([\d,]+)", out).group(1).replace(",", ""))
+    assert below == int((o.finals < np.float32(1000.0)).sum())
+    out = _run_relinked(tmp_path, exe_rb, [1, P, N], table1127)
+    m = re.search(r"mean: ([\d.]+) \| std: ([\d.]+)", out)
+    assert m, out[-500:]
+    ob = O.simulate("bootstrap_compat", N, P, returns=table1127, want_block_partials=True)
+    # examples/benchmark_mc_gpu_reduceBlock.cpp:7-26: mean of block means, sqrt(mean of block variances)
+    assert abs(float(m.group(1)) - ob.block_means.astype(np.float64).mean()) <= 0.02 + 1e-6 * fin.mean()
