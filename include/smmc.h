@@ -139,6 +139,83 @@ smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float 
 /* out = a + b on the device (reference vector_add_gpu, src/gpu.cu:17-47). Host pointers. */
 smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device);
 
+/* ---- exact order statistics of the finals without writing them to HBM ------------------- */
+
+/* The reference sorts all N finals on the host and reads quartiles off the sorted vector (update_quartiles,
+ * reference examples/visualize_returns_gpu.cpp:83-110: v[0], v[N/4], v[N/2], v[N/4 + N/2], v[N-1]).  Here the
+ * value of rank r (0-based, in ascending order) is found by a radix select over the finals' order-preserving
+ * 32-bit keys in three passes (11 + 11 + 10 key bits).  Every pass REPLAYS the simulation -- the RNG is
+ * counter-based, so a replay reproduces every path bit for bit -- and only builds digit histograms in shared
+ * memory; no per-path value is ever stored.  The result is exactly sorted(finals)[r].
+ *
+ * Pass protocol (this is what a one-process-per-GPU job runs, summing the histograms over ranks in between):
+ *   smmc_select_begin(&st, n, ranks);
+ *   while (st.bits_done < 32) { smmc_select_pass(cfg_of_my_shard, &st, hist); <all-reduce hist>; smmc_select_advance(&st, hist); }
+ *   smmc_select_values(&st, values);
+ * smmc_quantiles() runs the same protocol on n_gpus devices of this process. */
+#define SMMC_SELECT_MAX_TARGETS 8
+#define SMMC_SELECT_BINS 2048
+
+typedef struct smmc_select_state {
+  int32_t n_targets;                          /* 1..SMMC_SELECT_MAX_TARGETS */
+  int32_t bits_done;                          /* key bits resolved so far: 0 -> 11 -> 22 -> 32 */
+  uint64_t rank[SMMC_SELECT_MAX_TARGETS];     /* rank of target t among the keys that share its prefix */
+  uint32_t prefix[SMMC_SELECT_MAX_TARGETS];   /* the top bits_done bits of target t's key */
+} smmc_select_state;
+
+smmc_status smmc_select_begin(smmc_select_state *st, int32_t n_targets, const uint64_t *ranks);
+/* One replay of cfg's paths.  hist: SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS counters, row t = digit histogram
+ * of the keys under target t's prefix (first pass, bits_done == 0: only row 0 is produced and serves every target).
+ * Host pointer by default; with SMMC_FLAG_DEVICE_POINTERS `hist` (and cfg->returns) are device pointers, the call
+ * is asynchronous on cfg->stream and rows >= the number produced are zeroed.  Counters are exact and
+ * SUM-reducible across shards. */
+smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *st, uint64_t *hist);
+/* Consume the (globally summed) HOST histogram of the pass just run: fixes the next 11/11/10 key bits per target. */
+smmc_status smmc_select_advance(smmc_select_state *st, const uint64_t *hist);
+/* After the last pass (bits_done == 32): the order statistics themselves. */
+smmc_status smmc_select_values(const smmc_select_state *st, float *values);
+/* values[t] = sorted(finals)[ranks[t]] of cfg's N paths, sharded over devices 0..n_gpus-1 like smmc_run_multi.
+ * Host pointers.  device_ms (nullable): summed kernel time of the three passes (max over devices per pass). */
+smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_targets, const uint64_t *ranks,
+                           float *values, float *device_ms);
+
+/* ---- trajectory mode ------------------------------------------------------------------- */
+
+/* Full value paths of n_paths paths starting at cfg->stream_offset, from the SAME RNG streams and arithmetic as
+ * the statistics kernel: values[p*(P+1) + 0] = V0, values[p*(P+1) + m + 1] = value after month m, so that
+ * values[p*(P+1) + P] equals finals[p] of smmc_run bit for bit (reference: mc_simulations_keepdata,
+ * src/simulations.cpp:139-202, `mc_data[id] = many_updates(...)`, P+1 values per path).
+ * returns_pct (nullable) [n_paths * P]: the monthly return of each step in PERCENT, the reference's unit
+ * (bootstrap modes: the table entry drawn; Gaussian modes: 100 (g - 1)).  Host pointers; cfg->n_simulations is
+ * ignored. */
+smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *values, float *returns_pct);
+
+/* ---- data-format edges: host code, no device needed ---------------------------------------- */
+
+/* Reads the column named "returns" of a CSV file with a header line (reference read_historical_returns,
+ * src/simulations.cpp:83-93: io::CSVReader<1>, read_header(ignore_extra_column, "returns")).  Two-call pattern:
+ * out == NULL or cap too small still reports the row count in *n_out (status SMMC_ERR_INVALID_ARG if cap was
+ * too small and out != NULL). */
+smmc_status smmc_read_returns_csv(const char *path, float *out, int32_t cap, int32_t *n_out);
+/* Writes one trajectory in the reference's output format (write_data_file, src/helpers.cpp:23-39, read back by
+ * python/plot_returns.py:40):  "Returns,,r0,r1,...,\nValues,v0,v1,...,"  with ostream default float formatting. */
+smmc_status smmc_write_data_file(const char *path, const float *returns, int32_t n_returns, const float *values,
+                                 int32_t n_values);
+
+/* ---- launch planning (host only; used by the tests and for capacity questions) --------------------------------- */
+
+typedef struct smmc_plan {
+  int32_t grid;            /* CTAs (one per SM) */
+  int32_t threads;         /* threads per CTA: 32 x warps, warps chosen to fill the last wave of 256-path blocks */
+  int32_t table_copies;    /* bank-private copies of the return table per entry (32 = conflict-free gather) */
+  int32_t reserved;
+  uint64_t smem_bytes;     /* dynamic shared memory per CTA */
+} smmc_plan;
+/* The launch smmc_run would use for cfg on a device with n_sms SMs and smem_optin bytes of opt-in shared memory
+ * (B200: 148, 232448).  select_targets > 0 plans a select pass.  SMMC_ERR_UNSUPPORTED if the table cannot fit. */
+smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int32_t n_sms, uint64_t smem_optin,
+                             smmc_plan *plan);
+
 /* ---- introspection used by the parity tests (device code paths, tiny outputs) ---------------------------------- */
 
 /* Raw per-month draws of `n_paths` paths starting at cfg->stream_offset, computed ON THE DEVICE with the same

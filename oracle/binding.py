@@ -57,6 +57,12 @@ def load():
     lib.orc_num_threads.restype = C.c_int
     lib.orc_gauss_pairs.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p]
     lib.orc_gauss_pairs.restype = None
+    lib.orc_trajectories.argtypes = [P(N.SmmcConfig), C.c_int32, C.c_void_p, C.c_void_p]
+    lib.orc_trajectories.restype = C.c_int
+    lib.orc_quantiles.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.orc_quantiles.restype = C.c_int
+    lib.orc_quartile_ranks.argtypes = [C.c_int64, C.c_void_p]
+    lib.orc_quartile_ranks.restype = None
     _sobol_keep = np.ascontiguousarray(sobol_directions())
     lib.orc_sobol_set_table(_sobol_keep.ctypes.data, 1111)
     _lib = lib
@@ -100,6 +106,38 @@ def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0):
     if lib.orc_draws(C.byref(cfg), int(n_paths), out.ctypes.data) != 0:
         raise ValueError("oracle rejected the configuration")
     del keep
+    return out
+
+
+def trajectories(mode, n_paths, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False):
+    """Same contract as stock_market_monte_carlo_b200.trajectories, computed by the CPU oracle."""
+    lib = load()
+    cfg, keep = make_config(mode, n_paths, n_periods, initial_capital, returns, seed, stream_offset, gauss_mean,
+                            gauss_std)
+    values = np.zeros((int(n_paths), int(n_periods) + 1), dtype=np.float32)
+    rets = np.zeros((int(n_paths), int(n_periods)), dtype=np.float32) if want_returns else None
+    if lib.orc_trajectories(C.byref(cfg), int(n_paths), values.ctypes.data,
+                            rets.ctypes.data if rets is not None else None) != 0:
+        raise ValueError("oracle rejected the configuration")
+    del keep
+    return (values, rets) if want_returns else values
+
+
+def quartile_ranks(n):
+    r = np.zeros(5, dtype=np.uint64)
+    load().orc_quartile_ranks(int(n), r.ctypes.data)
+    return r
+
+
+def quantiles_of(finals, ranks):
+    """the reference's way (update_quartiles): sort all finals, read the value at each rank"""
+    lib = load()
+    f = np.ascontiguousarray(np.asarray(finals, dtype=np.float32))
+    r = np.ascontiguousarray(np.asarray(ranks, dtype=np.uint64))
+    out = np.zeros(r.size, dtype=np.float32)
+    if lib.orc_quantiles(f.ctypes.data, int(f.size), int(r.size), r.ctypes.data, out.ctypes.data) != 0:
+        raise ValueError("bad ranks")
     return out
 
 
@@ -158,6 +196,35 @@ def ref_gaussian_finals(n, n_periods, initial_capital, mean_pct, std_pct):
     threads = lib.ref_gaussian_finals(int(n), int(n_periods), float(initial_capital), float(mean_pct),
                                       float(std_pct), out.ctypes.data)
     return out, threads
+
+
+def ref_read_historical_returns(path, max_n=1 << 20):
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_read_historical_returns.argtypes = [C.c_char_p, C.c_void_p, C.c_long]
+    lib.ref_read_historical_returns.restype = C.c_long
+    out = np.zeros(int(max_n), dtype=np.float32)
+    n = lib.ref_read_historical_returns(str(path).encode(), out.ctypes.data, int(max_n))
+    return out[:n].copy()
+
+
+def ref_write_data_file(fname, returns, values):
+    """reference write_data_file: writes ./outputs/<fname> under the CURRENT working directory"""
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_write_data_file.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.ref_write_data_file.restype = None
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    v = np.ascontiguousarray(np.asarray(values, dtype=np.float32))
+    lib.ref_write_data_file(str(fname).encode(), r.ctypes.data, int(r.size), v.ctypes.data, int(v.size))
+
+
+def ref_many_updates(fund, returns):
+    lib = ref_lib("libref_cpu.so")
+    lib.ref_many_updates.argtypes = [C.c_float, C.c_void_p, C.c_uint, C.c_void_p]
+    lib.ref_many_updates.restype = None
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    out = np.zeros(r.size + 1, dtype=np.float32)
+    lib.ref_many_updates(float(fund), r.ctypes.data, int(r.size), out.ctypes.data)
+    return out
 
 
 def ref_update_fund(fund, ret):

@@ -83,3 +83,12 @@ long ref_read_historical_returns(const char *path, float *out, long max_n) {
   return n;
 }
 }
+
+// write_data_file (src/helpers.cpp:23-39) writes ./outputs/<fname> relative to the working directory
+#include "stock_market_monte_carlo/helpers.h"
+extern "C" void ref_write_data_file(const char *fname, const float *returns, int n_returns, const float *values,
+                                    int n_values) {
+  QuietStdout q(true);
+  std::vector<float> r(returns, returns + n_returns), v(values, values + n_values);
+  write_data_file(fname, r, v);
+}

@@ -229,17 +229,20 @@ static float normal_icdf(uint32_t x32) { /* returns z / sqrt(2) */
 typedef struct run_consts {
   const smmc_config *cfg;
   const float *tbl; /* returns * 0.01f, with one zero pad entry at [n] (compat one-past-the-end read) */
+  const float *raw; /* the same entries in percent (trajectory mode's returns_pct); sorted like tbl */
   gauss_consts gc;
   float sigma_sqrt2; /* (float)(sqrt(2) * (double)(std * 0.01f)) */
   const uint32_t *shift; /* per-month Sobol digital shift */
 } run_consts;
 
 /* draws[m] (optional) receives the table index (bootstrap modes) or the raw word (gaussian modes) of month m */
-static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws) {
+/* values[0..P] (optional): V0 and the value after every month; rets[m] (optional): that month's return in percent */
+static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *draws, float *values, float *rets) {
   const smmc_config *cfg = rc->cfg;
   const int P = cfg->n_periods;
   const int n = cfg->n_returns;
   float total = cfg->initial_capital;
+  if (values) values[0] = total;
   switch (cfg->mode) {
     case SMMC_MODE_BOOTSTRAP_COMPAT: {
       uint32_t state = orc_rand_pcg((uint32_t)path + 1u + (uint32_t)cfg->seed);
@@ -248,6 +251,8 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
         int32_t idx = orc_compat_index(state, n);
         if (draws) draws[m] = (uint32_t)idx;
         total = fmaf(total, rc->tbl[idx], total); /* total += total * r, one FFMA (reference SASS) */
+        if (values) values[m + 1] = total;
+        if (rets) rets[m] = idx < n ? rc->raw[idx] : 0.0f;
       }
     } break;
     case SMMC_MODE_BOOTSTRAP: {
@@ -258,6 +263,8 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
         uint32_t idx = boot_index(w, j, (uint32_t)n);
         if (draws) draws[m] = idx;
         total = fmaf(total, rc->tbl[idx], total);
+        if (values) values[m + 1] = total;
+        if (rets) rets[m] = rc->raw[idx];
       }
     } break;
     case SMMC_MODE_GAUSSIAN: {
@@ -269,6 +276,8 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
         if ((j & 1) == 0) gauss_pair(w[j >> 1], rc->gc, &g[0], &g[1]);
         if (draws) draws[m] = (j & 1) ? w[j >> 1] * 0x9E3779B1u : (w[j >> 1] & 0xFFFFFu); /* radius field | hashed angle word */
         total = total * g[j & 1];
+        if (values) values[m + 1] = total;
+        if (rets) rets[m] = (g[j & 1] - 1.0f) * 100.0f;
       }
     } break;
     case SMMC_MODE_SOBOL_BOOTSTRAP: {
@@ -277,18 +286,27 @@ static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws)
         uint32_t idx = (uint32_t)(((uint64_t)x * (uint32_t)n) >> 32);
         if (draws) draws[m] = idx;
         total = fmaf(total, rc->tbl[idx], total);
+        if (values) values[m + 1] = total;
+        if (rets) rets[m] = rc->raw[idx];
       }
     } break;
     case SMMC_MODE_SOBOL_GAUSSIAN: {
       for (int m = 0; m < P; m++) {
         uint32_t x = orc_sobol_point(path + SOBOL_SKIP, m) ^ rc->shift[m];
         if (draws) draws[m] = x;
-        total = total * fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
+        float gm = fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
+        total = total * gm;
+        if (values) values[m + 1] = total;
+        if (rets) rets[m] = (gm - 1.0f) * 100.0f;
       }
     } break;
     default: break;
   }
   return total;
+}
+
+static float simulate_path(const run_consts *rc, uint64_t path, uint32_t *draws) {
+  return simulate_path_full(rc, path, draws, NULL, NULL);
 }
 
 /* ------------------------------------------------------------------------------------------------------- */
@@ -491,6 +509,65 @@ int orc_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
   free(shift);
   free(tbl);
   return 0;
+}
+
+/* Same contract as smmc_trajectories: values [n_paths][P+1], returns_pct [n_paths][P] (nullable).  Reference:
+ * mc_simulations_keepdata stores many_updates()'s P+1 values per path (src/simulations.cpp:139-202, :24-39). */
+int orc_trajectories(const smmc_config *cfg, int32_t n_paths, float *values, float *returns_pct) {
+  if (!validate(cfg) || (n_paths > 0 && !values)) return 1;
+  run_consts rc;
+  memset(&rc, 0, sizeof rc);
+  rc.cfg = cfg;
+  const int P = cfg->n_periods;
+  float *tbl = build_table(cfg);
+  rc.tbl = tbl;
+  float *raw = NULL;
+  if (tbl) { /* percent values in the same (possibly sorted) order as tbl */
+    raw = (float *)malloc(((size_t)cfg->n_returns + 1) * sizeof(float));
+    memcpy(raw, cfg->returns, (size_t)cfg->n_returns * sizeof(float));
+    raw[cfg->n_returns] = 0.0f;
+    if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP) qsort(raw, (size_t)cfg->n_returns, sizeof(float), cmp_float);
+  }
+  rc.raw = raw;
+  rc.gc = make_gauss_consts(cfg->gauss_mean, cfg->gauss_std);
+  rc.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)(cfg->gauss_std * 0.01f));
+  uint32_t *shift = (uint32_t *)calloc((size_t)(P > 0 ? P : 1), sizeof(uint32_t));
+  if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
+    for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);
+  rc.shift = shift;
+  for (int32_t p = 0; p < n_paths; p++)
+    simulate_path_full(&rc, cfg->stream_offset + (uint64_t)p, NULL, values + (size_t)p * (P + 1),
+                       returns_pct ? returns_pct + (size_t)p * P : NULL);
+  free(shift);
+  free(raw);
+  free(tbl);
+  return 0;
+}
+
+/* Order statistics the way the reference takes them: fully sort the finals, read the value at each rank
+ * (update_quartiles, examples/visualize_returns_gpu.cpp:83-110: std::sort, then v[0], v[N/4], v[N/2], v[N/4+N/2], v[N-1]). */
+int orc_quantiles(const float *finals, int64_t n, int32_t n_targets, const uint64_t *ranks, float *out) {
+  if (!finals || n <= 0 || !ranks || !out) return 1;
+  float *v = (float *)malloc((size_t)n * sizeof(float));
+  memcpy(v, finals, (size_t)n * sizeof(float));
+  qsort(v, (size_t)n, sizeof(float), cmp_float);
+  int rc = 0;
+  for (int t = 0; t < n_targets; t++) {
+    if (ranks[t] >= (uint64_t)n) { rc = 1; break; }
+    out[t] = v[ranks[t]];
+  }
+  free(v);
+  return rc;
+}
+
+/* ranks of {min, Q1, median, Q3, max} as the reference indexes them (examples/visualize_returns_gpu.cpp:84-86, :109) */
+void orc_quartile_ranks(int64_t n, uint64_t ranks[5]) {
+  int64_t q1 = n / 4, q2 = n / 2, q3 = q1 + q2;
+  ranks[0] = 0;
+  ranks[1] = (uint64_t)q1;
+  ranks[2] = (uint64_t)q2;
+  ranks[3] = (uint64_t)q3;
+  ranks[4] = (uint64_t)(n - 1);
 }
 
 /* host restatements of the two small reference entry points, for their parity tests */

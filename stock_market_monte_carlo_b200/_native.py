@@ -73,6 +73,29 @@ class SmmcResult(C.Structure):
     ]
 
 
+SELECT_MAX_TARGETS = 8
+SELECT_BINS = 2048
+
+
+class SmmcSelectState(C.Structure):
+    _fields_ = [
+        ("n_targets", C.c_int32),
+        ("bits_done", C.c_int32),
+        ("rank", C.c_uint64 * SELECT_MAX_TARGETS),
+        ("prefix", C.c_uint32 * SELECT_MAX_TARGETS),
+    ]
+
+
+class SmmcPlan(C.Structure):
+    _fields_ = [
+        ("grid", C.c_int32),
+        ("threads", C.c_int32),
+        ("table_copies", C.c_int32),
+        ("reserved", C.c_int32),
+        ("smem_bytes", C.c_uint64),
+    ]
+
+
 class SmmcError(RuntimeError):
     def __init__(self, status, message):
         super().__init__(f"{STATUS_NAMES.get(status, status)}: {message}")
@@ -83,6 +106,8 @@ class SmmcError(RuntimeError):
 C_ABI_SYMBOLS = [
     "smmc_run", "smmc_run_multi", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_vector_add",
     "smmc_debug_draws", "smmc_debug_philox", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
+    "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
+    "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
 ]
 
 _lib = None
@@ -118,6 +143,24 @@ def load():
     lib.smmc_debug_philox.restype = C.c_int
     lib.smmc_kernel_times.argtypes = [C.c_int32, C.c_void_p, C.c_int32, P(C.c_int32)]
     lib.smmc_kernel_times.restype = C.c_int
+    lib.smmc_select_begin.argtypes = [P(SmmcSelectState), C.c_int32, C.c_void_p]
+    lib.smmc_select_begin.restype = C.c_int
+    lib.smmc_select_pass.argtypes = [P(SmmcConfig), P(SmmcSelectState), C.c_void_p]
+    lib.smmc_select_pass.restype = C.c_int
+    lib.smmc_select_advance.argtypes = [P(SmmcSelectState), C.c_void_p]
+    lib.smmc_select_advance.restype = C.c_int
+    lib.smmc_select_values.argtypes = [P(SmmcSelectState), C.c_void_p]
+    lib.smmc_select_values.restype = C.c_int
+    lib.smmc_quantiles.argtypes = [P(SmmcConfig), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, P(C.c_float)]
+    lib.smmc_quantiles.restype = C.c_int
+    lib.smmc_trajectories.argtypes = [P(SmmcConfig), C.c_int32, C.c_void_p, C.c_void_p]
+    lib.smmc_trajectories.restype = C.c_int
+    lib.smmc_read_returns_csv.argtypes = [C.c_char_p, C.c_void_p, C.c_int32, P(C.c_int32)]
+    lib.smmc_read_returns_csv.restype = C.c_int
+    lib.smmc_write_data_file.argtypes = [C.c_char_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.smmc_write_data_file.restype = C.c_int
+    lib.smmc_plan_launch.argtypes = [P(SmmcConfig), C.c_int32, C.c_int32, C.c_uint64, P(SmmcPlan)]
+    lib.smmc_plan_launch.restype = C.c_int
     lib.smmc_last_error.restype = C.c_char_p
     lib.smmc_version.restype = C.c_char_p
     lib.smmc_device_count.restype = C.c_int32

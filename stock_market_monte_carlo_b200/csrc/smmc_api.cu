@@ -32,6 +32,21 @@ smmc_status fail(smmc_status st, const char *fmt, ...) {
   return st;
 }
 
+}  // namespace
+
+namespace smmc {
+// error reporting for the other translation units of the library (smmc_io.cpp)
+smmc_status set_error(smmc_status st, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return st;
+}
+}  // namespace smmc
+
+namespace {
+
 #define CU(call)                                                                                       \
   do {                                                                                                 \
     cudaError_t e__ = (call);                                                                          \
@@ -70,7 +85,7 @@ struct Context {
   // ring of event pairs around the simulation kernel of the last kEventRing launches (smmc_kernel_times)
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
-  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift;
+  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift, selhist;
   int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
   uint64_t sobol_seed = 0;
   bool sobol_full_ready = false;
@@ -167,6 +182,10 @@ int variant_from_env() {
   const char *v = getenv("SMMC_ILP");
   return v ? atoi(v) : 0;
 }
+int warps_from_env() {  // development knob: force the warps per CTA (0 = plan_warps)
+  const char *v = getenv("SMMC_WARPS");
+  return v ? atoi(v) : 0;
+}
 
 smmc::PhiloxKeys make_keys(uint64_t seed) {
   smmc::PhiloxKeys k;
@@ -178,6 +197,27 @@ smmc::PhiloxKeys make_keys(uint64_t seed) {
     k1 += smmc::kPhiloxW1;
   }
   return k;
+}
+
+// the RNG-stream / arithmetic constants of a config (shared by the introspection and trajectory kernels; enqueue()
+// sets the same fields for the simulation kernel)
+void fill_stream_params(const smmc_config *cfg, smmc::KParams *p) {
+  p->path0 = cfg->stream_offset;
+  p->n_periods = cfg->n_periods;
+  p->n_returns = cfg->n_returns;
+  p->compat_seed = (uint32_t)cfg->seed;
+  p->keys = make_keys(cfg->seed);
+  const float mu = cfg->gauss_mean * 0.01f, sigma = cfg->gauss_std * 0.01f;
+  p->gc.a = 1.0f + mu;
+  p->gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
+  p->sigma_sqrt2 = (float)(1.41421356237309504880 * (double)sigma);
+  p->one = 0x3F800000u;
+  p->v0 = cfg->initial_capital;
+  p->idx_scale = (float)cfg->n_returns * 2.3283064365386963e-10f;  // exact: n < 2^24
+  p->bc.c21 = (float)(4 * cfg->n_returns);                          // exact: n < 2^21 (validated)
+  p->bc.k21 = (float)(8388608 - 4 * cfg->n_returns);
+  p->bc.c22 = (float)(2 * cfg->n_returns);
+  p->bc.k22 = (float)(8388608 - 2 * cfg->n_returns);
 }
 
 // host Philox4x32-10 (only for the per-month Sobol digital shift; same counter layout as the device stream)
@@ -239,6 +279,54 @@ smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream
   return SMMC_OK;
 }
 
+// Full [dims][32] direction-number table + per-month digital shift on the device (plain Gray-code evaluation:
+// debug_draws, trajectories).  Uses ctx->stream; synchronises it.
+smmc_status prepare_sobol_full(Context *ctx, int n_periods, uint64_t seed, const uint32_t **full_dev,
+                               const uint32_t **shift_dev) {
+  const int dims = smmc::sobol_table_dims();
+  if (n_periods > dims) return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support at most %d periods", dims);
+  if (!ctx->sobol_full_ready) {
+    CU(ctx->sobol_full.reserve((size_t)dims * 32 * 4));
+    CU(cudaMemcpyAsync(ctx->sobol_full.p, smmc::sobol_table(), (size_t)dims * 32 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->sobol_full_ready = true;
+  }
+  std::vector<uint32_t> shift((size_t)(n_periods > 0 ? n_periods : 1), 0u);
+  for (int m = 0; m < n_periods; m++) shift[m] = sobol_shift_host(m, seed);
+  CU(ctx->sobol_shift.reserve(shift.size() * 4));
+  CU(cudaMemcpyAsync(ctx->sobol_shift.p, shift.data(), shift.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *full_dev = (const uint32_t *)ctx->sobol_full.p;
+  *shift_dev = (const uint32_t *)ctx->sobol_shift.p;
+  return SMMC_OK;
+}
+
+// one radix-select pass over the finals' ordered keys (smmc_select_pass / smmc_quantiles)
+struct SelectPass {
+  int targets = 0;       // histograms kept by the kernel (1 in the first pass)
+  int digit_shift = 0;
+  uint32_t digit_mask = 0;
+  int prefix_shift = 32;
+  uint32_t prefix[SMMC_SELECT_MAX_TARGETS] = {};
+  unsigned long long *hist_dev = nullptr;  // caller's device buffer (DEVICE_POINTERS) or null = library workspace
+};
+
+// digit width of the pass that starts with `bits_done` key bits known: 11, 11, 10
+int select_width(int bits_done) { return bits_done >= 22 ? 10 : 11; }
+
+smmc_status make_select_pass(const smmc_select_state *st, SelectPass *sp) {
+  if (!st || st->n_targets < 1 || st->n_targets > SMMC_SELECT_MAX_TARGETS)
+    return fail(SMMC_ERR_INVALID_ARG, "select: n_targets must be in [1,%d]", SMMC_SELECT_MAX_TARGETS);
+  if (st->bits_done != 0 && st->bits_done != 11 && st->bits_done != 22)
+    return fail(SMMC_ERR_INVALID_ARG, "select: no pass left (bits_done = %d)", st->bits_done);
+  const int w = select_width(st->bits_done);
+  sp->targets = st->bits_done == 0 ? 1 : st->n_targets;
+  sp->digit_shift = 32 - st->bits_done - w;
+  sp->digit_mask = (1u << w) - 1u;
+  sp->prefix_shift = 32 - st->bits_done;
+  for (int t = 0; t < SMMC_SELECT_MAX_TARGETS; t++) sp->prefix[t] = t < st->n_targets && st->bits_done ? st->prefix[t] : 0u;
+  return SMMC_OK;
+}
+
 // everything a launched shard needs to be collected later
 struct Pending {
   Context *ctx = nullptr;
@@ -249,12 +337,15 @@ struct Pending {
   bool device_ptrs = false;
   float *finals_dev = nullptr, *bmeans_dev = nullptr, *bvars_dev = nullptr;
   double *stats_dev = nullptr;
+  unsigned long long *sel_dev = nullptr;
+  int sel_words = 0;
   int launches = 0;
   int ev_slot = 0;
 };
 
 // Enqueue one shard [cfg->stream_offset, +N) on cfg->device.  Caller holds ctx->mu.
-smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx, Pending *pd) {
+smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx, Pending *pd,
+                    const SelectPass *sel = nullptr) {
   CU(cudaSetDevice(ctx->device));
   const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
   cudaStream_t st = devp ? (cudaStream_t)cfg->stream : ctx->stream;
@@ -265,7 +356,8 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   const int variant = variant_from_env();
 
   smmc::LaunchInfo li;
-  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, ctx->n_sms, ctx->smem_optin, variant, &li))
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, N, ctx->n_sms, ctx->smem_optin,
+                         warps_from_env(), &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %zu bytes of shared memory", cfg->n_returns, ctx->smem_optin);
 
   smmc::KParams p;
@@ -366,6 +458,26 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   if (is_sobol(cfg->mode)) {
     smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p);
     if (sst != SMMC_OK) return sst;
+  }
+
+  pd->sel_dev = nullptr;
+  pd->sel_words = 0;
+  if (sel && sel->targets > 0) {
+    const size_t sel_bytes = (size_t)sel->targets * SMMC_SELECT_BINS * sizeof(unsigned long long);
+    unsigned long long *hd = sel->hist_dev;
+    if (!hd) {
+      CU(ctx->selhist.reserve(sel_bytes));
+      hd = (unsigned long long *)ctx->selhist.p;
+    }
+    CU(cudaMemsetAsync(hd, 0, sel_bytes, st));
+    p.sel_targets = sel->targets;
+    p.sel_digit_shift = sel->digit_shift;
+    p.sel_digit_mask = sel->digit_mask;
+    p.sel_prefix_shift = sel->prefix_shift;
+    for (int t = 0; t < SMMC_SELECT_MAX_TARGETS; t++) p.sel_prefix[t] = sel->prefix[t];
+    p.sel_hist_g = hd;
+    pd->sel_dev = hd;
+    pd->sel_words = sel->targets * SMMC_SELECT_BINS;
   }
 
   const int slot = (int)(ctx->ev_head % kEventRing);
@@ -564,6 +676,249 @@ smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t 
   return SMMC_OK;
 }
 
+// ---- exact order statistics by replay (radix select) ------------------------------------------------------------
+
+smmc_status smmc_select_begin(smmc_select_state *st, int32_t n_targets, const uint64_t *ranks) {
+  if (!st || !ranks || n_targets < 1 || n_targets > SMMC_SELECT_MAX_TARGETS)
+    return fail(SMMC_ERR_INVALID_ARG, "select_begin: n_targets must be in [1,%d]", SMMC_SELECT_MAX_TARGETS);
+  memset(st, 0, sizeof *st);
+  st->n_targets = n_targets;
+  for (int t = 0; t < n_targets; t++) st->rank[t] = ranks[t];
+  return SMMC_OK;
+}
+
+smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *sst, uint64_t *hist) {
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  if (!hist) return fail(SMMC_ERR_INVALID_ARG, "select_pass: null histogram");
+  smmc_config c2;
+  if (cfg) {
+    c2 = *cfg;
+    c2.hist_bins = 0;
+    c2.flags &= ~SMMC_FLAG_NO_SYNC;  // validated below without the stats_dev requirement
+  }
+  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
+  if (st != SMMC_OK) return st;
+  SelectPass sp;
+  st = make_select_pass(sst, &sp);
+  if (st != SMMC_OK) return st;
+  Context *ctx = nullptr;
+  st = get_context(cfg->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
+  const size_t all_bytes = (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS * sizeof(uint64_t);
+  Pending pd;
+  if (devp) {
+    CU(cudaSetDevice(cfg->device));
+    CU(cudaMemsetAsync(hist, 0, all_bytes, (cudaStream_t)cfg->stream));
+    sp.hist_dev = (unsigned long long *)hist;
+    return enqueue(&c2, &dummy, ctx, &pd, &sp);  // asynchronous on cfg->stream
+  }
+  st = enqueue(&c2, &dummy, ctx, &pd, &sp);
+  if (st != SMMC_OK) return st;
+  memset(hist, 0, all_bytes);
+  CU(cudaMemcpyAsync(hist, pd.sel_dev, (size_t)pd.sel_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, pd.stream));
+  CU(cudaStreamSynchronize(pd.stream));
+  return SMMC_OK;
+}
+
+smmc_status smmc_select_advance(smmc_select_state *st, const uint64_t *hist) {
+  if (!st || !hist) return fail(SMMC_ERR_INVALID_ARG, "select_advance: null argument");
+  SelectPass sp;
+  smmc_status rc = make_select_pass(st, &sp);
+  if (rc != SMMC_OK) return rc;
+  const int w = select_width(st->bits_done);
+  const int bins = 1 << w;
+  for (int t = 0; t < st->n_targets; t++) {
+    const uint64_t *h = hist + (size_t)(st->bits_done == 0 ? 0 : t) * SMMC_SELECT_BINS;
+    uint64_t cum = 0;
+    int b = 0;
+    for (; b < bins; b++) {
+      if (cum + h[b] > st->rank[t]) break;
+      cum += h[b];
+    }
+    if (b == bins) return fail(SMMC_ERR_INVALID_ARG, "select_advance: rank of target %d is beyond the number of paths", t);
+    st->rank[t] -= cum;
+    st->prefix[t] = (st->prefix[t] << w) | (uint32_t)b;
+  }
+  st->bits_done += w;
+  return SMMC_OK;
+}
+
+smmc_status smmc_select_values(const smmc_select_state *st, float *values) {
+  if (!st || !values) return fail(SMMC_ERR_INVALID_ARG, "select_values: null argument");
+  if (st->bits_done != 32) return fail(SMMC_ERR_INVALID_ARG, "select_values: %d of 32 key bits resolved", st->bits_done);
+  for (int t = 0; t < st->n_targets; t++) {
+    const uint32_t key = st->prefix[t];
+    const uint32_t bits = (key & 0x80000000u) ? (key ^ 0x80000000u) : ~key;  // inverse of smmc::ordered_key
+    memcpy(&values[t], &bits, 4);
+  }
+  return SMMC_OK;
+}
+
+smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_targets, const uint64_t *ranks,
+                           float *values, float *device_ms) {
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  smmc_status st = validate(cfg, &dummy);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "smmc_quantiles takes host pointers");
+  if (!values) return fail(SMMC_ERR_INVALID_ARG, "quantiles: null output");
+  smmc_select_state sel;
+  st = smmc_select_begin(&sel, n_targets, ranks);
+  if (st != SMMC_OK) return st;
+  for (int t = 0; t < n_targets; t++)
+    if (ranks[t] >= (uint64_t)cfg->n_simulations)
+      return fail(SMMC_ERR_INVALID_ARG, "quantiles: rank %llu >= n_simulations", (unsigned long long)ranks[t]);
+  const int ndev = probe_devices();
+  if (ndev <= 0) return fail(SMMC_ERR_NO_DEVICE, "no CUDA device of compute capability 10.x (sm_100a) is visible; this library has no CPU fallback");
+  if (n_gpus < 1 || n_gpus > ndev) return fail(SMMC_ERR_INVALID_ARG, "n_gpus %d out of range [1,%d]", n_gpus, ndev);
+
+  const int64_t N = cfg->n_simulations;
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int64_t per = (nb + n_gpus - 1) / n_gpus;
+  std::vector<Context *> ctxs((size_t)n_gpus, nullptr);
+  for (int g = 0; g < n_gpus; g++) {
+    st = get_context(g == 0 && n_gpus == 1 ? cfg->device : g, &ctxs[g]);
+    if (st != SMMC_OK) return st;
+  }
+  const size_t words = (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS;
+  std::vector<uint64_t> total(words), part(words);
+  float ms_total = 0.0f;
+  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.lock();
+  smmc_status rc = SMMC_OK;
+  while (rc == SMMC_OK && sel.bits_done < 32) {
+    SelectPass sp;
+    rc = make_select_pass(&sel, &sp);
+    std::vector<Pending> pend((size_t)n_gpus);
+    int launched = 0;
+    for (int g = 0; g < n_gpus && rc == SMMC_OK; g++) {
+      int64_t b0 = per * g, b1 = per * (g + 1);
+      if (b0 > nb) b0 = nb;
+      if (b1 > nb) b1 = nb;
+      int64_t p1 = b1 * SMMC_BLOCK;
+      if (p1 > N) p1 = N;
+      smmc_config c2 = *cfg;
+      c2.hist_bins = 0;
+      c2.device = ctxs[g]->device;
+      c2.stream_offset = cfg->stream_offset + (uint64_t)(b0 * SMMC_BLOCK);
+      c2.n_simulations = p1 - b0 * SMMC_BLOCK;
+      rc = enqueue(&c2, &dummy, ctxs[g], &pend[g], &sp);
+      if (rc == SMMC_OK) launched++;
+    }
+    std::fill(total.begin(), total.end(), 0ull);
+    float ms_pass = 0.0f;
+    for (int g = 0; g < launched; g++) {
+      const Pending &pd = pend[g];
+      cudaError_t e = cudaSetDevice(pd.ctx->device);
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(part.data(), pd.sel_dev, (size_t)pd.sel_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, pd.stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(pd.stream);
+      float ms = 0.0f;
+      if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, pd.ctx->ev0[pd.ev_slot], pd.ctx->ev1[pd.ev_slot]);
+      if (e != cudaSuccess) {
+        if (rc == SMMC_OK) rc = fail(SMMC_ERR_CUDA, "quantiles: %s", cudaGetErrorString(e));
+        continue;
+      }
+      for (int i = 0; i < pd.sel_words; i++) total[i] += part[i];
+      if (ms > ms_pass) ms_pass = ms;
+    }
+    ms_total += ms_pass;
+    if (rc == SMMC_OK) rc = smmc_select_advance(&sel, total.data());
+  }
+  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.unlock();
+  if (rc != SMMC_OK) return rc;
+  if (device_ms) *device_ms = ms_total;
+  return smmc_select_values(&sel, values);
+}
+
+// ---- trajectory mode -----------------------------------------------------------------------------------------------
+
+smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *values, float *returns_pct) {
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  smmc_config c2;
+  if (cfg) {
+    c2 = *cfg;
+    c2.n_simulations = n_paths;  // range checks (32-bit path ids, Sobol point indices) apply to the paths asked for
+    c2.hist_bins = 0;
+  }
+  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "trajectories takes host pointers");
+  if (n_paths < 0 || (n_paths > 0 && !values)) return fail(SMMC_ERR_INVALID_ARG, "trajectories: bad arguments");
+  Context *ctx = nullptr;
+  st = get_context(cfg->device, &ctx);
+  if (st != SMMC_OK) return st;
+  if (n_paths == 0) return SMMC_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(cfg->device));
+  cudaStream_t s = ctx->stream;
+  const int P = cfg->n_periods, n = cfg->n_returns;
+  smmc::KParams p;
+  memset(&p, 0, sizeof p);
+  fill_stream_params(cfg, &p);
+  const float *tbl = nullptr, *raw = nullptr;
+  if (is_bootstrap(cfg->mode)) {
+    CU(ctx->returns.reserve((size_t)n * 4));
+    CU(cudaMemcpyAsync(ctx->returns.p, cfg->returns, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    raw = (const float *)ctx->returns.p;
+    if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP) {
+      CU(ctx->sorted.reserve((size_t)n * 4));
+      smmc::launch_sort_table(raw, n, (float *)ctx->sorted.p, s);
+      CU(cudaGetLastError());
+      raw = (const float *)ctx->sorted.p;
+    }
+    const uint32_t tbl_floats = (uint32_t)((n + 1 + 3) & ~3);
+    CU(ctx->tbl.reserve((size_t)tbl_floats * 4));
+    smmc::launch_prep_table(raw, n, 1, (float *)ctx->tbl.p, tbl_floats, s);
+    CU(cudaGetLastError());
+    tbl = (const float *)ctx->tbl.p;
+  }
+  const uint32_t *full_dev = nullptr, *shift_dev = nullptr;
+  if (is_sobol(cfg->mode)) {
+    st = prepare_sobol_full(ctx, P, cfg->seed, &full_dev, &shift_dev);
+    if (st != SMMC_OK) return st;
+  }
+  const size_t vbytes = (size_t)n_paths * (size_t)(P + 1) * 4, rbytes = returns_pct ? (size_t)n_paths * (size_t)P * 4 : 0;
+  CU(ctx->scratch.reserve(vbytes + rbytes + 16));
+  float *vd = (float *)ctx->scratch.p, *rd = rbytes ? vd + (size_t)n_paths * (P + 1) : nullptr;
+  CU(smmc::launch_trajectories(cfg->mode, p, n_paths, tbl, raw, full_dev, shift_dev, vd, rd, s));
+  CU(cudaMemcpyAsync(values, vd, vbytes, cudaMemcpyDeviceToHost, s));
+  if (rbytes) CU(cudaMemcpyAsync(returns_pct, rd, rbytes, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return SMMC_OK;
+}
+
+// ---- launch planning -------------------------------------------------------------------------------------------------
+
+smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int32_t n_sms, uint64_t smem_optin,
+                             smmc_plan *plan) {
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  smmc_config c2;
+  if (cfg) {
+    c2 = *cfg;
+    if (!c2.returns && c2.n_returns > 0) c2.returns = (const float *)(uintptr_t)16;  // planning never reads the table
+  }
+  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
+  if (st != SMMC_OK) return st;
+  if (!plan || n_sms < 1 || select_targets < 0 || select_targets > SMMC_SELECT_MAX_TARGETS)
+    return fail(SMMC_ERR_INVALID_ARG, "plan_launch: bad arguments");
+  smmc::LaunchInfo li;
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, cfg->n_simulations, n_sms,
+                         (size_t)smem_optin, warps_from_env(), &li))
+    return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %llu bytes of shared memory", cfg->n_returns,
+                (unsigned long long)smem_optin);
+  plan->grid = li.grid;
+  plan->threads = li.threads;
+  plan->table_copies = li.rep;
+  plan->reserved = 0;
+  plan->smem_bytes = li.smem_bytes;
+  return SMMC_OK;
+}
+
 smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
@@ -578,35 +933,14 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
   CU(cudaSetDevice(cfg->device));
   smmc::KParams p;
   memset(&p, 0, sizeof p);
-  p.path0 = cfg->stream_offset;
-  p.n_periods = cfg->n_periods;
-  p.n_returns = cfg->n_returns;
-  p.compat_seed = (uint32_t)cfg->seed;
-  p.keys = make_keys(cfg->seed);
-  p.idx_scale = (float)cfg->n_returns * 2.3283064365386963e-10f;
-  p.one = 0x3F800000u;
-  p.bc.c21 = (float)(4 * cfg->n_returns);
-  p.bc.k21 = (float)(8388608 - 4 * cfg->n_returns);
-  p.bc.c22 = (float)(2 * cfg->n_returns);
-  p.bc.k22 = (float)(8388608 - 2 * cfg->n_returns);
+  fill_stream_params(cfg, &p);
   const size_t bytes = (size_t)n_paths * (size_t)cfg->n_periods * 4;
   if (bytes == 0) return SMMC_OK;
   CU(ctx->scratch.reserve(bytes));
   const uint32_t *full_dev = nullptr, *shift_dev = nullptr;
   if (is_sobol(cfg->mode)) {
-    const int dims = smmc::sobol_table_dims();
-    if (!ctx->sobol_full_ready) {
-      CU(ctx->sobol_full.reserve((size_t)dims * 32 * 4));
-      CU(cudaMemcpyAsync(ctx->sobol_full.p, smmc::sobol_table(), (size_t)dims * 32 * 4, cudaMemcpyHostToDevice, ctx->stream));
-      ctx->sobol_full_ready = true;
-    }
-    std::vector<uint32_t> shift((size_t)cfg->n_periods);
-    for (int m = 0; m < cfg->n_periods; m++) shift[m] = sobol_shift_host(m, cfg->seed);
-    CU(ctx->sobol_shift.reserve(shift.size() * 4));
-    CU(cudaMemcpyAsync(ctx->sobol_shift.p, shift.data(), shift.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    full_dev = (const uint32_t *)ctx->sobol_full.p;
-    shift_dev = (const uint32_t *)ctx->sobol_shift.p;
+    st = prepare_sobol_full(ctx, cfg->n_periods, cfg->seed, &full_dev, &shift_dev);
+    if (st != SMMC_OK) return st;
   }
   CU(smmc::launch_debug_draws(cfg->mode, p, n_paths, full_dev, shift_dev, (uint32_t *)ctx->scratch.p, ctx->stream));
   CU(cudaMemcpyAsync(outbuf, ctx->scratch.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -674,6 +1008,7 @@ void smmc_shutdown(void) {
     c.bmeans.release();
     c.bvars.release();
     c.scratch.release();
+    c.selhist.release();
     if (c.stats_host) cudaFreeHost(c.stats_host);
     c.stats_host = nullptr;
     c.stats_host_cap = 0;

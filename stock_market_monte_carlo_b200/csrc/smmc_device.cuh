@@ -4,6 +4,7 @@
 // citations (/root/reference) are given per function.
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <cuda_runtime.h>
 
 namespace smmc {
@@ -212,6 +213,18 @@ __device__ __forceinline__ int hist_bin(float x, float lo, float inv_w, int bins
   if (!(t >= 0.0f)) return 0;
   if (t >= (float)bins) return bins + 1;
   return 1 + (int)t;
+}
+
+// ---- order-preserving key of a float (radix select over the finals) -------------------------------------------
+// key(a) < key(b)  <=>  a < b for all non-NaN floats (-0 sorts just below +0); the inverse is key_to_float.
+__host__ __device__ __forceinline__ uint32_t ordered_key(float x) {
+#ifdef __CUDA_ARCH__
+  const uint32_t b = __float_as_uint(x);
+#else
+  uint32_t b;
+  memcpy(&b, &x, 4);
+#endif
+  return b ^ ((b & 0x80000000u) ? 0xFFFFFFFFu : 0x80000000u);
 }
 
 // ---- TMA bulk copy + mbarrier (table staging) ----------------------------------------------------------------

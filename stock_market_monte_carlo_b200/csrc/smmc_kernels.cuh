@@ -8,6 +8,9 @@
 
 namespace smmc {
 
+constexpr int kSelectMaxTargets = 8;  // = SMMC_SELECT_MAX_TARGETS
+constexpr int kSelectBins = 2048;      // = SMMC_SELECT_BINS (11-bit digits: 11 + 11 + 10 bits = 3 passes)
+
 struct KParams {
   int64_t n_paths;       // N of this launch
   uint64_t path0;        // global id of path 0 (multiple of 256)
@@ -44,7 +47,36 @@ struct KParams {
                              //              row 24: bit 7 again; row 25: digital shift per month (0 = plain)
   int32_t sobol_ppad;        // P rounded up to a multiple of 32
   uint32_t sobol_lo_bytes;   // P_pad * 32
+  // order-statistic search pass (smmc_select_pass): a radix-select digit histogram of the finals' ordered keys,
+  // restricted per target to the key prefix found so far.  sel_targets == 0: not a search pass.
+  int32_t sel_targets;          // histograms kept (1 in the first pass: no prefix yet)
+  int32_t sel_digit_shift;      // digit = (key >> sel_digit_shift) & sel_digit_mask
+  uint32_t sel_digit_mask;      // bins - 1
+  int32_t sel_prefix_shift;     // prefix = key >> sel_prefix_shift; 32 = first pass (every key matches)
+  uint32_t sel_prefix[kSelectMaxTargets];
+  unsigned long long *sel_hist_g;  // [sel_targets][bins], zeroed before launch
 };
+
+// CTA shape of the simulation kernel and its dynamic shared-memory layout (shared by the planner and the kernel)
+constexpr int kThreads = 1024;
+constexpr int kWarps = kThreads / 32;
+
+// shared memory layout (dynamic):
+// [0,8) mbarrier | [16, 16+8*(bins+2)) histogram | warp partials | select-pass digit histograms (u32) |
+// Sobol low direction numbers | table (128-B aligned)
+struct SmemLayout {
+  uint32_t hist_off, wp_off, sel_off, sob_off, tbl_off, total;
+};
+__host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, uint32_t sob_bytes, uint32_t tbl_bytes) {
+  SmemLayout L;
+  L.hist_off = 16;
+  L.wp_off = L.hist_off + 8u * (uint32_t)(bins + 2);
+  L.sel_off = (L.wp_off + 32u * kWarps + 15u) & ~15u;
+  L.sob_off = (L.sel_off + sel_bytes + 127u) & ~127u;
+  L.tbl_off = (L.sob_off + sob_bytes + 127u) & ~127u;
+  L.total = L.tbl_off + tbl_bytes;
+  return L;
+}
 
 constexpr uint32_t kSobolSkip = 256;  // first Sobol point used; keeps 256-path blocks aligned to 256-point blocks
 
@@ -56,8 +88,9 @@ struct LaunchInfo {
 };
 
 // Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
-bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int n_sms, size_t smem_optin, int variant,
-                 LaunchInfo *li);
+// Also picks the warps per CTA for `n_paths` (warps_override in 1..32 forces it; 0 = automatic).
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, int64_t n_paths, int n_sms,
+                 size_t smem_optin, int warps_override, LaunchInfo *li);
 
 // Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
 void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);
@@ -70,6 +103,10 @@ cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int vari
 // sobol_full: [n_dims][32] direction numbers (device), only read in the Sobol modes
 cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, const uint32_t *sobol_full,
                                const uint32_t *shift, uint32_t *out_dev, cudaStream_t s);
+// trajectory mode: values_dev [n_paths][P+1], rets_dev [n_paths][P] (nullable); tbl/raw: [n+1] scaled / percent
+cudaError_t launch_trajectories(int mode, const KParams &p, int n_paths, const float *tbl, const float *raw,
+                                const uint32_t *sobol_full, const uint32_t *shift, float *values_dev, float *rets_dev,
+                                cudaStream_t s);
 cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n, uint32_t *out_dev, cudaStream_t s);
 
 // small reference entry points

@@ -1,0 +1,440 @@
+// smmc_mc_kernel.cuh -- the fused persistent Monte Carlo kernel (template) shared by the per-mode translation units
+// smmc_mc_{compat,bootstrap,gaussian,sobol}.cu (split so that the modes compile in parallel).
+//
+// Replaces the reference kernels mc_simulations_gpu_kernel / mc_simulations_gpu_kernel_reduceBlock
+// (reference src/simulations.cu:112-247) with ONE persistent fused kernel per RNG mode:
+//   * one CTA per SM, the return table staged once per CTA into shared memory by a TMA bulk copy (UBLKCP),
+//     replicated 32x so that lane l only ever reads bank l (no bank conflicts on the random gather);
+//   * one warp owns one logical 256-path block (lane l holds paths 32*j + l, j < 8): the compounding runs in
+//     registers, the per-block mean / variance of the reference's reduceBlock layout is a pure warp-shuffle
+//     reduction that reproduces the reference's reduction tree bit for bit;
+//   * (count, mean, M2), the below-target count and a shared-memory privatised histogram are merged
+//     warp -> CTA -> grid inside the same kernel (last-CTA-done ticket), so per-path data only touches HBM
+//     when the caller asks for `finals`.
+#pragma once
+#include "smmc_kernels.cuh"
+
+#include "../../include/smmc.h"
+
+namespace smmc {
+
+namespace {
+
+// ---- (n, mean, M2) merge, Chan/Golub/LeVeque ------------------------------------------------------------------
+struct Moments {
+  double n, mean, m2;
+};
+__device__ __forceinline__ void merge(Moments &a, double nb, double meanb, double m2b) {
+  if (nb == 0.0) return;
+  const double tot = a.n + nb;
+  const double delta = meanb - a.mean;
+  a.mean += delta * (nb / tot);
+  a.m2 += m2b + delta * delta * (a.n * nb / tot);
+  a.n = tot;
+}
+
+// the reference's 256-slot reduction tree (src/simulations.cu:157-183) on values held 8 per lane (slot 32*j+lane):
+// strides 128, 64, 32 are lane-local adds, strides 16..1 are shuffles; lane 0's association order is the reference's.
+__device__ __forceinline__ float tree_sum_256(const float (&s)[8]) {
+  const float y0 = __fadd_rn(s[0], s[4]), y1 = __fadd_rn(s[1], s[5]);
+  const float y2 = __fadd_rn(s[2], s[6]), y3 = __fadd_rn(s[3], s[7]);
+  const float z0 = __fadd_rn(y0, y2), z1 = __fadd_rn(y1, y3);
+  float w = __fadd_rn(z0, z1);
+#pragma unroll
+  for (int st = 16; st >= 1; st >>= 1) w = __fadd_rn(w, __shfl_down_sync(0xffffffffu, w, st));
+  return __shfl_sync(0xffffffffu, w, 0);
+}
+
+// ---- one sub-batch of ILP paths through all P months ------------------------------------------------------------
+
+template <int ILP>
+__device__ __forceinline__ void run_compat(const KParams &p, const char *tbl, uint32_t lane_off, const uint32_t (&plo)[ILP],
+                                           float (&tot)[ILP]) {
+  uint32_t st[ILP];
+#pragma unroll
+  for (int i = 0; i < ILP; i++) st[i] = rand_pcg(plo[i] + 1u + p.compat_seed);
+  const float scale = p.idx_scale;
+  const uint32_t rep4 = p.rep4;
+#pragma unroll 4
+  for (int m = 0; m < p.n_periods; m++) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      st[i] = xorshift(st[i]);
+      // reference: idx = n * (state * 2^-32f), truncated (src/simulations.cu:148); one rounding either way
+      const int idx = (int)(__uint2float_rn(st[i]) * scale);
+      const float r = *reinterpret_cast<const float *>(tbl + (uint32_t)idx * rep4 + lane_off);
+      tot[i] = fmaf(tot[i], r, tot[i]);  // total += total * r (one FFMA, as the reference compiles)
+    }
+  }
+}
+
+__device__ __forceinline__ float boot_step(float tot, uint32_t w, const char *tbl, uint32_t nr4, uint32_t row_mask,
+                                           uint32_t lane_off) {
+  const uint32_t off = (__umulhi(w, nr4) & row_mask) | lane_off;  // (idx * rep + lane%rep) * 4, idx = mulhi(w, n)
+  const float r = *reinterpret_cast<const float *>(tbl + off);
+  return fmaf(tot, r, tot);
+}
+
+// months 6q..6q+5 of ILP paths: one Philox call each, six table gathers, six FFMAs
+template <int ILP, int SHIFT>
+__device__ __forceinline__ void run_bootstrap(const KParams &p, uint32_t base, const uint32_t (&plo)[ILP],
+                                              uint32_t phi, float (&tot)[ILP]) {
+  const BootConsts bc = p.bc;
+  const uint32_t one = p.one;
+  const int nq = p.n_periods / kFieldsPerCall;
+#pragma unroll 1
+  for (int q = 0; q < nq; q++) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      uint32_t w[4], m[6];
+      stream_words(plo[i], phi, (uint32_t)q, kTagBootstrap, p.keys, w);
+      field_mantissas(w, one, m);
+#pragma unroll
+      for (int j = 0; j < 6; j++) {
+        const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
+        tot[i] = fmaf(tot[i], r, tot[i]);
+      }
+    }
+  }
+  const int rem = p.n_periods - nq * kFieldsPerCall;
+  if (rem) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      uint32_t w[4], m[6];
+      stream_words(plo[i], phi, (uint32_t)nq, kTagBootstrap, p.keys, w);
+      field_mantissas(w, one, m);
+#pragma unroll
+      for (int j = 0; j < 5; j++)
+        if (j < rem) {
+          const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
+          tot[i] = fmaf(tot[i], r, tot[i]);
+        }
+    }
+  }
+}
+
+// months 8q..8q+7 of ILP paths: one Philox call each, four Box-Muller pairs
+template <int ILP>
+__device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&plo)[ILP], uint32_t phi,
+                                             float (&tot)[ILP]) {
+  const GaussConsts gc = p.gc;
+  const uint32_t one = p.one;
+  const int nq = p.n_periods / kGaussMonthsPerCall;
+#pragma unroll 1
+  for (int q = 0; q < nq; q++) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      uint32_t w[4];
+      stream_words(plo[i], phi, (uint32_t)q, kTagGaussian, p.keys, w);
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float g0, g1;
+        gauss_pair(w[j], one, gc, g0, g1);
+        tot[i] = __fmul_rn(__fmul_rn(tot[i], g0), g1);
+      }
+    }
+  }
+  const int rem = p.n_periods - nq * kGaussMonthsPerCall;
+  if (rem) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      uint32_t w[4];
+      stream_words(plo[i], phi, (uint32_t)nq, kTagGaussian, p.keys, w);
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float g0, g1;
+        gauss_pair(w[j], one, gc, g0, g1);
+        if (2 * j < rem) tot[i] = __fmul_rn(tot[i], g0);
+        if (2 * j + 1 < rem) tot[i] = __fmul_rn(tot[i], g1);
+      }
+    }
+  }
+}
+
+// ---- Sobol modes: all 8 paths of the lane at once -------------------------------------------------------------------
+// Point i = path + 256 = 256 h + c with c = 32 j + lane (the block base is 256-aligned), x_m(i) = XOR over the set
+// bits k of gray(i) of V[m][k].  gray bits >= 8 depend on h only: that part (U_m, with the digital shift and the
+// h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
+// broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
+// eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
+template <int MODE>
+__device__ __forceinline__ void run_sobol(const KParams &p, const char *tbl, uint32_t lane_off, const uint4 *vlo,
+                                          uint32_t h, uint32_t lane, float (&tot)[8]) {
+  const uint32_t mk0 = ((lane ^ (lane >> 1)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk1 = (((lane >> 1) ^ (lane >> 2)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk2 = (((lane >> 2) ^ (lane >> 3)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk3 = (((lane >> 3) ^ (lane >> 4)) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t mk4 = ((lane >> 4) & 1u) ? 0xffffffffu : 0u;
+  const uint32_t gh = h ^ (h >> 1);
+  const int ppad = p.sobol_ppad;
+  const uint32_t nr4 = p.nr4, row_mask = ~(p.rep4 - 1u);
+  const float a = p.gc.a, s2 = p.sigma_sqrt2;
+#pragma unroll 1
+  for (int m0 = 0; m0 < p.n_periods; m0 += 32) {
+    const uint32_t *col = p.sobol_hi + m0 + lane;
+    uint32_t U = __ldg(col + 25 * ppad);
+    if (h & 1u) U ^= __ldg(col + 24 * ppad);
+    for (uint32_t g = gh; g; g &= g - 1u) U ^= __ldg(col + (__ffs((int)g) - 1) * ppad);
+    const int mend = (p.n_periods - m0) < 32 ? (p.n_periods - m0) : 32;
+#pragma unroll 2
+    for (int mi = 0; mi < mend; mi++) {
+      const uint32_t Um = __shfl_sync(0xffffffffu, U, mi);
+      const uint4 va = vlo[(m0 + mi) * 2], vb = vlo[(m0 + mi) * 2 + 1];
+      uint32_t base = Um ^ (va.x & mk0);
+      base ^= (va.y & mk1);
+      base ^= (va.z & mk2);
+      base ^= (va.w & mk3);
+      base ^= (vb.x & mk4);
+      uint32_t x[8];
+      x[0] = base;
+      x[1] = base ^ vb.x ^ vb.y;
+      x[2] = base ^ vb.y ^ vb.z;
+      x[3] = base ^ vb.x ^ vb.z;
+      x[4] = base ^ vb.z ^ vb.w;
+      x[5] = x[1] ^ vb.z ^ vb.w;
+      x[6] = base ^ vb.y ^ vb.w;
+      x[7] = base ^ vb.x ^ vb.w;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = boot_step(tot[j], x[j], tbl, nr4, row_mask, lane_off);
+        else tot[j] = __fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a));
+      }
+    }
+  }
+}
+
+// ---- the fused persistent kernel ---------------------------------------------------------------------------------
+
+template <int MODE, int ILP, int SHIFT>
+__global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  constexpr bool kHasTable = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT || MODE == SMMC_MODE_BOOTSTRAP ||
+                              MODE == SMMC_MODE_SOBOL_BOOTSTRAP);
+  constexpr bool kSobol = (MODE == SMMC_MODE_SOBOL_BOOTSTRAP || MODE == SMMC_MODE_SOBOL_GAUSSIAN);
+  const SmemLayout L = smem_layout(p.hist_bins, (uint32_t)p.sel_targets * kSelectBins * 4u, kSobol ? p.sobol_lo_bytes : 0u,
+                                   kHasTable ? p.tbl_bytes : 0u);
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
+  unsigned long long *hist_s = reinterpret_cast<unsigned long long *>(smem + L.hist_off);
+  double *wp = reinterpret_cast<double *>(smem + L.wp_off);
+  unsigned int *sel_s = reinterpret_cast<unsigned int *>(smem + L.sel_off);
+  const char *tbl = reinterpret_cast<const char *>(smem + L.tbl_off);
+  const uint4 *vlo = reinterpret_cast<const uint4 *>(smem + L.sob_off);
+
+  const int tid = threadIdx.x;
+  const int n_warps = (int)(blockDim.x >> 5);  // chosen per launch (plan_launch): evens out the last wave
+  const uint32_t lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
+
+  // ---- stage the table: one thread arms the mbarrier and issues the bulk copies, everyone waits on the phase
+  if (kHasTable || kSobol) {
+    if (tid == 0) {
+      mbar_init(bar, 1);
+      fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t tb = kHasTable ? p.tbl_bytes : 0u, sb = kSobol ? p.sobol_lo_bytes : 0u;
+      mbar_arrive_expect_tx(bar, tb + sb);
+      constexpr uint32_t kChunk = 32768;
+      for (uint32_t o = 0; o < tb; o += kChunk)
+        tma_bulk_g2s(smem + L.tbl_off + o, reinterpret_cast<const char *>(p.tbl_rep) + o,
+                     (tb - o) < kChunk ? (tb - o) : kChunk, bar);
+      for (uint32_t o = 0; o < sb; o += kChunk)
+        tma_bulk_g2s(smem + L.sob_off + o, reinterpret_cast<const char *>(p.sobol_lo) + o,
+                     (sb - o) < kChunk ? (sb - o) : kChunk, bar);
+    }
+  }
+  for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x) hist_s[i] = 0ull;
+  for (int i = tid; i < p.sel_targets * kSelectBins; i += (int)blockDim.x) sel_s[i] = 0u;
+  __syncthreads();
+  if (kHasTable || kSobol) mbar_wait(bar, 0);
+
+  const int64_t N = p.n_paths;
+  const int64_t nb = (N + kBlock - 1) / kBlock;
+  const int64_t total_warps = (int64_t)gridDim.x * n_warps;
+  const uint32_t lane_off = (lane * 4u) & (p.rep4 - 1u);
+  constexpr bool kCompat = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT);
+  // BOOTSTRAP: shared-window address of this lane's column, minus the float exponent bits that boot_load shifts out
+  const uint32_t boot_base = smem_u32(tbl) + lane_off - (0x4B000000u << (SHIFT >= 0 ? (uint32_t)SHIFT : p.bc.row_shift));
+
+  Moments acc = {0.0, 0.0, 0.0};
+  unsigned int below_lane = 0;
+  unsigned long long below_acc = 0ull;
+
+  for (int64_t b = (int64_t)blockIdx.x * n_warps + warp; b < nb; b += total_warps) {
+    const uint64_t base = p.path0 + (uint64_t)b * kBlock;  // 256-aligned: low 8 bits free for the in-block offset
+    const uint32_t base_lo = (uint32_t)base, phi = (uint32_t)(base >> 32);
+    const int64_t rem_paths = N - b * kBlock;
+    const int live = rem_paths < kBlock ? (int)rem_paths : kBlock;
+
+    float x[kPathsPerLane];
+    if (kSobol) {
+#pragma unroll
+      for (int j = 0; j < kPathsPerLane; j++) x[j] = p.v0;
+      run_sobol<MODE>(p, tbl, lane_off, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
+    }
+#pragma unroll
+    for (int s = 0; s < (kSobol ? 0 : kPathsPerLane); s += ILP) {
+      uint32_t plo[ILP];
+      float tot[ILP];
+#pragma unroll
+      for (int i = 0; i < ILP; i++) {
+        plo[i] = base_lo + (uint32_t)((s + i) * 32) + lane;
+        tot[i] = p.v0;
+      }
+      if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP>(p, tbl, lane_off, plo, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT>(p, boot_base, plo, phi, tot);
+      if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP>(p, plo, phi, tot);
+#pragma unroll
+      for (int i = 0; i < ILP; i++) x[s + i] = tot[i];
+    }
+
+    // ---- per-path outputs: finals (optional), below-target count, histogram
+    bool valid[kPathsPerLane];
+#pragma unroll
+    for (int j = 0; j < kPathsPerLane; j++) {
+      valid[j] = (j * 32 + (int)lane) < live;
+      if (valid[j]) {
+        if (p.finals) p.finals[b * kBlock + j * 32 + lane] = x[j];
+        below_lane += (x[j] < p.target) ? 1u : 0u;
+        if (p.hist_bins > 0) atomicAdd(&hist_s[hist_bin(x[j], p.hist_lo, p.hist_inv_w, p.hist_bins)], 1ull);
+        if (p.sel_targets > 0) {  // radix-select pass: digit histogram of the keys under each target's prefix
+          const uint32_t key = ordered_key(x[j]);
+          const uint32_t digit = (key >> p.sel_digit_shift) & p.sel_digit_mask;
+          const uint32_t pre = p.sel_prefix_shift >= 32 ? 0u : key >> p.sel_prefix_shift;
+          for (int t = 0; t < p.sel_targets; t++)
+            if (pre == p.sel_prefix[t]) atomicAdd(&sel_s[t * kSelectBins + digit], 1u);
+        }
+      }
+    }
+
+    // ---- block mean / population variance in the reference's reduceBlock layout and reduction order
+    // (src/simulations.cu:224-246): dead slots contribute 0; COMPAT keeps the reference's divisor of 256 for a
+    // partial last block, the native modes divide by the number of live paths.
+    float s[kPathsPerLane];
+#pragma unroll
+    for (int j = 0; j < kPathsPerLane; j++) s[j] = valid[j] ? x[j] : 0.0f;
+    const float sum = tree_sum_256(s);
+    const bool full = (live == kBlock);
+    const float div = (kCompat || full) ? 256.0f : (float)live;
+    const float mean = __fdiv_rn(sum, div);
+#pragma unroll
+    for (int j = 0; j < kPathsPerLane; j++) {
+      const float d = __fsub_rn(x[j], mean);
+      s[j] = valid[j] ? __fmul_rn(d, d) : 0.0f;
+    }
+    const float sq = tree_sum_256(s);
+    if (lane == 0) {
+      if (p.bmeans) p.bmeans[b] = mean;
+      if (p.bvars) p.bvars[b] = __fdiv_rn(sq, div);
+    }
+    double mean_live = (double)mean, m2_live = (double)sq;
+    if (kCompat && !full) {  // global moments always describe the live paths only
+      const float tmean = __fdiv_rn(sum, (float)live);
+#pragma unroll
+      for (int j = 0; j < kPathsPerLane; j++) {
+        const float d = __fsub_rn(x[j], tmean);
+        s[j] = valid[j] ? __fmul_rn(d, d) : 0.0f;
+      }
+      mean_live = (double)tmean;
+      m2_live = (double)tree_sum_256(s);
+    }
+    merge(acc, (double)live, mean_live, m2_live);
+
+    if (below_lane > 0x7fffff00u) {  // keep the 32-bit per-lane counter far from wrapping
+      below_acc += below_lane;
+      below_lane = 0;
+    }
+  }
+
+  // ---- warp -> CTA -> grid
+  below_acc += below_lane;
+#pragma unroll
+  for (int st = 16; st >= 1; st >>= 1) below_acc += __shfl_xor_sync(0xffffffffu, below_acc, st);
+  if (lane == 0) {
+    wp[warp * 4 + 0] = acc.n;
+    wp[warp * 4 + 1] = acc.mean;
+    wp[warp * 4 + 2] = acc.m2;
+    wp[warp * 4 + 3] = (double)below_acc;  // < 2^53, exact
+  }
+  __syncthreads();
+  __shared__ bool is_last;
+  if (tid == 0) {
+    Moments c = {0.0, 0.0, 0.0};
+    double below = 0.0;
+    for (int w = 0; w < n_warps; w++) {
+      merge(c, wp[w * 4 + 0], wp[w * 4 + 1], wp[w * 4 + 2]);
+      below += wp[w * 4 + 3];
+    }
+    double *cp = p.cta_partials + (size_t)blockIdx.x * 4;
+    cp[0] = c.n;
+    cp[1] = c.mean;
+    cp[2] = c.m2;
+    cp[3] = below;
+  }
+  for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x)
+    if (hist_s[i]) atomicAdd(&p.hist_g[i], hist_s[i]);
+  for (int i = tid; i < p.sel_targets * kSelectBins; i += (int)blockDim.x)
+    if (sel_s[i]) atomicAdd(&p.sel_hist_g[i], (unsigned long long)sel_s[i]);
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) is_last = (atomicAdd(p.ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+
+  // last CTA: merge the per-CTA partials in CTA order (warp 0: lane-strided sequential merge, then a fixed
+  // butterfly), emit the allreduce-ready statistics vector (include/smmc.h, SMMC_STATS_HEADER)
+  if (warp == 0) {
+    Moments c = {0.0, 0.0, 0.0};
+    double below = 0.0;
+    for (unsigned g = lane; g < gridDim.x; g += 32) {
+      const double *cp = p.cta_partials + (size_t)g * 4;
+      merge(c, __ldcg(cp + 0), __ldcg(cp + 1), __ldcg(cp + 2));
+      below += __ldcg(cp + 3);
+    }
+#pragma unroll
+    for (int st = 1; st <= 16; st <<= 1) {
+      const double on = __shfl_xor_sync(0xffffffffu, c.n, st);
+      const double om = __shfl_xor_sync(0xffffffffu, c.mean, st);
+      const double o2 = __shfl_xor_sync(0xffffffffu, c.m2, st);
+      const double ob = __shfl_xor_sync(0xffffffffu, below, st);
+      // merge in a lane-symmetric order so every lane ends with identical bits: lower lane is always "a"
+      Moments a, bb;
+      if ((lane & st) == 0) {
+        a = c;
+        bb = {on, om, o2};
+      } else {
+        a = {on, om, o2};
+        bb = c;
+      }
+      merge(a, bb.n, bb.mean, bb.m2);
+      c = a;
+      below += ob;
+    }
+    if (lane == 0) {
+      const double dm = c.mean - (double)p.v0;
+      p.stats[0] = c.n;
+      p.stats[1] = below;
+      p.stats[2] = c.n * dm;               // S1 = sum (x - V0)
+      p.stats[3] = c.m2 + c.n * dm * dm;   // S2 = sum (x - V0)^2
+      p.stats[4] = 0.0;
+      p.stats[5] = 0.0;
+    }
+  }
+  for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x)
+    p.stats[SMMC_STATS_HEADER + i] = (double)__ldcg(&p.hist_g[i]);
+}
+
+template <int MODE, int ILP, int SHIFT = -1>
+cudaError_t launch_one(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
+  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP, SHIFT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)li.smem_bytes);
+  if (e != cudaSuccess) return e;
+  mc_kernel<MODE, ILP, SHIFT><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+}  // namespace smmc

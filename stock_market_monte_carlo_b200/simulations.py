@@ -253,6 +253,127 @@ def vector_add_gpu(out, a, b, n):
     N.check(lib.smmc_vector_add(out.ctypes.data, a32.ctypes.data, b32.ctypes.data, int(n), 0))
 
 
+# ---- order statistics (reference update_quartiles), trajectories (mc_simulations_keepdata), data-format edges -----
+
+def quartile_ranks(n):
+    """ranks of {min, Q1, median, Q3, max} in the sorted finals, as the reference indexes them
+    (examples/visualize_returns_gpu.cpp:84-86, :109: v[0], v[N/4], v[N/2], v[N/4 + N/2], v[N-1])"""
+    n = int(n)
+    q1, q2 = n // 4, n // 2
+    return [0, q1, q2, q1 + q2, n - 1]
+
+
+def quantiles(mode, n_simulations, n_periods, ranks=None, initial_capital=1000.0, returns=None, seed=0,
+              stream_offset=0, gauss_mean=0.5, gauss_std=10.0 / 12.0, device=0, n_gpus=1, return_ms=False):
+    """sorted(finals)[ranks] of the run, exactly, without materialising the finals: three replays of the
+    counter-based simulation drive a radix select in shared memory (`smmc_quantiles`).  ranks=None gives the
+    reference's five quartile ranks."""
+    lib = N.load()
+    cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
+                            gauss_mean, gauss_std, device=device)
+    r = np.ascontiguousarray(np.asarray(quartile_ranks(n_simulations) if ranks is None else ranks, dtype=np.uint64))
+    out = np.zeros(r.size, dtype=np.float32)
+    ms = C.c_float()
+    N.check(lib.smmc_quantiles(C.byref(cfg), int(n_gpus), int(r.size), r.ctypes.data, out.ctypes.data, C.byref(ms)))
+    del keep
+    return (out, float(ms.value)) if return_ms else out
+
+
+def update_quartiles(quartiles, mode, n_simulations, n_periods, **kw):
+    """Mirror of the reference helper of the same name (examples/visualize_returns_gpu.cpp:83-110), fed by the
+    simulation instead of a host vector of finals: quartiles <- {min, Q1, median, Q3, max}."""
+    quartiles.array = quantiles(mode, n_simulations, n_periods, None, **kw)
+
+
+class SelectState:
+    """Pass-by-pass protocol of the radix select, for one-process-per-GPU jobs (distributed.quantiles_sharded)."""
+
+    def __init__(self, ranks):
+        self.lib = N.load()
+        self.st = N.SmmcSelectState()
+        r = np.ascontiguousarray(np.asarray(ranks, dtype=np.uint64))
+        N.check(self.lib.smmc_select_begin(C.byref(self.st), int(r.size), r.ctypes.data))
+
+    @property
+    def done(self):
+        return int(self.st.bits_done) >= 32
+
+    def run_pass(self, cfg, hist_ptr=None):
+        """one replay; host histogram returned unless `hist_ptr` (device, with a DEVICE_POINTERS cfg) is given"""
+        if hist_ptr is not None:
+            N.check(self.lib.smmc_select_pass(C.byref(cfg), C.byref(self.st), int(hist_ptr)))
+            return None
+        hist = np.zeros(N.SELECT_MAX_TARGETS * N.SELECT_BINS, dtype=np.uint64)
+        N.check(self.lib.smmc_select_pass(C.byref(cfg), C.byref(self.st), hist.ctypes.data))
+        return hist
+
+    def advance(self, hist):
+        h = np.ascontiguousarray(np.asarray(hist, dtype=np.uint64).reshape(-1))
+        assert h.size == N.SELECT_MAX_TARGETS * N.SELECT_BINS
+        N.check(self.lib.smmc_select_advance(C.byref(self.st), h.ctypes.data))
+
+    def values(self):
+        out = np.zeros(int(self.st.n_targets), dtype=np.float32)
+        N.check(self.lib.smmc_select_values(C.byref(self.st), out.ctypes.data))
+        return out
+
+
+def trajectories(mode, n_paths, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False, device=0):
+    """values[n_paths][n_periods+1] (and the monthly returns in percent [n_paths][n_periods]) of paths
+    stream_offset .. stream_offset+n_paths-1: the reference's `mc_data` of mc_simulations_keepdata
+    (src/simulations.cpp:139-202), from the same RNG streams as the statistics kernel."""
+    lib = N.load()
+    cfg, keep = make_config(mode, n_paths, n_periods, initial_capital, returns, seed, stream_offset, gauss_mean,
+                            gauss_std, device=device)
+    values = np.zeros((int(n_paths), int(n_periods) + 1), dtype=np.float32)
+    rets = np.zeros((int(n_paths), int(n_periods)), dtype=np.float32) if want_returns else None
+    N.check(lib.smmc_trajectories(C.byref(cfg), int(n_paths), values.ctypes.data,
+                                  rets.ctypes.data if rets is not None else None))
+    del keep
+    return (values, rets) if want_returns else values
+
+
+def mc_simulations_keepdata(n_simulations, max_n_simulations, n_periods, initial_capital, historical_returns, mc_data,
+                            final_values):
+    """reference src/simulations.cpp:139-202: mc_data[i] <- the n_periods+1 values of path i, final_values[i] <- the
+    last one; n_simulations <- N.  (GPU bootstrap from the reference's RNG stream.)"""
+    v = trajectories("bootstrap_compat", max_n_simulations, n_periods, initial_capital, historical_returns)
+    mc_data[:] = [row for row in v]
+    final_values.array = np.ascontiguousarray(v[:, -1])
+    n_simulations.store(max_n_simulations)
+
+
+def read_historical_returns(csv_fpath):
+    """reference src/simulations.cpp:83-93: the "returns" column of a CSV with a header line, as float32"""
+    lib = N.load()
+    n = C.c_int32()
+    path = str(csv_fpath).encode()
+    N.check(lib.smmc_read_returns_csv(path, None, 0, C.byref(n)))
+    out = np.zeros(int(n.value), dtype=np.float32)
+    N.check(lib.smmc_read_returns_csv(path, out.ctypes.data, int(out.size), C.byref(n)))
+    return out
+
+
+def write_data_file(fname, returns, values):
+    """reference src/helpers.cpp:23-39 ("Returns,,r0,...,\nValues,v0,...,"); `fname` is the full path here (the
+    reference prepends ./outputs/)"""
+    lib = N.load()
+    r, v = _as_f32(returns), _as_f32(values)
+    N.check(lib.smmc_write_data_file(str(fname).encode(), r.ctypes.data, int(r.size), v.ctypes.data, int(v.size)))
+
+
+def plan_launch(mode, n_simulations, n_periods, n_returns=0, hist_bins=0, select_targets=0, n_sms=148,
+                smem_optin=232448):
+    """(grid, threads, table_copies, smem_bytes) smmc_run would use on a device with `n_sms` SMs (host only)"""
+    lib = N.load()
+    cfg, _ = make_config(mode, n_simulations, n_periods, hist_bins=hist_bins)
+    cfg.n_returns = int(n_returns)
+    plan = N.SmmcPlan()
+    N.check(lib.smmc_plan_launch(C.byref(cfg), int(select_targets), int(n_sms), int(smem_optin), C.byref(plan)))
+    return int(plan.grid), int(plan.threads), int(plan.table_copies), int(plan.smem_bytes)
+
+
 def debug_draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0, device=0):
     lib = N.load()
     cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset,

@@ -13,6 +13,8 @@ Fixtures written (all small; the reference tree does not exist on the GPU box, t
   ref_update_fund.npz      update_fund (src/simulations.cpp:14-16) on a grid of (fund, return) pairs
   oracle_regression.npz    the oracle's own outputs for every mode at N=600, P=37 (freezes the stream contract:
                            a change of the RNG/counter layout, field split, bin rule or Sobol skip shows up here)
+  ref_write_data_file.csv  the bytes the reference's write_data_file (src/helpers.cpp:23-39) writes for a fixed
+                           (returns, values) pair (tests/test_next_rows_cpu.py::_data_file_case)
 The GPU-side fixture (reference .cu kernels run on a B200) is made by make_golden_gpu.py.
 """
 import os
@@ -79,6 +81,22 @@ def oracle_regression():
     np.savez_compressed(os.path.join(HERE, "oracle_regression.npz"), **out)
 
 
+def write_data_file_fixture():
+    import tempfile
+    sys.path.insert(0, os.path.dirname(HERE))
+    from test_next_rows_cpu import _data_file_case
+    r, v = _data_file_case()
+    tmp = tempfile.mkdtemp()
+    cwd = os.getcwd()
+    os.chdir(tmp)  # the reference writes ./outputs/<fname>
+    try:
+        O.ref_write_data_file("ref.csv", r, v)
+    finally:
+        os.chdir(cwd)
+    data = open(os.path.join(tmp, "outputs", "ref.csv"), "rb").read()
+    open(os.path.join(HERE, "ref_write_data_file.csv"), "wb").write(data)
+
+
 if __name__ == "__main__":
     for name in ("libref_cpu.so", "libref_sobol.so"):
         if not O.ref_available(name):
@@ -87,4 +105,5 @@ if __name__ == "__main__":
     cpu_quantiles()
     update_fund_fixture()
     oracle_regression()
+    write_data_file_fixture()
     print("golden fixtures written to", HERE)
