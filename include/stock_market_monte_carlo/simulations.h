@@ -14,6 +14,7 @@
 #include <atomic>
 #include <cstdint>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 #include "../smmc.h"
@@ -76,3 +77,29 @@ void mc_simulations_gpu_reduceBlock(std::atomic<long> &n_simulations, long max_n
                                     float initial_capital, std::vector<float> &returns, std::vector<float> *means,
                                     std::vector<float> *variances, int n_gpus, const smmc::Options &opt,
                                     smmc::Statistics *stats);
+
+// ---- what the reference's callers do on the host around the GPU entry points ------------------
+// (in namespace smmc: the reference defines CPU functions of the same names in the global namespace, and its
+// programs keep linking those from their own src/simulations.cpp / src/helpers.cpp)
+namespace smmc {
+
+// quartiles <- {min, Q1, median, Q3, max} of the N finals, i.e. sorted[0], sorted[N/4], sorted[N/2],
+// sorted[N/4 + N/2], sorted[N-1] exactly as update_quartiles computes them after a full host sort
+// (reference examples/visualize_returns_gpu.cpp:83-110) -- by three replays of the counter-based simulation
+// driving a radix select on the device; the finals are never materialised.
+void update_quartiles(std::vector<float> &quartiles, long max_n_simulations, int n_periods, float initial_capital,
+                      std::vector<float> &returns, int n_gpus = 1, const Options &opt = Options{});
+
+// mc_data[i] <- the n_periods + 1 values of path i, final_values[i] <- the last one (reference
+// mc_simulations_keepdata, src/simulations.cpp:139-202), from the same RNG streams as mc_simulations_gpu.
+void mc_simulations_keepdata(std::atomic<long> &n_simulations, long max_n_simulations, unsigned int n_periods,
+                             float initial_capital, std::vector<float> &historical_returns,
+                             std::vector<std::vector<float>> &mc_data, std::vector<float> &final_values,
+                             const Options &opt = Options{});
+
+// reference read_historical_returns (src/simulations.cpp:83-93) / write_data_file (src/helpers.cpp:23-39; the
+// reference prepends "./outputs/", here `path` is used as given).  Throw std::runtime_error on failure.
+std::vector<float> read_historical_returns(const std::string &csv_fpath);
+void write_data_file(const std::string &path, std::vector<float> &returns, std::vector<float> &values);
+
+}  // namespace smmc

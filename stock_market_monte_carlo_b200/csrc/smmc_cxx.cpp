@@ -123,3 +123,49 @@ void vector_add(float *out, float *a, float *b, int n) {
 void vector_add_gpu(float *out, float *a, float *b, int n) {
   die_on(smmc_vector_add(out, a, b, n, 0), "vector_add_gpu");
 }
+
+// ---- SURVEY 8(f) rows ----------------------------------------------------------------------------------------------
+namespace smmc {
+
+void update_quartiles(std::vector<float> &quartiles, long N, int n_periods, float initial_capital,
+                      std::vector<float> &returns, int n_gpus, const Options &opt) {
+  smmc_config c = base_config(N, n_periods, initial_capital, returns, opt);
+  c.hist_bins = 0;
+  const long q1 = N / 4, q2 = N / 2;  // reference examples/visualize_returns_gpu.cpp:84-86
+  const uint64_t ranks[5] = {0, (uint64_t)q1, (uint64_t)q2, (uint64_t)(q1 + q2), (uint64_t)(N - 1)};
+  float v[5] = {0, 0, 0, 0, 0};
+  die_on(smmc_quantiles(&c, n_gpus, 5, ranks, v, nullptr), "update_quartiles");
+  quartiles.assign(v, v + 5);
+}
+
+void mc_simulations_keepdata(std::atomic<long> &n_simulations, long N, unsigned int n_periods, float initial_capital,
+                             std::vector<float> &historical_returns, std::vector<std::vector<float>> &mc_data,
+                             std::vector<float> &final_values, const Options &opt) {
+  smmc_config c = base_config(N, (int)n_periods, initial_capital, historical_returns, opt);
+  c.hist_bins = 0;
+  const size_t row = (size_t)n_periods + 1;
+  std::vector<float> flat((size_t)(N > 0 ? N : 0) * row);
+  die_on(smmc_trajectories(&c, (int32_t)N, flat.data(), nullptr), "mc_simulations_keepdata");
+  mc_data.resize((size_t)(N > 0 ? N : 0));
+  final_values.resize((size_t)(N > 0 ? N : 0));
+  for (long i = 0; i < N; i++) {
+    mc_data[(size_t)i].assign(flat.begin() + (size_t)i * row, flat.begin() + ((size_t)i + 1) * row);
+    final_values[(size_t)i] = flat[(size_t)i * row + n_periods];
+  }
+  n_simulations.store(N, std::memory_order_release);
+}
+
+std::vector<float> read_historical_returns(const std::string &csv_fpath) {
+  int32_t n = 0;
+  if (smmc_read_returns_csv(csv_fpath.c_str(), nullptr, 0, &n) != SMMC_OK) throw std::runtime_error(smmc_last_error());
+  std::vector<float> v((size_t)n);
+  if (smmc_read_returns_csv(csv_fpath.c_str(), v.data(), n, &n) != SMMC_OK) throw std::runtime_error(smmc_last_error());
+  return v;
+}
+
+void write_data_file(const std::string &path, std::vector<float> &returns, std::vector<float> &values) {
+  if (smmc_write_data_file(path.c_str(), returns.data(), (int32_t)returns.size(), values.data(), (int32_t)values.size()) != SMMC_OK)
+    throw std::runtime_error(smmc_last_error());
+}
+
+}  // namespace smmc

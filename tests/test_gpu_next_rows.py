@@ -175,3 +175,53 @@ def test_results_do_not_depend_on_warps_per_cta(S, O, table, mode, monkeypatch):
         assert np.array_equal(r.hist, base.hist) and r.below_count == base.below_count
         assert abs(r.mean - base.mean) <= 1e-12 * abs(base.mean) and abs(r.m2 - base.m2) <= 1e-9 * abs(base.m2)
     monkeypatch.delenv("SMMC_WARPS")
+
+
+# ---- the C++ side of the same rows -----------------------------------------------------------------------------------
+CALLER = r'''
+#include <cstdio>
+#include <algorithm>
+#include "stock_market_monte_carlo/simulations.h"
+int main(int argc, char **argv) {
+  std::vector<float> returns = smmc::read_historical_returns(argv[1]);
+  if (returns.size() != 1127) return 2;
+  std::atomic<long> n_sim{0};
+  const long N = 4000; const int P = 60;
+  std::vector<float> totals, quart, finals;
+  mc_simulations_gpu(n_sim, N, P, 1000.f, returns, totals, 1);
+  smmc::update_quartiles(quart, N, P, 1000.f, returns);
+  std::sort(totals.begin(), totals.end());  // the reference's update_quartiles (examples/visualize_returns_gpu.cpp:108-109)
+  const float want[5] = {totals.at(0), totals.at(N / 4), totals.at(N / 2), totals.at(N / 4 + N / 2), totals.back()};
+  if (quart.size() != 5) return 3;
+  for (int i = 0; i < 5; i++) if (quart[i] != want[i]) return 4;
+  std::vector<std::vector<float>> mc_data;
+  smmc::mc_simulations_keepdata(n_sim, 50, P, 1000.f, returns, mc_data, finals);
+  if (mc_data.size() != 50 || mc_data[7].size() != (size_t)P + 1 || finals[7] != mc_data[7].back() || mc_data[7][0] != 1000.f) return 5;
+  std::vector<float> r(returns.begin(), returns.begin() + P);
+  smmc::write_data_file(argv[2], r, mc_data[7]);
+  bool threw = false;
+  try { smmc::read_historical_returns("/nonexistent.csv"); } catch (const std::runtime_error &) { threw = true; }
+  return threw ? 0 : 6;
+}
+'''
+
+
+def test_cxx_callers_of_the_next_rows(S, table1127, tmp_path):
+    import os
+    import subprocess
+    from conftest import ROOT
+    from stock_market_monte_carlo_b200 import _native
+    libdir = os.path.dirname(_native.LIB_PATH)
+    (tmp_path / "caller.cpp").write_text(CALLER)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", str(tmp_path / "caller"), str(tmp_path / "caller.cpp"),
+                    f"-I{ROOT}/include", f"-L{libdir}", "-lsmmc", f"-Wl,-rpath,{libdir}"], check=True)
+    with open(tmp_path / "t.csv", "w") as f:
+        f.write("Date,returns\n")
+        for x in table1127:
+            f.write(f"1900-01-01,{float(x)!r}\n")
+    subprocess.run([str(tmp_path / "caller"), str(tmp_path / "t.csv"), str(tmp_path / "out.csv")], check=True)
+    text = (tmp_path / "out.csv").read_text()
+    assert text.startswith("Returns,,") and "\nValues,1000," in text
+    v = S.trajectories("bootstrap_compat", 50, 60, returns=table1127)[7]
+    got = np.array([float(t) for t in text.split("\nValues,")[1].rstrip(",").split(",")])
+    np.testing.assert_allclose(got, v, rtol=1e-5)
