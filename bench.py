@@ -51,6 +51,13 @@ UNIT = "path-months/s"
 # fields / 8 normals per call and need 12, so the fraction below stays an issue-slot utilisation (<= 1).  The
 # SURVEY-budget fraction is reported next to it as `frac_survey_budget`.
 I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 24}
+# Pipe floors (cycles per warp-month per SM sub-partition) from the measured reciprocal throughputs in
+# profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the binding
+# resource of these instruction mixes is a pipe, not the issue slot.
+#   gaussian   2 MUFU per normal x 8.0 cycles (XU, 4 lanes/clk per sub-partition)
+#   bootstrap  Philox: 8 per-lane rounds x 8.39 cycles (2 IMAD.WIDE + 2 LOP3, measured as a unit) per 6 months,
+#              + 16 further ALU-pipe instructions per call (fields, addresses) at their measured marginal 2.0 cycles
+PIPE_FLOOR = {"gaussian": ("xu", 16.0), "bootstrap": ("fmaheavy+alu (Philox)", (8 * 8.39 + 16 * 2.0) / 6.0)}
 I_ALG_SURVEY = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": None, "sobol_gaussian": None}
 
 WORKLOADS = {
@@ -340,6 +347,14 @@ def main():
                "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
                "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)"}
 
+    # ---- SURVEY 8(f) rank 1, reported next to the headline (outside the timed region): the quartiles of the same
+    # workload by three replays (radix select in shared memory) instead of a finals download + host sort
+    extras = None
+    if world == 1 and not args.no_e2e and not sobol:
+        q, q_ms = S.quantiles(mode, B, P, initial_capital=V0, returns=table, seed=seed, device=local, return_ms=True, **GAUSS)
+        extras = {"quartiles_min_q1_med_q3_max": [float(x) for x in q], "quartiles_device_ms": q_ms,
+                  "quartiles_how": "smmc_quantiles: 3 replays of the workload, 11+11+10-bit radix select on ordered keys; exact"}
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -362,6 +377,10 @@ def main():
         "peak_source": f"{n_sm} SMs x 128 thread-instr/clk x sm_max_mhz {f_max / 1e6:.0f} "
                        f"({'MEASURED_PEAKS.json' if peaks.get('sm_max_mhz') else 'nvidia-smi'}); HBM/tensor peaks do not bound this path",
     }
+    if mode in PIPE_FLOOR:
+        pipe, cyc = PIPE_FLOOR[mode]
+        floor_ms = B * P * cyc / (n_sm * 128 * f_max) * 1e3
+        roofline["pipe_floor"] = {"pipe": pipe, "cycles_per_warp_month": cyc, "floor_ms": floor_ms, "frac": floor_ms / k_ms}
     if clocks and clocks.get("sm_mhz"):
         roofline["frac_at_sampled_clock"] = achieved / (n_sm * 128 * clocks["sm_mhz"] * 1e6)
 
@@ -385,6 +404,7 @@ def main():
         "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,
         "result": {"count": final.count, "mean": final.mean, "std": final.std, "p_below_target": final.p_below_target},
+        "extras": extras,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -225,3 +225,16 @@ def test_cxx_callers_of_the_next_rows(S, table1127, tmp_path):
     v = S.trajectories("bootstrap_compat", 50, 60, returns=table1127)[7]
     got = np.array([float(t) for t in text.split("\nValues,")[1].rstrip(",").split(",")])
     np.testing.assert_allclose(got, v, rtol=1e-5)
+
+
+def test_more_than_2_pow_32_paths_in_one_call(S):
+    """64-bit block / path indexing: 5e9 paths x 1 month in ONE call (no per-path output); closed-form mean, every
+    path counted once in the histogram, and the tail of the range equals the same paths run on their own"""
+    N = 5_000_000_000
+    r = S.simulate("gaussian", N, 1, seed=3, hist_bins=8, hist_range=(950.0, 1050.0))
+    assert r.count == N and int(r.hist.sum()) == N
+    assert abs(r.mean - 1005.0) < 5 * (1000 / 120) / np.sqrt(N) + 1e-4   # E = V0 (1 + mu), sd = V0 sigma
+    assert abs(r.std - 1000 / 120) < 1e-3
+    head = S.simulate("gaussian", N - 1_000_192, 1, seed=3, hist_bins=8, hist_range=(950.0, 1050.0))
+    tail = S.simulate("gaussian", 1_000_192, 1, seed=3, stream_offset=N - 1_000_192, hist_bins=8, hist_range=(950.0, 1050.0))
+    assert np.array_equal(head.hist + tail.hist, r.hist) and head.below_count + tail.below_count == r.below_count

@@ -1,0 +1,47 @@
+"""Summarise gpurun_out/ of `bash tools/gpu_first_run.sh` into one text file for profiles/.
+usage: python tools/summarize_run.py "<header line>" > profiles/<name>.txt"""
+import collections
+import csv
+import json
+import os
+import subprocess
+import sys
+
+G = "gpurun_out"
+print("#", sys.argv[1] if len(sys.argv) > 1 else "GPU run")
+print("# command: gpurun -- 'bash tools/gpu_first_run.sh'\n")
+print("## pytest -m gpu")
+print("".join(open(f"{G}/pytest_gpu.log").readlines()[-2:]))
+print("## smoke")
+print(open(f"{G}/smoke.log").read())
+print("## bench.py (device-timed value | e2e through smmc_run with host buffers | kernel ms | frac by restated I_alg | pipe floor | clocks)")
+for w in ["c2", "c3", "c3compat", "c4", "c4boot"]:
+    d = json.loads(open(f"{G}/bench_{w}.json").read().strip().splitlines()[-1])
+    r, c = d["roofline"], d["clocks"]
+    pf = r.get("pipe_floor")
+    print(f"{w:9s} value {d['value']:.4e} pm/s  e2e {d['e2e']['value']:.4e}  ms/step {d['ms_per_step']:.3f}  kernel_ms {r['kernel_ms']:.3f}  "
+          f"i_alg {r['i_alg']}  frac {r['frac']:.3f}  frac_survey_budget {r['frac_survey_budget'] and round(r['frac_survey_budget'], 3)}  "
+          f"pipe_floor {pf and (pf['pipe'], round(pf['frac'], 3))}  sm_mhz {c['sm_mhz']} reasons {c['reasons']} power_w_max {c['power_w_max']}")
+    if d.get("cpu_baseline"):
+        print("   cpu_baseline:", d["cpu_baseline"])
+    if d.get("extras"):
+        print("   extras:", d["extras"])
+d = json.loads(open(f"{G}/bench_ref.json").read().strip().splitlines()[-1])
+print("--impl reference:", d["value"], d["cpu_baseline"])
+print("\n## ncu launch list of: python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e  (gpu__time_duration.sum)")
+rows = list(csv.reader(l for l in open(f"{G}/launches_c2.csv") if l.startswith('"')))
+h = rows[0]
+ki, vi, ui = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Unit")
+agg = collections.OrderedDict()
+for r in rows[1:]:
+    v = float(r[vi].replace(",", ""))
+    u = r[ui]
+    v = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
+    agg.setdefault(r[ki], []).append(v)
+tot = sum(sum(v) for v in agg.values())
+for k, v in agg.items():
+    print(f"{len(v):3d} x {k[:90]:90s} avg {sum(v) / len(v):10.1f} us  share {100 * sum(v) / tot:5.2f}%")
+for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian"]:
+    print(f"\n## ncu --set full --clock-control none: python tools/run_one.py {m} (20M x 360; sobol 5M x 1000)")
+    sys.stdout.flush()
+    subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "ncu_summary.py"), f"{G}/prof_{m}.ncu-rep"])
