@@ -47,9 +47,16 @@ __device__ __forceinline__ float tree_sum_256(const float (&s)[8]) {
 
 // ---- one sub-batch of ILP paths through all P months ------------------------------------------------------------
 
+// `base` = shared-window address of this lane's column of the table (smem_u32(tbl) + lane_off): the row address is
+// then ONE IMAD (idx * row_bytes + base) feeding a plain LDS
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float r;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(addr));
+  return r;
+}
+
 template <int ILP>
-__device__ __forceinline__ void run_compat(const KParams &p, const char *tbl, uint32_t lane_off, const uint32_t (&plo)[ILP],
-                                           float (&tot)[ILP]) {
+__device__ __forceinline__ void run_compat(const KParams &p, uint32_t base, const uint32_t (&plo)[ILP], float (&tot)[ILP]) {
   uint32_t st[ILP];
 #pragma unroll
   for (int i = 0; i < ILP; i++) st[i] = rand_pcg(plo[i] + 1u + p.compat_seed);
@@ -62,16 +69,14 @@ __device__ __forceinline__ void run_compat(const KParams &p, const char *tbl, ui
       st[i] = xorshift(st[i]);
       // reference: idx = n * (state * 2^-32f), truncated (src/simulations.cu:148); one rounding either way
       const int idx = (int)(__uint2float_rn(st[i]) * scale);
-      const float r = *reinterpret_cast<const float *>(tbl + (uint32_t)idx * rep4 + lane_off);
+      const float r = lds_f32((uint32_t)idx * rep4 + base);
       tot[i] = fmaf(tot[i], r, tot[i]);  // total += total * r (one FFMA, as the reference compiles)
     }
   }
 }
 
-__device__ __forceinline__ float boot_step(float tot, uint32_t w, const char *tbl, uint32_t nr4, uint32_t row_mask,
-                                           uint32_t lane_off) {
-  const uint32_t off = (__umulhi(w, nr4) & row_mask) | lane_off;  // (idx * rep + lane%rep) * 4, idx = mulhi(w, n)
-  const float r = *reinterpret_cast<const float *>(tbl + off);
+__device__ __forceinline__ float boot_step(float tot, uint32_t w, uint32_t nr4, uint32_t row_mask, uint32_t base) {
+  const float r = lds_f32((__umulhi(w, nr4) & row_mask) + base);  // (idx * rep + lane%rep) * 4, idx = mulhi(w, n)
   return fmaf(tot, r, tot);
 }
 
@@ -158,7 +163,7 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
 template <int MODE>
-__device__ __forceinline__ void run_sobol(const KParams &p, const char *tbl, uint32_t lane_off, const uint4 *vlo,
+__device__ __forceinline__ void run_sobol(const KParams &p, uint32_t tbl_base, const uint4 *vlo,
                                           uint32_t h, uint32_t lane, float (&tot)[8]) {
   const uint32_t mk0 = ((lane ^ (lane >> 1)) & 1u) ? 0xffffffffu : 0u;
   const uint32_t mk1 = (((lane >> 1) ^ (lane >> 2)) & 1u) ? 0xffffffffu : 0u;
@@ -196,7 +201,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const char *tbl, uin
       x[7] = base ^ vb.x ^ vb.w;
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = boot_step(tot[j], x[j], tbl, nr4, row_mask, lane_off);
+        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = boot_step(tot[j], x[j], nr4, row_mask, tbl_base);
         else tot[j] = __fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a));
       }
     }
@@ -255,7 +260,8 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   const uint32_t lane_off = (lane * 4u) & (p.rep4 - 1u);
   constexpr bool kCompat = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT);
   // BOOTSTRAP: shared-window address of this lane's column, minus the float exponent bits that boot_load shifts out
-  const uint32_t boot_base = smem_u32(tbl) + lane_off - (0x4B000000u << (SHIFT >= 0 ? (uint32_t)SHIFT : p.bc.row_shift));
+  const uint32_t lane_base = smem_u32(tbl) + lane_off;  // shared-window address of this lane's table column
+  const uint32_t boot_base = lane_base - (0x4B000000u << (SHIFT >= 0 ? (uint32_t)SHIFT : p.bc.row_shift));
 
   Moments acc = {0.0, 0.0, 0.0};
   unsigned int below_lane = 0;
@@ -271,7 +277,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     if (kSobol) {
 #pragma unroll
       for (int j = 0; j < kPathsPerLane; j++) x[j] = p.v0;
-      run_sobol<MODE>(p, tbl, lane_off, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
+      run_sobol<MODE>(p, lane_base, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
     }
 #pragma unroll
     for (int s = 0; s < (kSobol ? 0 : kPathsPerLane); s += ILP) {
@@ -282,7 +288,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
         plo[i] = base_lo + (uint32_t)((s + i) * 32) + lane;
         tot[i] = p.v0;
       }
-      if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP>(p, tbl, lane_off, plo, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP>(p, lane_base, plo, tot);
       if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT>(p, boot_base, plo, phi, tot);
       if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP>(p, plo, phi, tot);
 #pragma unroll
