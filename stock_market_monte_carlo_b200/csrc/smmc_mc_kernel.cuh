@@ -174,12 +174,22 @@ __device__ __forceinline__ void run_sobol(const KParams &p, uint32_t tbl_base, c
   const int ppad = p.sobol_ppad;
   const uint32_t nr4 = p.nr4, row_mask = ~(p.rep4 - 1u);
   const float a = p.gc.a, s2 = p.sigma_sqrt2;
-#pragma unroll 1
-  for (int m0 = 0; m0 < p.n_periods; m0 += 32) {
+  // warp-uniform part of month m0 + lane: every load is issued before the first is consumed (independent,
+  // predicated on the warp-uniform gray bits), and the next 32 months are fetched while the current 32 are computed
+  auto block_part = [&](int m0) {
     const uint32_t *col = p.sobol_hi + m0 + lane;
     uint32_t U = __ldg(col + 25 * ppad);
     if (h & 1u) U ^= __ldg(col + 24 * ppad);
-    for (uint32_t g = gh; g; g &= g - 1u) U ^= __ldg(col + (__ffs((int)g) - 1) * ppad);
+#pragma unroll
+    for (int k = 0; k < 24; k++)
+      if ((gh >> k) & 1u) U ^= __ldg(col + k * ppad);
+    return U;
+  };
+  uint32_t U_next = p.n_periods > 0 ? block_part(0) : 0u;
+#pragma unroll 1
+  for (int m0 = 0; m0 < p.n_periods; m0 += 32) {
+    const uint32_t U = U_next;
+    if (m0 + 32 < p.n_periods) U_next = block_part(m0 + 32);
     const int mend = (p.n_periods - m0) < 32 ? (p.n_periods - m0) : 32;
 #pragma unroll 2
     for (int mi = 0; mi < mend; mi++) {
