@@ -140,3 +140,32 @@ def test_validation_precedes_device_probe(S, table):
         with pytest.raises(S.SmmcError) as e:
             S.simulate(**kw)
         assert e.value.status == 1, kw
+
+
+def test_new_entry_points_fail_loudly_without_a_device(S, table):
+    """quantiles / select passes / trajectories are device work: no CPU fallback either"""
+    lib = S.load()
+    if lib.smmc_device_count() > 0:
+        pytest.skip("a device is visible")
+    for call in (lambda: S.quantiles("gaussian", 1000, 12),
+                 lambda: S.trajectories("bootstrap", 10, 12, returns=table),
+                 lambda: S.SelectState([0]).run_pass(S.make_config("gaussian", 1000, 12)[0])):
+        with pytest.raises(S.SmmcError) as e:
+            call()
+        assert e.value.status == 2 and "no CPU fallback" in str(e.value)
+
+
+def test_new_entry_points_validate_before_probing(S, table):
+    bad = [
+        lambda: S.quantiles("bootstrap", 100, 12),                               # no table
+        lambda: S.quantiles("gaussian", 100, 12, ranks=list(range(9))),          # > SMMC_SELECT_MAX_TARGETS
+        lambda: S.quantiles("gaussian", 100, 12, ranks=[]),
+        lambda: S.trajectories("sobol_gaussian", 4, 2000),
+        lambda: S.trajectories("gaussian", 4, 12, stream_offset=3),
+        lambda: S.plan_launch("gaussian", 100, 12, select_targets=9),
+        lambda: S.plan_launch("gaussian", 100, 12, n_sms=0),
+    ]
+    for call in bad:
+        with pytest.raises(S.SmmcError) as e:
+            call()
+        assert e.value.status == 1
