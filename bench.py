@@ -17,6 +17,7 @@ Workloads (BASELINE.json configs):
   c3        360 x 100 M bootstrap (Philox) from the synthetic 1200-month S&P-500-shaped table (shared-memory resident)
   c3compat  same through the reference's own RNG stream (bit-exact drop-in of src/simulations.cu)
   c4        1000 x 5 M Sobol (Joe-Kuo) Gaussian, histogram + P(target);  c4boot: Sobol bootstrap
+  c5        360 x 10^10 Gaussian + histogram: ONE run's paths sharded over the N GPUs (strong scaling; 1.8 s per step on 1 GPU)
 
 Printed: ONE JSON line (rank 0).  `value` is device-timed (CUDA events on the launching stream, summed over the K
 steps, max over ranks) with everything resident in HBM; `e2e` is the same metric through the public host-buffer
@@ -68,6 +69,9 @@ WORKLOADS = {
     "c3compat": dict(mode="bootstrap_compat", paths=100_000_000, periods=360, block_partials=True,
                      hist_range=(0.0, 200_000.0),
                      desc="360 months x 100M paths bootstrap, reference RNG stream (drop-in of src/simulations.cu)"),
+    "c5": dict(mode="gaussian", paths=10_000_000_000, periods=360, block_partials=False, hist_range=(0.0, 50_000.0),
+               strong=True,
+               desc="360 months x 10^10 paths Gaussian + histogram + P(target), the 10^10 paths of ONE run sharded over the GPUs (strong scaling)"),
     "c4": dict(mode="sobol_gaussian", paths=5_000_000, periods=1000, block_partials=False, hist_range=(0.0, 500_000.0),
                desc="1000 months x 5M paths Sobol (Joe-Kuo) Gaussian, histogram + P(target)"),
     "c4boot": dict(mode="sobol_bootstrap", paths=5_000_000, periods=1000, block_partials=False,
@@ -77,6 +81,14 @@ WORKLOADS = {
 HIST_BINS = 100
 V0 = 1000.0
 GAUSS = dict(gauss_mean=0.5, gauss_std=10.0 / 12.0)
+
+
+def ncu_traffic(mode):
+    """dram bytes per launch of the simulation kernel from the committed ncu capture (profiles/ncu_traffic.json)"""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["bytes_per_launch"].get(mode)
+    except Exception:
+        return None
 
 
 def measured_peaks():
@@ -214,7 +226,7 @@ def run_reference_arm(args, wl):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=0, help="timed steps (default 100; 5 for the 1.8 s steps of c5)")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
@@ -225,6 +237,8 @@ def main():
     wl = dict(WORKLOADS[args.workload])
     if args.paths:
         wl["paths"] = args.paths
+    if args.steps <= 0:
+        args.steps = 5 if wl.get("strong") else 100
     if args.impl == "reference":
         return run_reference_arm(args, wl)
     if args.warmup < 3:
@@ -249,6 +263,12 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     mode, B, P = wl["mode"], wl["paths"], wl["periods"]
+    strong = bool(wl.get("strong"))
+    job_paths = B if strong else world * B  # paths of one step over all ranks
+    if strong:  # B = this rank's shard of the fixed global run (whole 256-path blocks, distributed.shard_range)
+        from stock_market_monte_carlo_b200.distributed import shard_range
+        total_paths = B
+        shard_off, B = shard_range(total_paths, rank, world)
     nb = (B + 255) // 256
     table = S.synthetic_sp500_table(1200) if "bootstrap" in mode else None
     seed = 0 if mode == "bootstrap_compat" else 1234
@@ -267,6 +287,8 @@ def main():
         if sobol or mode == "bootstrap_compat":  # 32-bit point / path ids: wrap the offsets, still disjoint per rank
             span = (1 << 31) - 256 - B if mode == "bootstrap_compat" else (1 << 32) - 512 - B
             return (((step * world + rank) * B) % max(span, 1)) // 256 * 256
+        if strong:
+            return step * total_paths + shard_off
         return (step * world + rank) * B
 
     def device_step(step):
@@ -342,7 +364,7 @@ def main():
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * B * P * k_e2e / float(dt.item()), "unit": UNIT,
+        e2e = {"value": job_paths * P * k_e2e / float(dt.item()), "unit": UNIT,
                "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
                "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
                "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)"}
@@ -371,7 +393,8 @@ def main():
     achieved = B * P * I_ALG[mode] / (k_ms * 1e-3)
     roofline = {
         "bound": "issue", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tinstr/s", "frac": achieved / peak,
-        "traffic": None, "kernel": "smmc::mc_kernel<%s>" % mode, "kernel_ms": k_ms,
+        "traffic": ncu_traffic(mode), "traffic_unit": "dram bytes per launch (ncu); algorithmic HBM bytes: table + partials only",
+        "kernel": "smmc::mc_kernel<%s>" % mode, "kernel_ms": k_ms,
         "i_alg": I_ALG[mode], "survey_i_alg": I_ALG_SURVEY[mode],
         "frac_survey_budget": (achieved / I_ALG[mode] * I_ALG_SURVEY[mode] / peak) if I_ALG_SURVEY[mode] else None,
         "peak_source": f"{n_sm} SMs x 128 thread-instr/clk x sm_max_mhz {f_max / 1e6:.0f} "
@@ -392,10 +415,10 @@ def main():
         cpu_baseline = {"value": n * P / dt, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
                         "sample": f"{n} paths x {P} months in {dt:.1f} s; {cpu.desc}"}
 
-    value = world * B * P * args.steps / (total_ms * 1e-3)
+    value = job_paths * P * args.steps / (total_ms * 1e-3)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "mode": mode, "paths_per_gpu_per_step": B, "periods": P, "seed": seed,
                    "hist_bins": HIST_BINS, "block_partials": wl["block_partials"], "parallelism": f"paths sharded by RNG offset x{world}",

@@ -238,3 +238,17 @@ def test_more_than_2_pow_32_paths_in_one_call(S):
     head = S.simulate("gaussian", N - 1_000_192, 1, seed=3, hist_bins=8, hist_range=(950.0, 1050.0))
     tail = S.simulate("gaussian", 1_000_192, 1, seed=3, stream_offset=N - 1_000_192, hist_bins=8, hist_range=(950.0, 1050.0))
     assert np.array_equal(head.hist + tail.hist, r.hist) and head.below_count + tail.below_count == r.below_count
+
+
+def test_c5_size_ten_billion_paths_closed_form_moments(S):
+    """BASELINE config 5 on one GPU: 360 months x 10^10 Gaussian paths + histogram in ONE call (1.8 s): moments against
+    the closed forms E[V] = V0 (1+mu)^P, E[V^2] = V0^2 ((1+mu)^2 + sigma^2)^P (north_star: <= 1e-5 relative)"""
+    N, P = 10_000_000_000, 360
+    r = S.simulate("gaussian", N, P, seed=1234, hist_bins=100, hist_range=(0.0, 50_000.0))
+    mu, sg = 0.005, 1.0 / 120.0
+    mean = 1000.0 * (1 + mu) ** P
+    var = 1000.0 ** 2 * ((1 + mu) ** 2 + sg ** 2) ** P - mean ** 2
+    assert r.count == N and int(r.hist.sum()) == N
+    se_rel = np.sqrt(var / N) / mean                       # 1.6e-6
+    assert abs(r.mean - mean) / mean < 5 * se_rel + 2e-6     # + the fp32 compounding bias budget
+    assert abs(r.std - np.sqrt(var)) / np.sqrt(var) < 1e-4

@@ -16,11 +16,13 @@ python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/pla
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_c2.csv \
     python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_bench.log 2>&1
 for m in gaussian bootstrap bootstrap_compat; do
-  python tools/run_one.py $m 20000000 360 > gpurun_out/plain_$m.log 2>&1 &&
+  python tools/run_one.py $m 100000000 360 > gpurun_out/plain_$m.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:mc_kernel -s 1 -c 1 -f -o gpurun_out/prof_$m \
-      python tools/run_one.py $m 20000000 360 > gpurun_out/ncu_$m.log 2>&1
+      python tools/run_one.py $m 100000000 360 > gpurun_out/ncu_$m.log 2>&1
 done
-python tools/run_one.py sobol_gaussian 5000000 1000 > gpurun_out/plain_sobol_gaussian.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:mc_kernel -s 1 -c 1 -f -o gpurun_out/prof_sobol_gaussian \
-    python tools/run_one.py sobol_gaussian 5000000 1000 > gpurun_out/ncu_sobol_gaussian.log 2>&1
+for m in sobol_gaussian sobol_bootstrap; do
+  python tools/run_one.py $m 5000000 1000 > gpurun_out/plain_$m.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k regex:mc_kernel -s 1 -c 1 -f -o gpurun_out/prof_$m \
+      python tools/run_one.py $m 5000000 1000 > gpurun_out/ncu_$m.log 2>&1
+done
 ls -la gpurun_out

@@ -11,5 +11,5 @@ if "bootstrap" in mode:
 if mode == "bootstrap_compat":
     kw["seed"] = 0
 S.simulate(mode, 256 * 148 * 32, P, **kw)
-r = S.simulate(mode, N, P, hist_bins=100, want_block_partials=True, want_finals=len(sys.argv) > 4, **kw)
+r = S.simulate(mode, N, P, hist_bins=100, want_block_partials=not mode.startswith("sobol"), want_finals=len(sys.argv) > 4, **kw)
 print(mode, N, P, "ms", r.device_ms, "Tpm/s", N * P / r.device_ms / 1e9, "mean", r.mean, "std", r.std)

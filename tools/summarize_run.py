@@ -41,7 +41,22 @@ for r in rows[1:]:
 tot = sum(sum(v) for v in agg.values())
 for k, v in agg.items():
     print(f"{len(v):3d} x {k[:90]:90s} avg {sum(v) / len(v):10.1f} us  share {100 * sum(v) / tot:5.2f}%")
-for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian"]:
-    print(f"\n## ncu --set full --clock-control none: python tools/run_one.py {m} (20M x 360; sobol 5M x 1000)")
+traffic = {}
+for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian", "sobol_bootstrap"]:
+    if not os.path.exists(f"{G}/prof_{m}.ncu-rep"):
+        continue
+    print(f"\n## ncu --set full --clock-control none: python tools/run_one.py {m} (the bench launch: 100M x 360; sobol 5M x 1000)")
     sys.stdout.flush()
     subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "ncu_summary.py"), f"{G}/prof_{m}.ncu-rep"])
+    raw = subprocess.run(["ncu", "-i", f"{G}/prof_{m}.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units, vals = rows[0], rows[1], rows[2]
+    tot = 0.0
+    for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        i = hdr.index(k)
+        v = float(vals[i].replace(",", ""))
+        tot += v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[units[i]]
+    traffic[m] = int(tot)
+# dram bytes (read + write) of the simulation kernel per launch at the bench size: bench.py's roofline.traffic
+json.dump({"source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch of the bench workload",
+           "bytes_per_launch": traffic}, open("profiles/ncu_traffic.json", "w"), indent=1)
