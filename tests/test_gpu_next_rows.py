@@ -252,3 +252,37 @@ def test_c5_size_ten_billion_paths_closed_form_moments(S):
     se_rel = np.sqrt(var / N) / mean                       # 1.6e-6
     assert abs(r.mean - mean) / mean < 5 * se_rel + 2e-6     # + the fp32 compounding bias budget
     assert abs(r.std - np.sqrt(var)) / np.sqrt(var) < 1e-4
+
+
+def test_fused_benchmark_program_prints_the_reference_programs_statistics(S, O, table1127, tmp_path):
+    """examples/benchmark_mc_fused.cpp: the reference's benchmark CLI on the fused entry points -- same mean / std /
+    count-below lines as examples/benchmark_mc_gpu.cpp computes on the host from N finals, plus exact quartiles"""
+    import os
+    import re
+    import subprocess
+    from conftest import ROOT
+    from stock_market_monte_carlo_b200 import _native
+    libdir = os.path.dirname(_native.LIB_PATH)
+    exe = tmp_path / "benchmark_mc_fused"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", str(exe), os.path.join(ROOT, "examples", "benchmark_mc_fused.cpp"),
+                    f"-I{ROOT}/include", f"-L{libdir}", "-lsmmc", f"-Wl,-rpath,{libdir}"], check=True)
+    (tmp_path / "data").mkdir()
+    with open(tmp_path / "data" / "SP500_monthly_returns.csv", "w") as f:
+        f.write("Date,returns\n")
+        for x in table1127:
+            f.write(f"1900-01-01,{float(x)!r}\n")
+    N, P = 200_000, 360
+    out = subprocess.run([str(exe), "1", str(P), str(N)], cwd=tmp_path, capture_output=True, text=True, check=True).stdout
+    fin = O.simulate("bootstrap_compat", N, P, returns=table1127, want_finals=True).finals
+    mean, std = map(float, re.search(r"mean: ([\d.]+) \| std: ([\d.]+)", out).groups())
+    x = fin.astype(np.float64)
+    assert abs(mean - x.mean()) <= 0.006 + 1e-6 * x.mean() and abs(std - x.std()) <= 0.006 + 1e-5 * x.std()
+    below = int(re.search(r"count_below [\d.]+: (\d+)", out).group(1))
+    assert below == int((fin < np.float32(1000.0)).sum())
+    q = [float(v) for v in re.search(r"min: ([\d.]+) \| Q1: ([\d.]+) \| median: ([\d.]+) \| Q3: ([\d.]+) \| max: ([\d.]+)", out).groups()]
+    want = np.sort(fin)[S.quartile_ranks(N)].astype(np.float64)
+    np.testing.assert_allclose(q, want, rtol=0, atol=0.006 + 1e-7 * want.max())
+    out = subprocess.run([str(exe), "1", "120", "100000", "gaussian", "7"], cwd=tmp_path, capture_output=True, text=True,
+                         check=True).stdout
+    g = S.simulate("gaussian", 100_000, 120, seed=7)
+    assert abs(float(re.search(r"mean: ([\d.]+)", out).group(1)) - g.mean) < 0.006
