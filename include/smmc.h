@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SMMC_ABI_VERSION 1
+#define SMMC_ABI_VERSION 2
 #define SMMC_BLOCK 256          /* logical block = THREADS_PER_BLOCK of the reference (src/simulations.cu:17) */
 #define SMMC_MAX_HIST_BINS 4096
 
@@ -81,6 +81,13 @@ typedef struct smmc_config {
   int32_t device;              /* CUDA device ordinal */
   uint32_t flags;
   void *stream;                /* cudaStream_t (DEVICE_POINTERS only; NULL = legacy default stream) */
+  /* ---- ABI 2: per-period withdrawals (the reference README's open "withdrawal strategies" item, README.md:130-133).
+   * After the return of period m:  value <- max(value * (1 - pct_m/100) - withdraw_fixed, 0);  0 is absorbing.
+   * All zero / NULL = no withdrawals: the default kernels, results bit-identical to ABI 1. */
+  float withdraw_fixed;        /* fixed amount taken out every period (unit of initial_capital) */
+  float withdraw_pct;          /* percent of the value taken out every period */
+  const float *withdraw_pct_schedule; /* optional [n_periods] percent per period (overrides withdraw_pct);
+                                         always a HOST pointer, copied by the call */
 } smmc_config;
 
 /* Device-side reduced statistics, laid out as doubles so that ONE sum-allreduce (ncclFloat64) over

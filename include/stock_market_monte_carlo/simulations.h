@@ -57,6 +57,11 @@ struct Options {
   float target = -1.0f;               // < 0: use initial_capital (reference examples/benchmark_mc_gpu.cpp:79)
   int hist_bins = 0;
   float hist_lo = 0.0f, hist_hi = 0.0f;
+  // withdrawals after every period (reference README.md:130-133, unimplemented there): value <- max(value *
+  // (1 - pct/100) - withdraw_fixed, 0); withdraw_pct_schedule (one percent per period) overrides withdraw_pct
+  float withdraw_fixed = 0.0f;
+  float withdraw_pct = 0.0f;
+  const std::vector<float> *withdraw_pct_schedule = nullptr;
 };
 
 struct Statistics {

@@ -71,11 +71,11 @@ def load():
 
 def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
              gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
-             want_finals=False, want_block_partials=False) -> Result:
+             want_finals=False, want_block_partials=False, **withdrawals) -> Result:
     """Same signature and result as stock_market_monte_carlo_b200.simulate, computed by the CPU oracle."""
     lib = load()
     cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
-                            gauss_mean, gauss_std, target, hist_bins, hist_range)
+                            gauss_mean, gauss_std, target, hist_bins, hist_range, **withdrawals)
     res = N.SmmcResult()
     out = Result()
     nb = (int(n_simulations) + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
@@ -110,11 +110,11 @@ def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0):
 
 
 def trajectories(mode, n_paths, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
-                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False):
+                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False, **withdrawals):
     """Same contract as stock_market_monte_carlo_b200.trajectories, computed by the CPU oracle."""
     lib = load()
     cfg, keep = make_config(mode, n_paths, n_periods, initial_capital, returns, seed, stream_offset, gauss_mean,
-                            gauss_std)
+                            gauss_std, **withdrawals)
     values = np.zeros((int(n_paths), int(n_periods) + 1), dtype=np.float32)
     rets = np.zeros((int(n_paths), int(n_periods)), dtype=np.float32) if want_returns else None
     if lib.orc_trajectories(C.byref(cfg), int(n_paths), values.ctypes.data,

@@ -233,9 +233,29 @@ typedef struct run_consts {
   gauss_consts gc;
   float sigma_sqrt2; /* (float)(sqrt(2) * (double)(std * 0.01f)) */
   const uint32_t *shift; /* per-month Sobol digital shift */
+  const float *flow_q;   /* per-month keep-fraction 1 - pct/100 of the withdrawal schedule, NULL = no withdrawals */
+  float flow_w;          /* fixed amount per period */
 } run_consts;
 
 /* draws[m] (optional) receives the table index (bootstrap modes) or the raw word (gaussian modes) of month m */
+/* withdrawals (include/smmc.h, ABI 2): after month m's return, value <- max(value * q_m - w, 0), one FFMA + one max,
+ * as the device's Flow<true> computes it */
+static float apply_flow(const run_consts *rc, float v, int m) {
+  if (!rc->flow_q) return v;
+  return fmaxf(fmaf(v, rc->flow_q[m], -rc->flow_w), 0.0f);
+}
+
+static float *build_flow(const smmc_config *cfg) {
+  if (cfg->withdraw_fixed == 0.0f && cfg->withdraw_pct == 0.0f && !cfg->withdraw_pct_schedule) return NULL;
+  int P = cfg->n_periods;
+  float *q = (float *)malloc((size_t)(P > 0 ? P : 1) * sizeof(float));
+  for (int m = 0; m < P; m++) {
+    float pct = cfg->withdraw_pct_schedule ? cfg->withdraw_pct_schedule[m] : cfg->withdraw_pct;
+    q[m] = 1.0f - pct * 0.01f;
+  }
+  return q;
+}
+
 /* values[0..P] (optional): V0 and the value after every month; rets[m] (optional): that month's return in percent */
 static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *draws, float *values, float *rets) {
   const smmc_config *cfg = rc->cfg;
@@ -250,7 +270,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
         state = orc_xorshift(state);
         int32_t idx = orc_compat_index(state, n);
         if (draws) draws[m] = (uint32_t)idx;
-        total = fmaf(total, rc->tbl[idx], total); /* total += total * r, one FFMA (reference SASS) */
+        total = apply_flow(rc, fmaf(total, rc->tbl[idx], total), m); /* total += total * r, one FFMA (reference SASS) */
         if (values) values[m + 1] = total;
         if (rets) rets[m] = idx < n ? rc->raw[idx] : 0.0f;
       }
@@ -262,7 +282,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
         if (j == 0) stream_words(path, (uint32_t)(m / 6), TAG_BOOTSTRAP, cfg->seed, w);
         uint32_t idx = boot_index(w, j, (uint32_t)n);
         if (draws) draws[m] = idx;
-        total = fmaf(total, rc->tbl[idx], total);
+        total = apply_flow(rc, fmaf(total, rc->tbl[idx], total), m);
         if (values) values[m + 1] = total;
         if (rets) rets[m] = rc->raw[idx];
       }
@@ -275,7 +295,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
         if (j == 0) stream_words(path, (uint32_t)(m / 8), TAG_GAUSSIAN, cfg->seed, w);
         if ((j & 1) == 0) gauss_pair(w[j >> 1], rc->gc, &g[0], &g[1]);
         if (draws) draws[m] = (j & 1) ? w[j >> 1] * 0x9E3779B1u : (w[j >> 1] & 0xFFFFFu); /* radius field | hashed angle word */
-        total = total * g[j & 1];
+        total = apply_flow(rc, total * g[j & 1], m);
         if (values) values[m + 1] = total;
         if (rets) rets[m] = (g[j & 1] - 1.0f) * 100.0f;
       }
@@ -285,7 +305,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
         uint32_t x = orc_sobol_point(path + SOBOL_SKIP, m) ^ rc->shift[m];
         uint32_t idx = (uint32_t)(((uint64_t)x * (uint32_t)n) >> 32);
         if (draws) draws[m] = idx;
-        total = fmaf(total, rc->tbl[idx], total);
+        total = apply_flow(rc, fmaf(total, rc->tbl[idx], total), m);
         if (values) values[m + 1] = total;
         if (rets) rets[m] = rc->raw[idx];
       }
@@ -295,7 +315,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
         uint32_t x = orc_sobol_point(path + SOBOL_SKIP, m) ^ rc->shift[m];
         if (draws) draws[m] = x;
         float gm = fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
-        total = total * gm;
+        total = apply_flow(rc, total * gm, m);
         if (values) values[m + 1] = total;
         if (rets) rets[m] = (gm - 1.0f) * 100.0f;
       }
@@ -428,6 +448,9 @@ int orc_run(const smmc_config *cfg, smmc_result *out) {
   if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
     for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);
   rc.shift = shift;
+  float *flowq = build_flow(cfg);
+  rc.flow_q = flowq;
+  rc.flow_w = cfg->withdraw_fixed;
 
   const float inv_w = bins > 0 ? orc_hist_inv_width(cfg->hist_lo, cfg->hist_hi, bins) : 0.0f;
   uint64_t *hist = (uint64_t *)calloc((size_t)bins + 2, sizeof(uint64_t));
@@ -486,6 +509,7 @@ int orc_run(const smmc_config *cfg, smmc_result *out) {
   free(bmean);
   free(bm2);
   free(shift);
+  free(flowq);
   free(tbl);
   return 0;
 }
@@ -505,8 +529,12 @@ int orc_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
   if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
     for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);
   rc.shift = shift;
+  float *flowq = build_flow(cfg);
+  rc.flow_q = flowq;
+  rc.flow_w = cfg->withdraw_fixed;
   for (int32_t p = 0; p < n_paths; p++) simulate_path(&rc, cfg->stream_offset + (uint64_t)p, outbuf + (size_t)p * P);
   free(shift);
+  free(flowq);
   free(tbl);
   return 0;
 }
@@ -535,10 +563,14 @@ int orc_trajectories(const smmc_config *cfg, int32_t n_paths, float *values, flo
   if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN)
     for (int m = 0; m < P; m++) shift[m] = sobol_shift(m, cfg->seed);
   rc.shift = shift;
+  float *flowq = build_flow(cfg);
+  rc.flow_q = flowq;
+  rc.flow_w = cfg->withdraw_fixed;
   for (int32_t p = 0; p < n_paths; p++)
     simulate_path_full(&rc, cfg->stream_offset + (uint64_t)p, NULL, values + (size_t)p * (P + 1),
                        returns_pct ? returns_pct + (size_t)p * P : NULL);
   free(shift);
+  free(flowq);
   free(raw);
   free(tbl);
   return 0;

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libsmmc.so")
 
-SMMC_ABI_VERSION = 1
+SMMC_ABI_VERSION = 2
 SMMC_BLOCK = 256
 SMMC_STATS_HEADER = 6
 SMMC_MAX_HIST_BINS = 4096
@@ -54,6 +54,9 @@ class SmmcConfig(C.Structure):
         ("device", C.c_int32),
         ("flags", C.c_uint32),
         ("stream", C.c_void_p),
+        ("withdraw_fixed", C.c_float),
+        ("withdraw_pct", C.c_float),
+        ("withdraw_pct_schedule", C.c_void_p),
     ]
 
 

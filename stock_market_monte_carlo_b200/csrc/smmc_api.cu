@@ -85,7 +85,8 @@ struct Context {
   // ring of event pairs around the simulation kernel of the last kEventRing launches (smmc_kernel_times)
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
-  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift, selhist;
+  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift, selhist, flow;
+  std::vector<float> flow_host;  // keep-fractions of the last withdrawal schedule uploaded
   int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
   uint64_t sobol_seed = 0;
   bool sobol_full_ready = false;
@@ -147,6 +148,9 @@ smmc_status get_context(int device, Context **out) {
 bool is_bootstrap(int mode) {
   return mode == SMMC_MODE_BOOTSTRAP_COMPAT || mode == SMMC_MODE_BOOTSTRAP || mode == SMMC_MODE_SOBOL_BOOTSTRAP;
 }
+bool has_withdrawals(const smmc_config *cfg) {
+  return cfg->withdraw_fixed != 0.0f || cfg->withdraw_pct != 0.0f || cfg->withdraw_pct_schedule != nullptr;
+}
 bool is_sobol(int mode) { return mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN; }
 
 smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
@@ -171,6 +175,8 @@ smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
   }
   if (cfg->hist_bins < 0 || cfg->hist_bins > SMMC_MAX_HIST_BINS) return fail(SMMC_ERR_INVALID_ARG, "hist_bins out of range");
   if (cfg->hist_bins > 0 && !(cfg->hist_hi > cfg->hist_lo)) return fail(SMMC_ERR_INVALID_ARG, "hist_hi must be > hist_lo");
+  if (!std::isfinite(cfg->withdraw_fixed) || !std::isfinite(cfg->withdraw_pct))
+    return fail(SMMC_ERR_INVALID_ARG, "withdraw_fixed / withdraw_pct must be finite");
   if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !(cfg->flags & SMMC_FLAG_DEVICE_POINTERS))
     return fail(SMMC_ERR_INVALID_ARG, "SMMC_FLAG_NO_SYNC requires SMMC_FLAG_DEVICE_POINTERS");
   if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !out->stats_dev)
@@ -300,6 +306,28 @@ smmc_status prepare_sobol_full(Context *ctx, int n_periods, uint64_t seed, const
   return SMMC_OK;
 }
 
+// Per-period keep-fractions q[m] = 1 - pct_m/100 on the device (withdrawal variant of the kernels); null when the config
+// asks for no withdrawals.
+smmc_status prepare_flow(Context *ctx, const smmc_config *cfg, cudaStream_t st, smmc::KParams *p) {
+  p->flow_q = nullptr;
+  p->flow_w = 0.0f;
+  if (!has_withdrawals(cfg)) return SMMC_OK;
+  const int P = cfg->n_periods;
+  ctx->flow_host.resize((size_t)(P > 0 ? P : 1));
+  for (int m = 0; m < P; m++) {
+    const float pct = cfg->withdraw_pct_schedule ? cfg->withdraw_pct_schedule[m] : cfg->withdraw_pct;
+    if (!std::isfinite(pct)) return fail(SMMC_ERR_INVALID_ARG, "withdraw_pct_schedule[%d] is not finite", m);
+    ctx->flow_host[(size_t)m] = 1.0f - pct * 0.01f;
+  }
+  if (P == 0) ctx->flow_host[0] = 1.0f;
+  CU(ctx->flow.reserve(ctx->flow_host.size() * 4));
+  CU(cudaStreamSynchronize(st));  // a previous launch on this stream may still read the cached schedule
+  CU(cudaMemcpyAsync(ctx->flow.p, ctx->flow_host.data(), ctx->flow_host.size() * 4, cudaMemcpyHostToDevice, st));
+  p->flow_q = (const float *)ctx->flow.p;
+  p->flow_w = cfg->withdraw_fixed;
+  return SMMC_OK;
+}
+
 // one radix-select pass over the finals' ordered keys (smmc_select_pass / smmc_quantiles)
 struct SelectPass {
   int targets = 0;       // histograms kept by the kernel (1 in the first pass)
@@ -356,9 +384,10 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   const int variant = variant_from_env();
 
   smmc::LaunchInfo li;
-  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, N, ctx->n_sms, ctx->smem_optin,
-                         warps_from_env(), &li))
-    return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %zu bytes of shared memory", cfg->n_returns, ctx->smem_optin);
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, has_withdrawals(cfg), N, ctx->n_sms,
+                         ctx->smem_optin, warps_from_env(), &li))
+    return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries (+ histograms / schedules) does not fit in %zu bytes of shared memory",
+                cfg->n_returns, ctx->smem_optin);
 
   smmc::KParams p;
   memset(&p, 0, sizeof p);
@@ -458,6 +487,11 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   if (is_sobol(cfg->mode)) {
     smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p);
     if (sst != SMMC_OK) return sst;
+  }
+
+  {
+    smmc_status fst = prepare_flow(ctx, cfg, st, &p);
+    if (fst != SMMC_OK) return fst;
   }
 
   pd->sel_dev = nullptr;
@@ -884,6 +918,8 @@ smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *va
   const size_t vbytes = (size_t)n_paths * (size_t)(P + 1) * 4, rbytes = returns_pct ? (size_t)n_paths * (size_t)P * 4 : 0;
   CU(ctx->scratch.reserve(vbytes + rbytes + 16));
   float *vd = (float *)ctx->scratch.p, *rd = rbytes ? vd + (size_t)n_paths * (P + 1) : nullptr;
+  st = prepare_flow(ctx, cfg, s, &p);
+  if (st != SMMC_OK) return st;
   CU(smmc::launch_trajectories(cfg->mode, p, n_paths, tbl, raw, full_dev, shift_dev, vd, rd, s));
   CU(cudaMemcpyAsync(values, vd, vbytes, cudaMemcpyDeviceToHost, s));
   if (rbytes) CU(cudaMemcpyAsync(returns_pct, rd, rbytes, cudaMemcpyDeviceToHost, s));
@@ -907,8 +943,8 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
   if (!plan || n_sms < 1 || select_targets < 0 || select_targets > SMMC_SELECT_MAX_TARGETS)
     return fail(SMMC_ERR_INVALID_ARG, "plan_launch: bad arguments");
   smmc::LaunchInfo li;
-  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, cfg->n_simulations, n_sms,
-                         (size_t)smem_optin, warps_from_env(), &li))
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, has_withdrawals(cfg),
+                         cfg->n_simulations, n_sms, (size_t)smem_optin, warps_from_env(), &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %llu bytes of shared memory", cfg->n_returns,
                 (unsigned long long)smem_optin);
   plan->grid = li.grid;
@@ -1009,6 +1045,7 @@ void smmc_shutdown(void) {
     c.bvars.release();
     c.scratch.release();
     c.selhist.release();
+    c.flow.release();
     if (c.stats_host) cudaFreeHost(c.stats_host);
     c.stats_host = nullptr;
     c.stats_host_cap = 0;

@@ -37,6 +37,13 @@ smmc_config base_config(long N, int n_periods, float initial_capital, std::vecto
   c.hist_bins = opt.hist_bins;
   c.hist_lo = opt.hist_lo;
   c.hist_hi = opt.hist_hi;
+  c.withdraw_fixed = opt.withdraw_fixed;
+  c.withdraw_pct = opt.withdraw_pct;
+  if (opt.withdraw_pct_schedule) {
+    if ((long)opt.withdraw_pct_schedule->size() != (long)n_periods)
+      throw std::invalid_argument("withdraw_pct_schedule needs one entry per period");
+    c.withdraw_pct_schedule = opt.withdraw_pct_schedule->data();
+  }
   return c;
 }
 

@@ -57,12 +57,14 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
   float tot = p.v0;
   v[0] = tot;
   const int n = p.n_returns;
+  // withdrawals (same formula and order as Flow<true> in smmc_mc_kernel.cuh)
+  auto flow = [&](float x, int m) { return p.flow_q ? fmaxf(fmaf(x, __ldg(p.flow_q + m), -p.flow_w), 0.0f) : x; };
   if (mode == SMMC_MODE_BOOTSTRAP_COMPAT) {
     uint32_t st = rand_pcg(plo + 1u + p.compat_seed);
     for (int m = 0; m < P; m++) {
       st = xorshift(st);
       const int idx = (int)(__uint2float_rn(st) * p.idx_scale);
-      tot = fmaf(tot, tbl[idx], tot);
+      tot = flow(fmaf(tot, tbl[idx], tot), m);
       v[m + 1] = tot;
       if (rp) rp[m] = idx < n ? raw[idx] : 0.0f;
     }
@@ -76,7 +78,7 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
       }
       const float y = __fmaf_rz(__uint_as_float(mt[j]), j < 4 ? p.bc.c21 : p.bc.c22, j < 4 ? p.bc.k21 : p.bc.k22);
       const uint32_t idx = __float_as_uint(y) - 0x4B000000u;
-      tot = fmaf(tot, tbl[idx], tot);
+      tot = flow(fmaf(tot, tbl[idx], tot), m);
       v[m + 1] = tot;
       if (rp) rp[m] = raw[idx];
     }
@@ -88,7 +90,7 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
       if (j == 0) stream_words(plo, phi, (uint32_t)(m / kGaussMonthsPerCall), kTagGaussian, p.keys, w);
       if ((j & 1) == 0) gauss_pair(w[j >> 1], p.one, p.gc, g[0], g[1]);
       const float gm = g[j & 1];
-      tot = __fmul_rn(tot, gm);
+      tot = flow(__fmul_rn(tot, gm), m);
       v[m + 1] = tot;
       if (rp) rp[m] = __fmul_rn(__fsub_rn(gm, 1.0f), 100.0f);
     }
@@ -100,11 +102,11 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
       for (uint32_t gg = gray; gg; gg &= gg - 1u) x ^= sobol_full[m * 32 + (__ffs((int)gg) - 1)];
       if (mode == SMMC_MODE_SOBOL_BOOTSTRAP) {
         const uint32_t idx = __umulhi(x, (uint32_t)n);
-        tot = fmaf(tot, tbl[idx], tot);
+        tot = flow(fmaf(tot, tbl[idx], tot), m);
         if (rp) rp[m] = raw[idx];
       } else {
         const float gm = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);
-        tot = __fmul_rn(tot, gm);
+        tot = flow(__fmul_rn(tot, gm), m);
         if (rp) rp[m] = __fmul_rn(__fsub_rn(gm, 1.0f), 100.0f);
       }
       v[m + 1] = tot;
@@ -229,9 +231,10 @@ int plan_warps(int64_t n_paths, int n_sms) {
   return best;
 }
 
-bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, int64_t n_paths, int n_sms,
-                 size_t smem_optin, int warps_override, LaunchInfo *li) {
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, int64_t n_paths,
+                 int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li) {
   const uint32_t sel_bytes = (uint32_t)sel_targets * kSelectBins * 4u;
+  const uint32_t flow_bytes = withdrawals ? (uint32_t)n_periods * 4u : 0u;
   const bool sobol = (mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN);
   const uint32_t sob_bytes = sobol ? (uint32_t)(((n_periods + 31) & ~31) * 32) : 0u;
   const bool has_table = (mode == SMMC_MODE_BOOTSTRAP_COMPAT || mode == SMMC_MODE_BOOTSTRAP ||
@@ -244,12 +247,12 @@ bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_
     int rep = 32;
     for (; rep >= 1; rep >>= 1) {
       tbl_bytes = (uint32_t)((((size_t)(n_returns + 1) * rep * 4) + 15) & ~(size_t)15);
-      if (smem_layout(hist_bins, sel_bytes, sob_bytes, tbl_bytes).total <= smem_optin) break;
+      if (smem_layout(hist_bins, sel_bytes, flow_bytes, sob_bytes, tbl_bytes).total <= smem_optin) break;
     }
     if (rep < 1) return false;
     li->rep = rep;
   }
-  li->smem_bytes = smem_layout(hist_bins, sel_bytes, sob_bytes, tbl_bytes).total;
+  li->smem_bytes = smem_layout(hist_bins, sel_bytes, flow_bytes, sob_bytes, tbl_bytes).total;
   return li->smem_bytes <= smem_optin;
 }
 

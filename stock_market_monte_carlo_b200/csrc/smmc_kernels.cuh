@@ -55,6 +55,9 @@ struct KParams {
   int32_t sel_prefix_shift;     // prefix = key >> sel_prefix_shift; 32 = first pass (every key matches)
   uint32_t sel_prefix[kSelectMaxTargets];
   unsigned long long *sel_hist_g;  // [sel_targets][bins], zeroed before launch
+  // per-period withdrawals (null = none): value <- max(value * flow_q[m] - flow_w, 0) after month m's return
+  const float *flow_q;  // [n_periods] keep-fractions 1 - pct_m/100 (device)
+  float flow_w;         // fixed amount per period
 };
 
 // CTA shape of the simulation kernel and its dynamic shared-memory layout (shared by the planner and the kernel)
@@ -65,14 +68,16 @@ constexpr int kWarps = kThreads / 32;
 // [0,8) mbarrier | [16, 16+8*(bins+2)) histogram | warp partials | select-pass digit histograms (u32) |
 // Sobol low direction numbers | table (128-B aligned)
 struct SmemLayout {
-  uint32_t hist_off, wp_off, sel_off, sob_off, tbl_off, total;
+  uint32_t hist_off, wp_off, sel_off, flow_off, sob_off, tbl_off, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, uint32_t sob_bytes, uint32_t tbl_bytes) {
+__host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, uint32_t flow_bytes, uint32_t sob_bytes,
+                                                  uint32_t tbl_bytes) {
   SmemLayout L;
   L.hist_off = 16;
   L.wp_off = L.hist_off + 8u * (uint32_t)(bins + 2);
   L.sel_off = (L.wp_off + 32u * kWarps + 15u) & ~15u;
-  L.sob_off = (L.sel_off + sel_bytes + 127u) & ~127u;
+  L.flow_off = (L.sel_off + sel_bytes + 15u) & ~15u;
+  L.sob_off = (L.flow_off + flow_bytes + 127u) & ~127u;
   L.tbl_off = (L.sob_off + sob_bytes + 127u) & ~127u;
   L.total = L.tbl_off + tbl_bytes;
   return L;
@@ -89,8 +94,8 @@ struct LaunchInfo {
 
 // Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
 // Also picks the warps per CTA for `n_paths` (warps_override in 1..32 forces it; 0 = automatic).
-bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, int64_t n_paths, int n_sms,
-                 size_t smem_optin, int warps_override, LaunchInfo *li);
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, int64_t n_paths,
+                 int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li);
 
 // Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
 void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);

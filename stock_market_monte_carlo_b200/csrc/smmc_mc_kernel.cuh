@@ -47,6 +47,20 @@ __device__ __forceinline__ float tree_sum_256(const float (&s)[8]) {
 
 // ---- one sub-batch of ILP paths through all P months ------------------------------------------------------------
 
+// ---- per-period withdrawals (the reference README's open "withdrawal strategies" item, README.md:130-133) -------------
+// After the month's return: value <- max(value * q_m - w, 0), q_m = 1 - (percent taken out in month m)/100 read from a
+// shared-memory schedule, w = fixed amount; 0 is absorbing (a ruined fund stays ruined).  FLOW = false compiles to
+// nothing: the default kernels are unchanged.
+template <bool FLOW>
+struct Flow {
+  const float *q;
+  float w;
+  __device__ __forceinline__ float operator()(float v, int m) const {
+    if (!FLOW) return v;
+    return fmaxf(fmaf(v, q[m], -w), 0.0f);
+  }
+};
+
 // `base` = shared-window address of this lane's column of the table (smem_u32(tbl) + lane_off): the row address is
 // then ONE IMAD (idx * row_bytes + base) feeding a plain LDS
 __device__ __forceinline__ float lds_f32(uint32_t addr) {
@@ -55,8 +69,9 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
   return r;
 }
 
-template <int ILP>
-__device__ __forceinline__ void run_compat(const KParams &p, uint32_t base, const uint32_t (&plo)[ILP], float (&tot)[ILP]) {
+template <int ILP, bool FLOW>
+__device__ __forceinline__ void run_compat(const KParams &p, const Flow<FLOW> &fl, uint32_t base, const uint32_t (&plo)[ILP],
+                                           float (&tot)[ILP]) {
   uint32_t st[ILP];
 #pragma unroll
   for (int i = 0; i < ILP; i++) st[i] = rand_pcg(plo[i] + 1u + p.compat_seed);
@@ -70,7 +85,7 @@ __device__ __forceinline__ void run_compat(const KParams &p, uint32_t base, cons
       // reference: idx = n * (state * 2^-32f), truncated (src/simulations.cu:148); one rounding either way
       const int idx = (int)(__uint2float_rn(st[i]) * scale);
       const float r = lds_f32((uint32_t)idx * rep4 + base);
-      tot[i] = fmaf(tot[i], r, tot[i]);  // total += total * r (one FFMA, as the reference compiles)
+      tot[i] = fl(fmaf(tot[i], r, tot[i]), m);  // total += total * r (one FFMA, as the reference compiles)
     }
   }
 }
@@ -81,9 +96,9 @@ __device__ __forceinline__ float boot_step(float tot, uint32_t w, uint32_t nr4, 
 }
 
 // months 6q..6q+5 of ILP paths: one Philox call each, six table gathers, six FFMAs
-template <int ILP, int SHIFT>
-__device__ __forceinline__ void run_bootstrap(const KParams &p, uint32_t base, const uint32_t (&plo)[ILP],
-                                              uint32_t phi, float (&tot)[ILP]) {
+template <int ILP, int SHIFT, bool FLOW>
+__device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW> &fl, uint32_t base,
+                                              const uint32_t (&plo)[ILP], uint32_t phi, float (&tot)[ILP]) {
   const BootConsts bc = p.bc;
   const uint32_t one = p.one;
   const int nq = p.n_periods / kFieldsPerCall;
@@ -97,7 +112,7 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, uint32_t base, c
 #pragma unroll
       for (int j = 0; j < 6; j++) {
         const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
-        tot[i] = fmaf(tot[i], r, tot[i]);
+        tot[i] = fl(fmaf(tot[i], r, tot[i]), q * kFieldsPerCall + j);
       }
     }
   }
@@ -112,16 +127,16 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, uint32_t base, c
       for (int j = 0; j < 5; j++)
         if (j < rem) {
           const float r = boot_load<SHIFT>(m[j], j < 4 ? bc.c21 : bc.c22, j < 4 ? bc.k21 : bc.k22, base, bc.row_shift);
-          tot[i] = fmaf(tot[i], r, tot[i]);
+          tot[i] = fl(fmaf(tot[i], r, tot[i]), nq * kFieldsPerCall + j);
         }
     }
   }
 }
 
 // months 8q..8q+7 of ILP paths: one Philox call each, four Box-Muller pairs
-template <int ILP>
-__device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&plo)[ILP], uint32_t phi,
-                                             float (&tot)[ILP]) {
+template <int ILP, bool FLOW>
+__device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> &fl, const uint32_t (&plo)[ILP],
+                                             uint32_t phi, float (&tot)[ILP]) {
   const GaussConsts gc = p.gc;
   const uint32_t one = p.one;
   const int nq = p.n_periods / kGaussMonthsPerCall;
@@ -135,7 +150,8 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
       for (int j = 0; j < 4; j++) {
         float g0, g1;
         gauss_pair(w[j], one, gc, g0, g1);
-        tot[i] = __fmul_rn(__fmul_rn(tot[i], g0), g1);
+        const int m = q * kGaussMonthsPerCall + 2 * j;
+        tot[i] = fl(__fmul_rn(fl(__fmul_rn(tot[i], g0), m), g1), m + 1);
       }
     }
   }
@@ -149,8 +165,9 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
       for (int j = 0; j < 4; j++) {
         float g0, g1;
         gauss_pair(w[j], one, gc, g0, g1);
-        if (2 * j < rem) tot[i] = __fmul_rn(tot[i], g0);
-        if (2 * j + 1 < rem) tot[i] = __fmul_rn(tot[i], g1);
+        const int m = nq * kGaussMonthsPerCall + 2 * j;
+        if (2 * j < rem) tot[i] = fl(__fmul_rn(tot[i], g0), m);
+        if (2 * j + 1 < rem) tot[i] = fl(__fmul_rn(tot[i], g1), m + 1);
       }
     }
   }
@@ -162,8 +179,8 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const uint32_t (&
 // h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
-template <int MODE>
-__device__ __forceinline__ void run_sobol(const KParams &p, uint32_t tbl_base, const uint4 *vlo,
+template <int MODE, bool FLOW>
+__device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, uint32_t tbl_base, const uint4 *vlo,
                                           uint32_t h, uint32_t lane, float (&tot)[8]) {
   const uint32_t mk0 = ((lane ^ (lane >> 1)) & 1u) ? 0xffffffffu : 0u;
   const uint32_t mk1 = (((lane >> 1) ^ (lane >> 2)) & 1u) ? 0xffffffffu : 0u;
@@ -211,8 +228,8 @@ __device__ __forceinline__ void run_sobol(const KParams &p, uint32_t tbl_base, c
       x[7] = base ^ vb.x ^ vb.w;
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = boot_step(tot[j], x[j], nr4, row_mask, tbl_base);
-        else tot[j] = __fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a));
+        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
+        else tot[j] = fl(__fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a)), m0 + mi);
       }
     }
   }
@@ -220,18 +237,19 @@ __device__ __forceinline__ void run_sobol(const KParams &p, uint32_t tbl_base, c
 
 // ---- the fused persistent kernel ---------------------------------------------------------------------------------
 
-template <int MODE, int ILP, int SHIFT>
+template <int MODE, int ILP, int SHIFT, bool FLOW>
 __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr bool kHasTable = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT || MODE == SMMC_MODE_BOOTSTRAP ||
                               MODE == SMMC_MODE_SOBOL_BOOTSTRAP);
   constexpr bool kSobol = (MODE == SMMC_MODE_SOBOL_BOOTSTRAP || MODE == SMMC_MODE_SOBOL_GAUSSIAN);
-  const SmemLayout L = smem_layout(p.hist_bins, (uint32_t)p.sel_targets * kSelectBins * 4u, kSobol ? p.sobol_lo_bytes : 0u,
-                                   kHasTable ? p.tbl_bytes : 0u);
+  const SmemLayout L = smem_layout(p.hist_bins, (uint32_t)p.sel_targets * kSelectBins * 4u, FLOW ? (uint32_t)p.n_periods * 4u : 0u,
+                                   kSobol ? p.sobol_lo_bytes : 0u, kHasTable ? p.tbl_bytes : 0u);
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
   unsigned long long *hist_s = reinterpret_cast<unsigned long long *>(smem + L.hist_off);
   double *wp = reinterpret_cast<double *>(smem + L.wp_off);
   unsigned int *sel_s = reinterpret_cast<unsigned int *>(smem + L.sel_off);
+  float *flow_s = reinterpret_cast<float *>(smem + L.flow_off);
   const char *tbl = reinterpret_cast<const char *>(smem + L.tbl_off);
   const uint4 *vlo = reinterpret_cast<const uint4 *>(smem + L.sob_off);
 
@@ -261,6 +279,9 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   }
   for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x) hist_s[i] = 0ull;
   for (int i = tid; i < p.sel_targets * kSelectBins; i += (int)blockDim.x) sel_s[i] = 0u;
+  if (FLOW)
+    for (int i = tid; i < p.n_periods; i += (int)blockDim.x) flow_s[i] = __ldg(p.flow_q + i);
+  const Flow<FLOW> fl = {flow_s, p.flow_w};
   __syncthreads();
   if (kHasTable || kSobol) mbar_wait(bar, 0);
 
@@ -287,7 +308,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     if (kSobol) {
 #pragma unroll
       for (int j = 0; j < kPathsPerLane; j++) x[j] = p.v0;
-      run_sobol<MODE>(p, lane_base, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
+      run_sobol<MODE, FLOW>(p, fl, lane_base, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
     }
 #pragma unroll
     for (int s = 0; s < (kSobol ? 0 : kPathsPerLane); s += ILP) {
@@ -298,9 +319,9 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
         plo[i] = base_lo + (uint32_t)((s + i) * 32) + lane;
         tot[i] = p.v0;
       }
-      if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP>(p, lane_base, plo, tot);
-      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT>(p, boot_base, plo, phi, tot);
-      if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP>(p, plo, phi, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP, FLOW>(p, fl, lane_base, plo, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT, FLOW>(p, fl, boot_base, plo, phi, tot);
+      if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP, FLOW>(p, fl, plo, phi, tot);
 #pragma unroll
       for (int i = 0; i < ILP; i++) x[s + i] = tot[i];
     }
@@ -442,13 +463,19 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     p.stats[SMMC_STATS_HEADER + i] = (double)__ldcg(&p.hist_g[i]);
 }
 
-template <int MODE, int ILP, int SHIFT = -1>
-cudaError_t launch_one(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP, SHIFT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <int MODE, int ILP, int SHIFT, bool FLOW>
+cudaError_t launch_flow(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
+  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP, SHIFT, FLOW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)li.smem_bytes);
   if (e != cudaSuccess) return e;
-  mc_kernel<MODE, ILP, SHIFT><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
+  mc_kernel<MODE, ILP, SHIFT, FLOW><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
   return cudaGetLastError();
+}
+
+// the withdrawal variant is a separate instantiation: the default kernels carry no trace of it
+template <int MODE, int ILP, int SHIFT = -1>
+cudaError_t launch_one(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
+  return p.flow_q ? launch_flow<MODE, ILP, SHIFT, true>(p, li, s) : launch_flow<MODE, ILP, SHIFT, false>(p, li, s);
 }
 
 }  // namespace

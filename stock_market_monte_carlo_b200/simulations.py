@@ -97,7 +97,8 @@ class Result:
 
 def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
                 gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None, device=0,
-                flags=0, stream=0, returns_ptr=None, n_returns=None):
+                flags=0, stream=0, returns_ptr=None, n_returns=None, withdraw_fixed=0.0, withdraw_pct=0.0,
+                withdraw_pct_schedule=None):
     cfg = N.SmmcConfig()
     cfg.abi_version = N.SMMC_ABI_VERSION
     cfg.mode = N.MODES[mode] if isinstance(mode, str) else int(mode)
@@ -124,16 +125,25 @@ def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=
     cfg.device = int(device)
     cfg.flags = int(flags)
     cfg.stream = int(stream) if stream else None
+    cfg.withdraw_fixed = float(withdraw_fixed)
+    cfg.withdraw_pct = float(withdraw_pct)
+    if withdraw_pct_schedule is not None:
+        sched = _as_f32(withdraw_pct_schedule)
+        if sched.size != int(n_periods):
+            raise ValueError("withdraw_pct_schedule needs one entry per period")
+        cfg.withdraw_pct_schedule = sched.ctypes.data
+        keep = (keep, sched)
     return cfg, keep
 
 
 def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
              gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
-             want_finals=False, want_block_partials=False, device=0, n_gpus=1) -> Result:
-    """One blocking run through `smmc_run` / `smmc_run_multi` with HOST buffers (the call a user makes)."""
+             want_finals=False, want_block_partials=False, device=0, n_gpus=1, **withdrawals) -> Result:
+    """One blocking run through `smmc_run` / `smmc_run_multi` with HOST buffers (the call a user makes).
+    withdrawals: withdraw_fixed=, withdraw_pct=, withdraw_pct_schedule= (include/smmc.h, ABI 2)."""
     lib = N.load()
     cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
-                            gauss_mean, gauss_std, target, hist_bins, hist_range, device)
+                            gauss_mean, gauss_std, target, hist_bins, hist_range, device, **withdrawals)
     res = N.SmmcResult()
     out = Result()
     nb = (int(n_simulations) + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
@@ -166,7 +176,7 @@ def stats_len(hist_bins):
 def simulate_device(mode, n_simulations, n_periods, stats_ptr, initial_capital=1000.0, returns_ptr=None,
                     n_returns=0, seed=0, stream_offset=0, gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None,
                     hist_bins=0, hist_range=None, finals_ptr=None, block_means_ptr=None, block_vars_ptr=None,
-                    device=0, stream=0):
+                    device=0, stream=0, **withdrawals):
     """Asynchronous run over DEVICE pointers on `stream` (e.g. torch tensors' data_ptr() and torch's current
     stream).  Nothing is synchronised; `stats_ptr` (stats_len(hist_bins) float64 on the device) receives the
     allreduce-ready statistics vector described in include/smmc.h.  Returns the number of kernels launched."""
@@ -174,7 +184,7 @@ def simulate_device(mode, n_simulations, n_periods, stats_ptr, initial_capital=1
     cfg, _ = make_config(mode, n_simulations, n_periods, initial_capital, None, seed, stream_offset, gauss_mean,
                          gauss_std, target, hist_bins, hist_range, device,
                          flags=N.FLAG_DEVICE_POINTERS | N.FLAG_NO_SYNC, stream=stream,
-                         returns_ptr=returns_ptr, n_returns=n_returns)
+                         returns_ptr=returns_ptr, n_returns=n_returns, **withdrawals)
     res = N.SmmcResult()
     res.stats_dev = int(stats_ptr)
     res.finals = int(finals_ptr) if finals_ptr else None
@@ -264,13 +274,14 @@ def quartile_ranks(n):
 
 
 def quantiles(mode, n_simulations, n_periods, ranks=None, initial_capital=1000.0, returns=None, seed=0,
-              stream_offset=0, gauss_mean=0.5, gauss_std=10.0 / 12.0, device=0, n_gpus=1, return_ms=False):
+              stream_offset=0, gauss_mean=0.5, gauss_std=10.0 / 12.0, device=0, n_gpus=1, return_ms=False,
+              **withdrawals):
     """sorted(finals)[ranks] of the run, exactly, without materialising the finals: three replays of the
     counter-based simulation drive a radix select in shared memory (`smmc_quantiles`).  ranks=None gives the
     reference's five quartile ranks."""
     lib = N.load()
     cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
-                            gauss_mean, gauss_std, device=device)
+                            gauss_mean, gauss_std, device=device, **withdrawals)
     r = np.ascontiguousarray(np.asarray(quartile_ranks(n_simulations) if ranks is None else ranks, dtype=np.uint64))
     out = np.zeros(r.size, dtype=np.float32)
     ms = C.c_float()
@@ -319,13 +330,13 @@ class SelectState:
 
 
 def trajectories(mode, n_paths, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
-                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False, device=0):
+                 gauss_mean=0.5, gauss_std=10.0 / 12.0, want_returns=False, device=0, **withdrawals):
     """values[n_paths][n_periods+1] (and the monthly returns in percent [n_paths][n_periods]) of paths
     stream_offset .. stream_offset+n_paths-1: the reference's `mc_data` of mc_simulations_keepdata
     (src/simulations.cpp:139-202), from the same RNG streams as the statistics kernel."""
     lib = N.load()
     cfg, keep = make_config(mode, n_paths, n_periods, initial_capital, returns, seed, stream_offset, gauss_mean,
-                            gauss_std, device=device)
+                            gauss_std, device=device, **withdrawals)
     values = np.zeros((int(n_paths), int(n_periods) + 1), dtype=np.float32)
     rets = np.zeros((int(n_paths), int(n_periods)), dtype=np.float32) if want_returns else None
     N.check(lib.smmc_trajectories(C.byref(cfg), int(n_paths), values.ctypes.data,
