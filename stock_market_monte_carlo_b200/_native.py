@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libsmmc.so")
+LIB_PATH = os.environ.get("SMMC_LIB") or os.path.join(_HERE, "lib", "libsmmc.so")  # SMMC_LIB: development override
 
 SMMC_ABI_VERSION = 2
 SMMC_BLOCK = 256

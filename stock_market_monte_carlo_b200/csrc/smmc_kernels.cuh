@@ -61,7 +61,10 @@ struct KParams {
 };
 
 // CTA shape of the simulation kernel and its dynamic shared-memory layout (shared by the planner and the kernel)
-constexpr int kThreads = 1024;
+#ifndef SMMC_MAX_THREADS
+#define SMMC_MAX_THREADS 1024
+#endif
+constexpr int kThreads = SMMC_MAX_THREADS;
 constexpr int kWarps = kThreads / 32;
 
 // shared memory layout (dynamic):
