@@ -51,7 +51,7 @@ UNIT = "path-months/s"
 # 4 draws per Philox call + IMAD.HI index) and 22 (gaussian: 2 normals per 2 words); the shipped recipes draw 6
 # fields / 8 normals per call and need 12, so the fraction below stays an issue-slot utilisation (<= 1).  The
 # SURVEY-budget fraction is reported next to it as `frac_survey_budget`.
-I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 24}
+I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 20}
 # Pipe floors (cycles per warp-month per SM sub-partition) from the measured reciprocal throughputs in
 # profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the binding
 # resource of these instruction mixes is a pipe, not the issue slot.

@@ -192,13 +192,13 @@ static uint32_t sobol_shift(int32_t dim, uint64_t seed) {
  * Central/tail split of Giles' erfinv approximation ("Approximating the erfinv function", GPU Gems 2012),
  * evaluated with explicit fmaf so that host and device agree up to the log2/sqrt approximations. */
 static float normal_icdf(uint32_t x32) { /* returns z / sqrt(2) */
-  /* u in (0,1), symmetric about 0.5:  u = (x + 0.5) * 2^-32;   z = sqrt(2) * erfinv(2u - 1) */
-  float y = fmaf((float)(int32_t)(x32 ^ 0x80000000u), 4.6566128730773926e-10f, 2.3283064365386963e-10f); /* 2u-1 */
-  float t = fmaxf(fmaf(-y, y, 1.0f), 5.9604645e-08f); /* 1 - y^2, clamped at 2^-24 so |y| = 1 stays finite */
-  float w = log2f(t) * -0.69314718055994530942f;
+  /* u in (0,1), symmetric about 0.5:  u = (x + 0.5) * 2^-32;  y = (2u - 1)(1 - 2^-23): |y| <= 1 - 2^-23, so
+   * 1 - y^2 >= 2^-22 for every word (no clamp);  z = sqrt(2) * erfinv(y).  Constants are the device's, digit for digit. */
+  float y = fmaf((float)(int32_t)(x32 ^ 0x80000000u), 4.6566123179654e-10f, 2.3283064365386963e-10f);
+  float t = fmaf(-y, y, 1.0f);
+  float w = fmaf(log2f(t), -0.69314718055994530942f, -2.5f); /* w - 2.5 of Giles' central branch, one FFMA */
   float p;
-  if (w < 5.0f) {
-    w = w - 2.5f;
+  if (w < 2.5f) {
     p = 2.81022636e-08f;
     p = fmaf(p, w, 3.43273939e-07f);
     p = fmaf(p, w, -3.5233877e-06f);
@@ -209,7 +209,7 @@ static float normal_icdf(uint32_t x32) { /* returns z / sqrt(2) */
     p = fmaf(p, w, 0.246640727f);
     p = fmaf(p, w, 1.50140941f);
   } else {
-    w = sqrtf(w) - 3.0f;
+    w = sqrtf(w + 2.5f) - 3.0f;
     p = -0.000200214257f;
     p = fmaf(p, w, 0.000100950558f);
     p = fmaf(p, w, 0.00134934322f);

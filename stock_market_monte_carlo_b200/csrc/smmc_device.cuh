@@ -176,13 +176,19 @@ __device__ __forceinline__ void gauss_pair(uint32_t w, uint32_t one, const Gauss
 // ---- inverse normal CDF (SOBOL_GAUSSIAN) ----------------------------------------------------------------------
 // Giles, "Approximating the erfinv function" (GPU Computing Gems, 2012), single-precision central/tail split.
 // Returns p*y with z = sqrt(2) * p * y; the caller folds sqrt(2)*sigma into its FFMA.
-__device__ __forceinline__ float erfinv_py(uint32_t x32) {
-  const float y = fmaf(__int2float_rn((int)(x32 ^ 0x80000000u)), 4.6566128730773926e-10f, 2.3283064365386963e-10f);
-  const float t = fmaxf(fmaf(-y, y, 1.0f), 5.9604645e-08f);
-  float w = lg2_approx(t) * -0.69314718055994530942f;
+//   y = 2u - 1,  u = (x + 1/2) / 2^32, scaled by (1 - 2^-23) so that |y| <= 1 - 2^-23 and 1 - y^2 >= 2^-22 > 0 for every
+//       32-bit word (no clamp, no special case; the scaling moves z by < 1.2e-7 relative);
+//   w - 2.5 = fma(lg2(1 - y^2), -ln 2, -2.5) feeds the central polynomial directly (one FFMA instead of FMUL + FADD).
+// `xs` is the Sobol word with its top bit flipped (x ^ 0x80000000) read as a signed integer: the simulation kernel gets
+// the flip for free from the per-month digital-shift row (smmc_api.cu, prepare_sobol), the other callers apply it.
+constexpr float kIcdfScale = 4.6566123179654e-10f;   // 2^-31 (1 - 2^-23)
+constexpr float kIcdfOffset = 2.3283064365386963e-10f;  // 2^-32
+__device__ __forceinline__ float erfinv_py_signed(int32_t xs) {
+  const float y = fmaf(__int2float_rn(xs), kIcdfScale, kIcdfOffset);
+  const float t = fmaf(-y, y, 1.0f);
+  float w = fmaf(lg2_approx(t), -0.69314718055994530942f, -2.5f);
   float p;
-  if (w < 5.0f) {
-    w = w - 2.5f;
+  if (w < 2.5f) {
     p = 2.81022636e-08f;
     p = fmaf(p, w, 3.43273939e-07f);
     p = fmaf(p, w, -3.5233877e-06f);
@@ -193,7 +199,7 @@ __device__ __forceinline__ float erfinv_py(uint32_t x32) {
     p = fmaf(p, w, 0.246640727f);
     p = fmaf(p, w, 1.50140941f);
   } else {
-    w = sqrt_approx(w) - 3.0f;
+    w = sqrt_approx(w + 2.5f) - 3.0f;
     p = -0.000200214257f;
     p = fmaf(p, w, 0.000100950558f);
     p = fmaf(p, w, 0.00134934322f);
@@ -206,6 +212,7 @@ __device__ __forceinline__ float erfinv_py(uint32_t x32) {
   }
   return p * y;
 }
+__device__ __forceinline__ float erfinv_py(uint32_t x32) { return erfinv_py_signed((int32_t)(x32 ^ 0x80000000u)); }
 
 // ---- histogram bin rule (DESIGN.md "Histogram") ------------------------------------------------------------
 __device__ __forceinline__ int hist_bin(float x, float lo, float inv_w, int bins) {

@@ -229,7 +229,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
-        else tot[j] = fl(__fmul_rn(tot[j], fmaf(erfinv_py(x[j]), s2, a)), m0 + mi);
+        else tot[j] = fl(__fmul_rn(tot[j], fmaf(erfinv_py_signed((int32_t)x[j]), s2, a)), m0 + mi);  // x arrives top-bit-flipped
       }
     }
   }
