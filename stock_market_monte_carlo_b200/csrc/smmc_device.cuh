@@ -183,33 +183,41 @@ __device__ __forceinline__ void gauss_pair(uint32_t w, uint32_t one, const Gauss
 // the flip for free from the per-month digital-shift row (smmc_api.cu, prepare_sobol), the other callers apply it.
 constexpr float kIcdfScale = 4.6566123179654e-10f;   // 2^-31 (1 - 2^-23)
 constexpr float kIcdfOffset = 2.3283064365386963e-10f;  // 2^-32
-__device__ __forceinline__ float erfinv_py_signed(int32_t xs) {
-  const float y = fmaf(__int2float_rn(xs), kIcdfScale, kIcdfOffset);
+// The three pieces are separate so that the simulation kernel can evaluate the central polynomial of its eight paths
+// branch-free (eight independent FFMA chains) and patch the rare tail elements (P = 0.34 % per draw) behind warp-uniform
+// votes; every caller executes the same FMAs on the same operands, so the results are bit-identical either way.
+__device__ __forceinline__ void icdf_arg(int32_t xs, float &y, float &w) {
+  y = fmaf(__int2float_rn(xs), kIcdfScale, kIcdfOffset);
   const float t = fmaf(-y, y, 1.0f);
-  float w = fmaf(lg2_approx(t), -0.69314718055994530942f, -2.5f);
-  float p;
-  if (w < 2.5f) {
-    p = 2.81022636e-08f;
-    p = fmaf(p, w, 3.43273939e-07f);
-    p = fmaf(p, w, -3.5233877e-06f);
-    p = fmaf(p, w, -4.39150654e-06f);
-    p = fmaf(p, w, 0.00021858087f);
-    p = fmaf(p, w, -0.00125372503f);
-    p = fmaf(p, w, -0.00417768164f);
-    p = fmaf(p, w, 0.246640727f);
-    p = fmaf(p, w, 1.50140941f);
-  } else {
-    w = sqrt_approx(w + 2.5f) - 3.0f;
-    p = -0.000200214257f;
-    p = fmaf(p, w, 0.000100950558f);
-    p = fmaf(p, w, 0.00134934322f);
-    p = fmaf(p, w, -0.00367342844f);
-    p = fmaf(p, w, 0.00573950773f);
-    p = fmaf(p, w, -0.0076224613f);
-    p = fmaf(p, w, 0.00943887047f);
-    p = fmaf(p, w, 1.00167406f);
-    p = fmaf(p, w, 2.83297682f);
-  }
+  w = fmaf(lg2_approx(t), -0.69314718055994530942f, -2.5f);
+}
+__device__ __forceinline__ float icdf_central(float w) {  // w - 2.5 < 2.5
+  float p = 2.81022636e-08f;
+  p = fmaf(p, w, 3.43273939e-07f);
+  p = fmaf(p, w, -3.5233877e-06f);
+  p = fmaf(p, w, -4.39150654e-06f);
+  p = fmaf(p, w, 0.00021858087f);
+  p = fmaf(p, w, -0.00125372503f);
+  p = fmaf(p, w, -0.00417768164f);
+  p = fmaf(p, w, 0.246640727f);
+  return fmaf(p, w, 1.50140941f);
+}
+__device__ __forceinline__ float icdf_tail(float w) {  // w - 2.5 >= 2.5
+  w = sqrt_approx(w + 2.5f) - 3.0f;
+  float p = -0.000200214257f;
+  p = fmaf(p, w, 0.000100950558f);
+  p = fmaf(p, w, 0.00134934322f);
+  p = fmaf(p, w, -0.00367342844f);
+  p = fmaf(p, w, 0.00573950773f);
+  p = fmaf(p, w, -0.0076224613f);
+  p = fmaf(p, w, 0.00943887047f);
+  p = fmaf(p, w, 1.00167406f);
+  return fmaf(p, w, 2.83297682f);
+}
+__device__ __forceinline__ float erfinv_py_signed(int32_t xs) {
+  float y, w;
+  icdf_arg(xs, y, w);
+  const float p = (w < 2.5f) ? icdf_central(w) : icdf_tail(w);
   return p * y;
 }
 __device__ __forceinline__ float erfinv_py(uint32_t x32) { return erfinv_py_signed((int32_t)(x32 ^ 0x80000000u)); }

@@ -179,6 +179,11 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 // h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
+#ifndef SMMC_ICDF_CHUNK
+#define SMMC_ICDF_CHUNK 4
+#endif
+constexpr int kIcdfChunk = SMMC_ICDF_CHUNK;
+
 template <int MODE, bool FLOW>
 __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, uint32_t tbl_base, const uint4 *vlo,
                                           uint32_t h, uint32_t lane, float (&tot)[8]) {
@@ -226,10 +231,38 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
       x[5] = x[1] ^ vb.z ^ vb.w;
       x[6] = base ^ vb.y ^ vb.w;
       x[7] = base ^ vb.x ^ vb.w;
+      if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) {
 #pragma unroll
-      for (int j = 0; j < 8; j++) {
-        if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
-        else tot[j] = fl(__fmul_rn(tot[j], fmaf(erfinv_py_signed((int32_t)x[j]), s2, a)), m0 + mi);  // x arrives top-bit-flipped
+        for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
+      } else {
+        // inverse CDF of the eight words (they arrive top-bit-flipped): the central polynomial of all eight as
+        // independent branch-free FFMA chains, then the tail elements (0.34 % of the draws) patched behind
+        // warp-uniform votes -- the same FMAs as erfinv_py_signed, without a divergent branch per element
+        // (four at a time: eight live (y, w, p) triples would push the lane masks out of the 64-register budget)
+#pragma unroll
+        for (int j0 = 0; j0 < 8; j0 += kIcdfChunk) {
+          float y[kIcdfChunk], w[kIcdfChunk], pv[kIcdfChunk];
+          bool any_tail = false;
+#pragma unroll
+          for (int j = 0; j < kIcdfChunk; j++) {
+            icdf_arg((int32_t)x[j0 + j], y[j], w[j]);
+            any_tail |= !(w[j] < 2.5f);
+            pv[j] = icdf_central(w[j]);
+          }
+          if (__any_sync(0xffffffffu, any_tail)) {
+#pragma unroll
+            for (int j = 0; j < kIcdfChunk; j++) {
+              const bool tail = !(w[j] < 2.5f);
+              if (__any_sync(0xffffffffu, tail)) {
+                const float pt = icdf_tail(w[j]);
+                pv[j] = tail ? pt : pv[j];
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < kIcdfChunk; j++)
+            tot[j0 + j] = fl(__fmul_rn(tot[j0 + j], fmaf(__fmul_rn(pv[j], y[j]), s2, a)), m0 + mi);
+        }
       }
     }
   }
