@@ -51,14 +51,17 @@ UNIT = "path-months/s"
 # 4 draws per Philox call + IMAD.HI index) and 22 (gaussian: 2 normals per 2 words); the shipped recipes draw 6
 # fields / 8 normals per call and need 12, so the fraction below stays an issue-slot utilisation (<= 1).  The
 # SURVEY-budget fraction is reported next to it as `frac_survey_budget`.
-I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 20}
+I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 9}
 # Pipe floors (cycles per warp-month per SM sub-partition) from the measured reciprocal throughputs in
 # profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the binding
 # resource of these instruction mixes is a pipe, not the issue slot.
-#   gaussian   2 MUFU per normal x 8.0 cycles (XU, 4 lanes/clk per sub-partition)
+#   gaussian, sobol_gaussian   2 MUFU per normal x 8.0 cycles (XU, 4 lanes/clk per sub-partition): both are
+#              Box-Muller pairs (sobol_gaussian: point 2 + pair {2 I2FP, FFMA, LG2, FMUL, SQRT, FMUL, FMUL.RZ, SIN, COS,
+#              2 FFMA, 2 FMUL}/2 = 7 -> I_alg 9)
 #   bootstrap  Philox: 8 per-lane rounds x 8.39 cycles (2 IMAD.WIDE + 2 LOP3, measured as a unit) per 6 months,
 #              + 16 further ALU-pipe instructions per call (fields, addresses) at their measured marginal 2.0 cycles
-PIPE_FLOOR = {"gaussian": ("xu", 16.0), "bootstrap": ("fmaheavy+alu (Philox)", (8 * 8.39 + 16 * 2.0) / 6.0)}
+PIPE_FLOOR = {"gaussian": ("xu", 16.0), "sobol_gaussian": ("xu", 16.0),
+              "bootstrap": ("fmaheavy+alu (Philox)", (8 * 8.39 + 16 * 2.0) / 6.0)}
 I_ALG_SURVEY = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": None, "sobol_gaussian": None}
 
 WORKLOADS = {
@@ -73,7 +76,7 @@ WORKLOADS = {
                strong=True,
                desc="360 months x 10^10 paths Gaussian + histogram + P(target), the 10^10 paths of ONE run sharded over the GPUs (strong scaling)"),
     "c4": dict(mode="sobol_gaussian", paths=5_000_000, periods=1000, block_partials=False, hist_range=(0.0, 500_000.0),
-               desc="1000 months x 5M paths Sobol (Joe-Kuo) Gaussian, histogram + P(target)"),
+               desc="1000 months x 5M paths Sobol (Joe-Kuo) Gaussian (Box-Muller on dimension pairs), histogram + P(target)"),
     "c4boot": dict(mode="sobol_bootstrap", paths=5_000_000, periods=1000, block_partials=False,
                    hist_range=(0.0, 1.0e8),
                    desc="1000 months x 5M paths Sobol (Joe-Kuo) bootstrap, histogram + P(target)"),

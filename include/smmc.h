@@ -47,8 +47,11 @@ typedef enum smmc_mode {
   /* Philox4x32-10 counter stream + Box-Muller (one 32-bit word per pair); r ~ N(gauss_mean, gauss_std) in percent
    * (reference CPU semantics: sample_returns_gaussian, src/simulations.cpp:41-55). */
   SMMC_MODE_GAUSSIAN = 2,
-  /* Sobol (Joe-Kuo direction numbers as vendored in reference include/sobol/sobol.cpp), point = path id + 1,
-   * dimension = month; optional Philox-keyed digital shift when seed != 0. */
+  /* Sobol (Joe-Kuo direction numbers as vendored in reference include/sobol/sobol.cpp), point = path id + 256,
+   * dimension = month; optional Philox-keyed digital shift when seed != 0.
+   * SOBOL_BOOTSTRAP: index = mulhi(word, n) into the SORTED table (empirical quantile function).
+   * SOBOL_GAUSSIAN: Box-Muller on dimension pairs -- month 2k takes its radius from the word of dimension 2k, month
+   * 2k+1 its angle from dimension 2k+1; the unpaired last month of an odd horizon takes the inverse normal CDF. */
   SMMC_MODE_SOBOL_BOOTSTRAP = 3,
   SMMC_MODE_SOBOL_GAUSSIAN = 4
 } smmc_mode;

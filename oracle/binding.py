@@ -57,6 +57,8 @@ def load():
     lib.orc_num_threads.restype = C.c_int
     lib.orc_gauss_pairs.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p]
     lib.orc_gauss_pairs.restype = None
+    lib.orc_sobol_gauss_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p]
+    lib.orc_sobol_gauss_pairs.restype = None
     lib.orc_trajectories.argtypes = [P(N.SmmcConfig), C.c_int32, C.c_void_p, C.c_void_p]
     lib.orc_trajectories.restype = C.c_int
     lib.orc_quantiles.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
@@ -147,6 +149,18 @@ def gauss_pairs(words, mean_pct=0.0, std_pct=100.0):
     w = np.ascontiguousarray(np.asarray(words, dtype=np.uint32))
     g = np.zeros((w.size, 2), dtype=np.float32)
     lib.orc_gauss_pairs(w.ctypes.data, int(w.size), float(mean_pct), float(std_pct), g.ctypes.data)
+    return g
+
+
+def sobol_gauss_pairs(xr, xa, mean_pct=0.0, std_pct=100.0):
+    """SOBOL_GAUSSIAN growth factors (g0, g1) of each (radius word, angle word) pair of Sobol words; with mean 0 % and
+    std 100 % they are the normals (z0, z1)"""
+    lib = load()
+    xr = np.ascontiguousarray(np.asarray(xr, dtype=np.uint32))
+    xa = np.ascontiguousarray(np.asarray(xa, dtype=np.uint32))
+    assert xr.shape == xa.shape
+    g = np.zeros((xr.size, 2), dtype=np.float32)
+    lib.orc_sobol_gauss_pairs(xr.ctypes.data, xa.ctypes.data, int(xr.size), float(mean_pct), float(std_pct), g.ctypes.data)
     return g
 
 

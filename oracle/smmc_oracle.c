@@ -188,7 +188,26 @@ static uint32_t sobol_shift(int32_t dim, uint64_t seed) {
   return w[dim & 3];
 }
 
-/* inverse normal CDF used by SOBOL_GAUSSIAN: single-precision restatement, see DESIGN.md "Sobol Gaussian".
+/* SOBOL_GAUSSIAN growth factors of months 2k, 2k+1 from the words of dimensions 2k (radius) and 2k+1 (angle)
+ * (device: sobol_gauss_pair in csrc/smmc_device.cuh):
+ *   u = (x_r + 1/2)/2^32 as fma(float(x_r), 2^-32, 2^-33);  v = 2 pi int32(x_a)/2^32;
+ *   (g0, g1) = a + sqrt(log2(u) k) (cos v, sin v).  Constants are the device's, digit for digit; libm here, MUFU there. */
+static void sobol_gauss_pair(uint32_t xr, uint32_t xa, gauss_consts gc, float *g0, float *g1) {
+  float u = fmaf((float)xr, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+  float v = (float)(int32_t)xa * 1.4629180792671596e-09f;
+  float t = log2f(u) * gc.k;
+  float rs = sqrtf(t);
+  *g0 = fmaf(rs, cosf(v), gc.a);
+  *g1 = fmaf(rs, sinf(v), gc.a);
+}
+
+/* test hook: growth factors of n (radius word, angle word) pairs (g[2i], g[2i+1]) */
+void orc_sobol_gauss_pairs(const uint32_t *xr, const uint32_t *xa, int64_t n, float mean_pct, float std_pct, float *g) {
+  gauss_consts gc = make_gauss_consts(mean_pct, std_pct);
+  for (int64_t i = 0; i < n; i++) sobol_gauss_pair(xr[i], xa[i], gc, &g[2 * i], &g[2 * i + 1]);
+}
+
+/* inverse normal CDF used by SOBOL_GAUSSIAN for the unpaired last month of an odd horizon: single-precision restatement, see DESIGN.md "Sobol Gaussian".
  * Central/tail split of Giles' erfinv approximation ("Approximating the erfinv function", GPU Gems 2012),
  * evaluated with explicit fmaf so that host and device agree up to the log2/sqrt approximations. */
 static float normal_icdf(uint32_t x32) { /* returns z / sqrt(2) */
@@ -311,10 +330,21 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
       }
     } break;
     case SMMC_MODE_SOBOL_GAUSSIAN: {
+      /* Box-Muller on dimension pairs: months 2k (radius word) and 2k+1 (angle word); an unpaired last month of an
+       * odd horizon takes the inverse normal CDF of its word */
+      float g[2] = {1.0f, 1.0f};
       for (int m = 0; m < P; m++) {
         uint32_t x = orc_sobol_point(path + SOBOL_SKIP, m) ^ rc->shift[m];
         if (draws) draws[m] = x;
-        float gm = fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
+        if ((m & 1) == 0) {
+          if (m + 1 < P) {
+            uint32_t xa = orc_sobol_point(path + SOBOL_SKIP, m + 1) ^ rc->shift[m + 1];
+            sobol_gauss_pair(x, xa, rc->gc, &g[0], &g[1]);
+          } else {
+            g[0] = fmaf(normal_icdf(x), rc->sigma_sqrt2, rc->gc.a);
+          }
+        }
+        float gm = g[m & 1];
         total = apply_flow(rc, total * gm, m);
         if (values) values[m + 1] = total;
         if (rets) rets[m] = (gm - 1.0f) * 100.0f;

@@ -89,7 +89,6 @@ struct Context {
   std::vector<float> flow_host;  // keep-fractions of the last withdrawal schedule uploaded
   int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
   uint64_t sobol_seed = 0;
-  bool sobol_flip = false;
   bool sobol_full_ready = false;
   double *stats_host = nullptr;  // pinned
   size_t stats_host_cap = 0;
@@ -258,19 +257,17 @@ uint32_t sobol_shift_host(int m, uint64_t seed) {
 }
 
 // (Re)build the per-launch Sobol tables for (n_periods, seed) on `st`; cached per context.
-// `flip`: SOBOL_GAUSSIAN folds the x ^ 0x80000000 of its inverse-CDF argument (smmc_device.cuh, erfinv_py_signed) into
-// the per-month digital-shift row, where it is free.
-smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, bool flip, cudaStream_t st, smmc::KParams *p) {
+smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream_t st, smmc::KParams *p) {
   const int ppad = (n_periods + 31) & ~31;
   const uint32_t *V = smmc::sobol_table();
   if (n_periods > smmc::sobol_table_dims()) return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support at most %d periods", smmc::sobol_table_dims());
-  if (ppad > 0 && (ctx->sobol_periods != n_periods || ctx->sobol_seed != seed || ctx->sobol_flip != flip)) {
+  if (ppad > 0 && (ctx->sobol_periods != n_periods || ctx->sobol_seed != seed)) {
     std::vector<uint32_t> lo((size_t)ppad * 8, 0u), hi((size_t)26 * ppad, 0u);
     for (int m = 0; m < n_periods; m++) {
       for (int k = 0; k < 8; k++) lo[(size_t)m * 8 + k] = V[(size_t)m * 32 + k];
       for (int k = 0; k < 24; k++) hi[(size_t)k * ppad + m] = V[(size_t)m * 32 + 8 + k];
       hi[(size_t)24 * ppad + m] = V[(size_t)m * 32 + 7];
-      hi[(size_t)25 * ppad + m] = sobol_shift_host(m, seed) ^ (flip ? 0x80000000u : 0u);
+      hi[(size_t)25 * ppad + m] = sobol_shift_host(m, seed);
     }
     CU(ctx->sobol_lo.reserve(lo.size() * 4));
     CU(ctx->sobol_hi.reserve(hi.size() * 4));
@@ -280,7 +277,6 @@ smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, bool flip,
     CU(cudaStreamSynchronize(st));  // lo/hi are stack-lifetime host vectors
     ctx->sobol_periods = n_periods;
     ctx->sobol_seed = seed;
-    ctx->sobol_flip = flip;
   }
   p->sobol_lo = (const uint32_t *)ctx->sobol_lo.p;
   p->sobol_hi = (const uint32_t *)ctx->sobol_hi.p;
@@ -489,7 +485,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   }
 
   if (is_sobol(cfg->mode)) {
-    smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN, st, &p);
+    smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p);
     if (sst != SMMC_OK) return sst;
   }
 

@@ -97,15 +97,24 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
   } else {  // Sobol modes: plain Gray-code evaluation over all 32 direction numbers of dimension m
     const uint64_t i = path + kSobolSkip;
     const uint32_t gray = (uint32_t)(i ^ (i >> 1));
-    for (int m = 0; m < P; m++) {
+    auto word = [&](int m) {
       uint32_t x = shift[m];
       for (uint32_t gg = gray; gg; gg &= gg - 1u) x ^= sobol_full[m * 32 + (__ffs((int)gg) - 1)];
+      return x;
+    };
+    float g[2] = {1.0f, 1.0f};
+    for (int m = 0; m < P; m++) {
+      const uint32_t x = word(m);
       if (mode == SMMC_MODE_SOBOL_BOOTSTRAP) {
         const uint32_t idx = __umulhi(x, (uint32_t)n);
         tot = flow(fmaf(tot, tbl[idx], tot), m);
         if (rp) rp[m] = raw[idx];
-      } else {
-        const float gm = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);
+      } else {  // Box-Muller on dimension pairs; an unpaired last month takes the inverse CDF (smmc_device.cuh)
+        if ((m & 1) == 0) {
+          if (m + 1 < P) sobol_gauss_pair(x, word(m + 1), p.gc, g[0], g[1]);
+          else g[0] = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);
+        }
+        const float gm = g[m & 1];
         tot = flow(__fmul_rn(tot, gm), m);
         if (rp) rp[m] = __fmul_rn(__fsub_rn(gm, 1.0f), 100.0f);
       }

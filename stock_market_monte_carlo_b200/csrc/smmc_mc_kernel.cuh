@@ -179,11 +179,6 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 // h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
-#ifndef SMMC_ICDF_CHUNK
-#define SMMC_ICDF_CHUNK 4
-#endif
-constexpr int kIcdfChunk = SMMC_ICDF_CHUNK;
-
 template <int MODE, bool FLOW>
 __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, uint32_t tbl_base, const uint4 *vlo,
                                           uint32_t h, uint32_t lane, float (&tot)[8]) {
@@ -195,7 +190,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   const uint32_t gh = h ^ (h >> 1);
   const int ppad = p.sobol_ppad;
   const uint32_t nr4 = p.nr4, row_mask = ~(p.rep4 - 1u);
-  const float a = p.gc.a, s2 = p.sigma_sqrt2;
+  const GaussConsts gc = p.gc;
   // warp-uniform part of month m0 + lane: every load is issued before the first is consumed (independent,
   // predicated on the warp-uniform gray bits), and the next 32 months are fetched while the current 32 are computed
   auto block_part = [&](int m0) {
@@ -207,62 +202,57 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
       if ((gh >> k) & 1u) U ^= __ldg(col + k * ppad);
     return U;
   };
+  // the eight words of month m (one per path of the lane) from the broadcast block part Um
+  auto month_words = [&](int m, uint32_t Um, uint32_t (&x)[8]) {
+    const uint4 va = vlo[m * 2], vb = vlo[m * 2 + 1];
+    uint32_t base = Um ^ (va.x & mk0);
+    base ^= (va.y & mk1);
+    base ^= (va.z & mk2);
+    base ^= (va.w & mk3);
+    base ^= (vb.x & mk4);
+    x[0] = base;
+    x[1] = base ^ vb.x ^ vb.y;
+    x[2] = base ^ vb.y ^ vb.z;
+    x[3] = base ^ vb.x ^ vb.z;
+    x[4] = base ^ vb.z ^ vb.w;
+    x[5] = x[1] ^ vb.z ^ vb.w;
+    x[6] = base ^ vb.y ^ vb.w;
+    x[7] = base ^ vb.x ^ vb.w;
+  };
   uint32_t U_next = p.n_periods > 0 ? block_part(0) : 0u;
 #pragma unroll 1
   for (int m0 = 0; m0 < p.n_periods; m0 += 32) {
     const uint32_t U = U_next;
     if (m0 + 32 < p.n_periods) U_next = block_part(m0 + 32);
     const int mend = (p.n_periods - m0) < 32 ? (p.n_periods - m0) : 32;
+    if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) {
 #pragma unroll 2
-    for (int mi = 0; mi < mend; mi++) {
-      const uint32_t Um = __shfl_sync(0xffffffffu, U, mi);
-      const uint4 va = vlo[(m0 + mi) * 2], vb = vlo[(m0 + mi) * 2 + 1];
-      uint32_t base = Um ^ (va.x & mk0);
-      base ^= (va.y & mk1);
-      base ^= (va.z & mk2);
-      base ^= (va.w & mk3);
-      base ^= (vb.x & mk4);
-      uint32_t x[8];
-      x[0] = base;
-      x[1] = base ^ vb.x ^ vb.y;
-      x[2] = base ^ vb.y ^ vb.z;
-      x[3] = base ^ vb.x ^ vb.z;
-      x[4] = base ^ vb.z ^ vb.w;
-      x[5] = x[1] ^ vb.z ^ vb.w;
-      x[6] = base ^ vb.y ^ vb.w;
-      x[7] = base ^ vb.x ^ vb.w;
-      if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) {
+      for (int mi = 0; mi < mend; mi++) {
+        uint32_t x[8];
+        month_words(m0 + mi, __shfl_sync(0xffffffffu, U, mi), x);
 #pragma unroll
         for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
-      } else {
-        // inverse CDF of the eight words (they arrive top-bit-flipped): the central polynomial of all eight as
-        // independent branch-free FFMA chains, then the tail elements (0.34 % of the draws) patched behind
-        // warp-uniform votes -- the same FMAs as erfinv_py_signed, without a divergent branch per element
-        // (four at a time: eight live (y, w, p) triples would push the lane masks out of the 64-register budget)
+      }
+    } else {
+      // Box-Muller on dimension pairs (smmc_device.cuh): even month = radius word, odd month = angle word
+#pragma unroll 1
+      for (int mi = 0; mi + 1 < mend; mi += 2) {
+        uint32_t xr[8], xa[8];
+        month_words(m0 + mi, __shfl_sync(0xffffffffu, U, mi), xr);
+        month_words(m0 + mi + 1, __shfl_sync(0xffffffffu, U, mi + 1), xa);
 #pragma unroll
-        for (int j0 = 0; j0 < 8; j0 += kIcdfChunk) {
-          float y[kIcdfChunk], w[kIcdfChunk], pv[kIcdfChunk];
-          bool any_tail = false;
-#pragma unroll
-          for (int j = 0; j < kIcdfChunk; j++) {
-            icdf_arg((int32_t)x[j0 + j], y[j], w[j]);
-            any_tail |= !(w[j] < 2.5f);
-            pv[j] = icdf_central(w[j]);
-          }
-          if (__any_sync(0xffffffffu, any_tail)) {
-#pragma unroll
-            for (int j = 0; j < kIcdfChunk; j++) {
-              const bool tail = !(w[j] < 2.5f);
-              if (__any_sync(0xffffffffu, tail)) {
-                const float pt = icdf_tail(w[j]);
-                pv[j] = tail ? pt : pv[j];
-              }
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < kIcdfChunk; j++)
-            tot[j0 + j] = fl(__fmul_rn(tot[j0 + j], fmaf(__fmul_rn(pv[j], y[j]), s2, a)), m0 + mi);
+        for (int j = 0; j < 8; j++) {
+          float g0, g1;
+          sobol_gauss_pair(xr[j], xa[j], gc, g0, g1);
+          tot[j] = fl(__fmul_rn(fl(__fmul_rn(tot[j], g0), m0 + mi), g1), m0 + mi + 1);
         }
+      }
+      if (mend & 1) {  // odd horizon: the last month has no partner dimension -> inverse normal CDF of its word
+        uint32_t x[8];
+        month_words(m0 + mend - 1, __shfl_sync(0xffffffffu, U, mend - 1), x);
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+          tot[j] = fl(__fmul_rn(tot[j], fmaf(erfinv_py(x[j]), p.sigma_sqrt2, gc.a)), m0 + mend - 1);
       }
     }
   }

@@ -243,6 +243,50 @@ def test_box_muller_pairs_are_jointly_normal(O):
     assert stats.chi2.sf(chi, 9999) > 1e-4
 
 
+def test_sobol_gaussian_pairs(O):
+    """SOBOL_GAUSSIAN = Box-Muller on dimension pairs: month 2k takes the radius from the word of
+    dimension 2k, month 2k+1 the angle from dimension 2k+1; an odd last month takes the inverse normal CDF.  Checked here:
+    the pair transform against a float64 Box-Muller of the same words, normality on random words, the month <-> word
+    wiring through orc_draws / trajectories, and the randomised-QMC accuracy against the closed-form moments."""
+    from scipy import stats
+    from scipy.special import ndtri
+    rng = np.random.default_rng(11)
+    n = 2_000_000
+    xr = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    xa = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    edge = np.array([0, 1, 2 ** 32 - 1, 2 ** 31, 2 ** 31 - 1, 12345], dtype=np.uint32)  # u -> 2^-33 ... 1, v = -pi ... pi
+    xr[:6], xa[:6] = edge, edge[::-1]
+    z = O.sobol_gauss_pairs(xr, xa, 0.0, 100.0).astype(np.float64) - 1.0
+    u = (xr.astype(np.float64) + 0.5) / 2.0 ** 32
+    v = 2.0 * np.pi * xa.astype(np.int32).astype(np.float64) / 2.0 ** 32
+    rad = np.sqrt(-2.0 * np.log(u))
+    assert np.all(np.isfinite(z))
+    err = np.maximum(np.abs(z[:, 0] - rad * np.cos(v)), np.abs(z[:, 1] - rad * np.sin(v)))
+    # fp32 evaluation; u is a float, i.e. 24 bits: next to u = 1 (radius -> 0) 1 - u is only resolved to 2^-25, which moves
+    # a radius of r by 3e-8 / r (at most 2.5e-4, for the 1e-7 of the draws with r < 5e-4)
+    assert np.max(err[u < 0.99]) < 3e-6 and np.max(err) < 2.5e-4
+    for k in (0, 1):
+        assert stats.kstest(z[:, k], "norm").pvalue > 1e-3
+    assert abs((z[:, 0] * z[:, 1]).mean()) < 5 / np.sqrt(n)
+    # wiring: returns of a trajectory = 100 (g - 1) of the pair built from that path's own words, months (2k, 2k+1);
+    # the odd last month is the inverse CDF of its word
+    P, mean, std = 7, 0.5, 10.0 / 12.0
+    x = O.draws("sobol_gaussian", 300, P, seed=5).reshape(300, P)
+    _, rets = O.trajectories("sobol_gaussian", 300, P, seed=5, gauss_mean=mean, gauss_std=std, want_returns=True)
+    g = O.sobol_gauss_pairs(x[:, 0:6:2].ravel(), x[:, 1:6:2].ravel(), mean, std).reshape(300, 3, 2)
+    want = ((g.reshape(300, 6) - np.float32(1.0)) * np.float32(100.0)).astype(np.float32)
+    assert np.array_equal(rets[:, :6], want)
+    z_last = (rets[:, 6].astype(np.float64) - mean) / std
+    assert np.max(np.abs(z_last - ndtri((x[:, 6].astype(np.float64) + 0.5) / 2.0 ** 32))) < 2e-5
+    # randomised QMC (4 digital shifts) against the closed form: mean to ~1e-5, far below the MC standard error
+    Pm, N = 360, 1 << 17
+    mu, sg = float(np.float32(0.5) * np.float32(0.01)), float(np.float32(10.0 / 12.0) * np.float32(0.01))
+    exact = 1000.0 * (1.0 + mu) ** Pm
+    mc_se = np.sqrt(1000.0 ** 2 * ((1.0 + mu) ** 2 + sg ** 2) ** Pm - exact ** 2) / np.sqrt(N)
+    errs = [O.simulate("sobol_gaussian", N, Pm, seed=s).mean - exact for s in (1, 2, 3, 4)]
+    assert np.sqrt(np.mean(np.square(errs))) < 0.2 * mc_se, (errs, mc_se)
+
+
 def test_bootstrap_index_is_the_exact_floor(O, table):
     """idx = floor(f n / 2^bits) for the six fields of a call; every index < n; near-uniform over the table"""
     d = O.draws("bootstrap", 2000, 600, returns=table, seed=9)
