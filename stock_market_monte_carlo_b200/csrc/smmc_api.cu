@@ -435,7 +435,6 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.tbl_rep = (const float *)ctx->tbl.p;
     p.tbl_bytes = tbl_bytes;
     p.rep4 = (uint32_t)li.rep * 4u;
-    p.nr4 = (uint32_t)n * (uint32_t)li.rep * 4u;
     p.idx_scale = (float)n * 2.3283064365386963e-10f;  // exact: n < 2^24
     p.bc.c21 = (float)(4 * n);                          // exact: n < 2^21 (validated)
     p.bc.k21 = (float)(8388608 - 4 * n);

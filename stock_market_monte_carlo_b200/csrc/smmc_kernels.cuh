@@ -21,7 +21,6 @@ struct KParams {
   const float *tbl_rep;
   uint32_t tbl_bytes;  // bytes to stage (multiple of 16)
   uint32_t rep4;       // rep * 4: bytes per table row
-  uint32_t nr4;        // n * rep * 4: mulhi(word, nr4) = byte offset of the row + sub-row fraction
   float idx_scale;     // compat: float(n) * 2^-32
   BootConsts bc;       // BOOTSTRAP: fma.rz index constants and the row shift
   uint32_t one;        // 0x3F800000, passed as a value the compiler cannot fold: keeps (w & mask) | one a single LOP3

@@ -90,8 +90,8 @@ __device__ __forceinline__ void run_compat(const KParams &p, const Flow<FLOW> &f
   }
 }
 
-__device__ __forceinline__ float boot_step(float tot, uint32_t w, uint32_t nr4, uint32_t row_mask, uint32_t base) {
-  const float r = lds_f32((__umulhi(w, nr4) & row_mask) + base);  // (idx * rep + lane%rep) * 4, idx = mulhi(w, n)
+__device__ __forceinline__ float boot_step(float tot, uint32_t w, uint32_t n, uint32_t rep4, uint32_t base) {
+  const float r = lds_f32(__umulhi(w, n) * rep4 + base);  // idx = mulhi(w, n); row address by one IMAD
   return fmaf(tot, r, tot);
 }
 
@@ -189,7 +189,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   const uint32_t mk4 = ((lane >> 4) & 1u) ? 0xffffffffu : 0u;
   const uint32_t gh = h ^ (h >> 1);
   const int ppad = p.sobol_ppad;
-  const uint32_t nr4 = p.nr4, row_mask = ~(p.rep4 - 1u);
+  const uint32_t n = (uint32_t)p.n_returns, rep4 = p.rep4;
   const GaussConsts gc = p.gc;
   // warp-uniform part of month m0 + lane: every load is issued before the first is consumed (independent,
   // predicated on the warp-uniform gray bits), and the next 32 months are fetched while the current 32 are computed
@@ -231,7 +231,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
         uint32_t x[8];
         month_words(m0 + mi, __shfl_sync(0xffffffffu, U, mi), x);
 #pragma unroll
-        for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], nr4, row_mask, tbl_base), m0 + mi);
+        for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], n, rep4, tbl_base), m0 + mi);
       }
     } else {
       // Box-Muller on dimension pairs (smmc_device.cuh): even month = radius word, odd month = angle word
