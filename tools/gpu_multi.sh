@@ -20,3 +20,11 @@ d=json.loads(open('gpurun_out/scale_$n.json').read().strip().splitlines()[-1])
 print('n_gpus',d['n_gpus'],'value %.4e'%d['value'],'ms/step',round(d['ms_per_step'],3),'e2e %.4e'%d['e2e']['value'],'clocks',d['clocks']['sm_mhz'],d['clocks']['reasons'])"
   fi
 done
+# C5 (360 months x 10^10 paths of ONE run, strong scaling): 1 GPU and N GPUs
+python bench.py --gpus 1 --workload c5 --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/c5_1.json 2> gpurun_out/c5_1.err; echo "c5 N=1 rc=$?"
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 \
+  bench.py --gpus $N --workload c5 --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/c5_$N.json 2> gpurun_out/c5_$N.err; echo "c5 N=$N rc=$?"
+for n in 1 $N; do python -c "
+import json
+d=json.loads(open('gpurun_out/c5_$n.json').read().strip().splitlines()[-1])
+print('c5 n_gpus',d['n_gpus'],'value %.4e'%d['value'],'ms/step',round(d['ms_per_step'],3),'scaling',d['scaling'],'result',d.get('result'))"; done
