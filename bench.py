@@ -370,7 +370,9 @@ def main():
         e2e = {"value": job_paths * P * k_e2e / float(dt.item()), "unit": UNIT,
                "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
                "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
-               "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)"}
+               "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)",
+               "inputs": ("return table copied host->device every step" if table is not None else
+                          "none to copy: the Gaussian modes take scalars only (mean, std, seed, offset)")}
 
     # ---- SURVEY 8(f) rank 1, reported next to the headline (outside the timed region): the quartiles of the same
     # workload by three replays (radix select in shared memory) instead of a finals download + host sort
