@@ -119,6 +119,34 @@ def test_against_reference_kernels_on_this_gpu(S, O, table1127):
     assert means.size() == 20 and np.array_equal(means.array, rm) and np.array_equal(variances.array, rv)
 
 
+def test_against_reference_kernels_at_baseline_size(S, O, table1127):
+    """config C3's shape (100 M paths x 360 months) through the reference's own kernels compiled for sm_100a: every final
+    and every block mean / variance bit for bit -- except where the reference's result is undefined: a state >= 2^32 - 128
+    maps to idx == n_returns and the reference then reads bufferReturns[1127], one float past its
+    shared array (src/simulations.cu:123, :148-149), i.e. stale shared memory; this build reads a zero pad there.
+    Expected 10^8 * 360 * 128 / 2^32 = 1073 such paths; every differing path must be one of them (checked with the
+    oracle's draws)."""
+    if not O.ref_available("libref_gpu.so"):
+        pytest.skip("oracle/_ref/libref_gpu.so did not travel with the snapshot")
+    N, P, n = 100_000_000, 360, 1127
+    g = S.simulate("bootstrap_compat", N, P, returns=table1127, want_finals=True, want_block_partials=True)
+    ref = O.ref_mc_simulations_gpu(N, P, 1000.0, table1127)
+    bad = np.flatnonzero(ref != g.finals)
+    del ref
+    expected = N * P * 128 / 2.0 ** 32
+    assert bad.size < expected + 6 * np.sqrt(expected), bad.size
+    for b in bad:
+        blk = (int(b) // 256) * 256
+        d = O.draws("bootstrap_compat", 256, P, returns=table1127, stream_offset=blk).reshape(256, P)
+        assert (d[int(b) - blk] == n).any(), f"path {b} differs from the reference kernel without an idx == n draw"
+    rm, rv = O.ref_mc_simulations_gpu_reduceBlock(N, P, 1000.0, table1127)
+    assert rm.size == (N + 255) // 256
+    clean = np.ones(rm.size, dtype=bool)
+    clean[bad // 256] = False
+    # the reduceBlock kernel's own out-of-bounds read lands in different stale memory: its affected blocks are the same
+    assert np.array_equal(rm[clean], g.block_means[clean]) and np.array_equal(rv[clean], g.block_vars[clean])
+
+
 @pytest.mark.parametrize("mode", ALL_MODES)
 def test_sharding_identity_on_device(S, table, mode):
     kw = mode_kwargs(mode, table)
