@@ -22,7 +22,7 @@ GAUSS_RTOL = 2e-5
 MOMENT_RTOL = 1e-5
 
 SHAPES = [(0, 360), (1, 1), (1, 0), (31, 5), (255, 7), (256, 360), (257, 13), (1000, 361), (1000, 362), (1000, 363),
-          (65536 + 77, 360), (200_000, 120), (20_000, 1000)]
+          (65536 + 77, 360), (200_000, 120), (20_000, 1000), (777, 1111), (513, 1110), (300, 33)]
 
 
 def _compare(S, O, mode, N, P, table, **extra):
