@@ -225,6 +225,61 @@ def run_reference_arm(args, wl):
     return 0
 
 
+# ---- auxiliary workload: reduce_mean_gpu, the one HBM-bound kernel of the path ------------------
+def run_reduce_mean(args):
+    """Mean of 2^28 device-resident floats (1 GiB, larger than the 126 MB L2) through smmc_reduce_mean_device.
+    Algorithmic traffic: 4 bytes read per element, nothing written.  Peak: MEASURED_PEAKS.json hbm_gbs (a copy: read+write
+    bytes), else the profiling guide's fallback."""
+    import torch
+    import stock_market_monte_carlo_b200 as S
+    if S.load().smmc_device_count() < 1:
+        raise SystemExit("bench.py needs a B200: the product has no CPU fallback")
+    torch.cuda.set_device(0)
+    n = args.paths or (1 << 28)
+    steps, warm = (args.steps or 50), max(args.warmup, 3)
+    bufs = [torch.full((n,), 1.0 + 0.25 * i, dtype=torch.float32, device="cuda") for i in range(2)]  # alternate: 2 GiB > L2
+    stream = torch.cuda.current_stream().cuda_stream
+    for i in range(warm):
+        S.reduce_mean_device(bufs[i & 1].data_ptr(), n, stream=stream)
+    sampler = ClockSampler([0])
+    sampler.begin()
+    ms, ok = [], True
+    for i in range(steps):
+        m, k = S.reduce_mean_device(bufs[i & 1].data_ptr(), n, stream=stream)
+        ok = ok and (m == 1.0 + 0.25 * (i & 1))
+        ms.append(k)
+    sampler.end()
+    clocks = sampler.stop()
+    # end to end through the reference-named call with a HOST vector (H2D copy of 4 B/element inside the timed region)
+    h = torch.ones(1 << 26, dtype=torch.float32).numpy()
+    S.reduce_mean_gpu(h, h.size)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        S.reduce_mean_gpu(h, h.size)
+    e2e_s = (time.perf_counter() - t0) / 3
+    peaks = measured_peaks()
+    peak = float(peaks.get("hbm_gbs") or 6400.0)
+    k_ms = sum(ms) / len(ms)
+    gbs = 4.0 * n / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": "elements/sec (reduce_mean_gpu, device-timed)", "value": n / (k_ms * 1e-3), "unit": "elements/s", "n_gpus": 1,
+        "steps": steps, "warmup": warm, "ms_per_step": k_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32 in, f64 accumulation", "data": "synthetic",
+        "config": {"workload": f"reduce_mean_gpu over {n} device-resident floats ({4 * n / 2**30:.2f} GiB)",
+                   "l2": "two 1 GiB buffers alternate between steps: every step reads from HBM"},
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                     "traffic": ncu_traffic("reduce_mean") if n == (1 << 28) else None, "algorithmic_bytes": 4 * n,
+                     "kernel": "smmc::reduce_sum_kernel", "kernel_ms": k_ms, "bytes_per_element": 4,
+                     "peak_source": ("MEASURED_PEAKS.json hbm_gbs (copy: read + write bytes)" if peaks.get("hbm_gbs")
+                                     else "fallback 6400 GB/s (B200_PROFILING.md)")},
+        "e2e": {"value": h.size / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(h.nbytes), "d2h_bytes_per_step": 8,
+                "api": "reduce_mean_gpu(host vector) -> smmc_reduce_mean: pageable H2D + kernel"},
+        "gpu_launches": steps, "clocks": clocks, "result": {"exact": bool(ok)},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 # ---- the GPU arm --------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -232,11 +287,13 @@ def main():
     ap.add_argument("--steps", type=int, default=0, help="timed steps (default 100; 5 for the 1.8 s steps of c5)")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["reduce_mean"])
     ap.add_argument("--paths", type=int, default=0, help="override paths per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
+    if args.workload == "reduce_mean":
+        return run_reduce_mean(args)
     wl = dict(WORKLOADS[args.workload])
     if args.paths:
         wl["paths"] = args.paths

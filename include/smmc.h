@@ -146,6 +146,12 @@ smmc_status smmc_stats_finalize(const double *stats, int32_t hist_bins, float in
 /* mean of n host floats (reference reduce_mean_gpu, src/simulations.cu:269-341), single-pass fp64-accumulating
  * device reduction; 64-bit indexing. */
 smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float *mean_out);
+/* The same reduction over n floats already RESIDENT on `device` (e.g. the `finals` buffer of a DEVICE_POINTERS run):
+ * launched on `stream` (NULL = legacy default stream), blocks until done.  vec_dev: any 4-byte-aligned device pointer.
+ * kernel_ms (nullable): CUDA-event duration of the reduction kernel on that stream -- the kernel is HBM-bound at
+ * 4 bytes per element. */
+smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t device, void *stream, float *mean_out,
+                                    float *kernel_ms);
 /* out = a + b on the device (reference vector_add_gpu, src/gpu.cu:17-47). Host pointers. */
 smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device);
 

@@ -85,6 +85,7 @@ struct Context {
   // ring of event pairs around the simulation kernel of the last kEventRing launches (smmc_kernel_times)
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
+  cudaEvent_t red0 = nullptr, red1 = nullptr;  // around the reduce_mean kernel (smmc_reduce_mean_device)
   DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift, selhist, flow;
   std::vector<float> flow_host;  // keep-fractions of the last withdrawal schedule uploaded
   int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
@@ -136,6 +137,8 @@ smmc_status get_context(int device, Context **out) {
       CU(cudaEventCreate(&c.ev0[i]));
       CU(cudaEventCreate(&c.ev1[i]));
     }
+    CU(cudaEventCreate(&c.red0));
+    CU(cudaEventCreate(&c.red1));
     c.device = device;
     c.n_sms = sms;
     c.smem_optin = (size_t)optin;
@@ -669,6 +672,24 @@ smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out)
                              &out->mean, &out->m2, out->hist);
 }
 
+namespace {
+// sum of n device floats on `st`; blocks until done; kernel_ms (nullable) = CUDA-event time of the reduction kernel
+smmc_status reduce_sum_device(Context *ctx, const float *v_dev, int64_t n, cudaStream_t st, double *sum, float *kernel_ms) {
+  const size_t part = (size_t)ctx->n_sms * 4 * sizeof(double);
+  CU(ctx->work.reserve(part + 32));
+  char *w = (char *)ctx->work.p;
+  CU(cudaMemsetAsync(w + part, 0, 32, st));
+  cudaEvent_t e0 = ctx->red0, e1 = ctx->red1;
+  if (kernel_ms) CU(cudaEventRecord(e0, st));
+  CU(smmc::launch_reduce_sum(v_dev, n, (double *)w, (unsigned int *)(w + part + 16), (double *)(w + part), ctx->n_sms, st));
+  if (kernel_ms) CU(cudaEventRecord(e1, st));
+  CU(cudaMemcpyAsync(sum, w + part, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (kernel_ms) CU(cudaEventElapsedTime(kernel_ms, e0, e1));
+  return SMMC_OK;
+}
+}  // namespace
+
 smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float *mean_out) {
   if (!vec || !mean_out || n <= 0) return fail(SMMC_ERR_INVALID_ARG, "reduce_mean: need n > 0 and non-null pointers");
   Context *ctx = nullptr;
@@ -676,17 +697,28 @@ smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float 
   if (st != SMMC_OK) return st;
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(cudaSetDevice(device));
-  const size_t part = (size_t)ctx->n_sms * 4 * sizeof(double);
   CU(ctx->scratch.reserve((size_t)n * 4));
-  CU(ctx->work.reserve(part + 32));
-  char *w = (char *)ctx->work.p;
   CU(cudaMemcpyAsync(ctx->scratch.p, vec, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
-  CU(cudaMemsetAsync(w + part, 0, 32, ctx->stream));
-  CU(smmc::launch_reduce_sum((const float *)ctx->scratch.p, n, (double *)w, (unsigned int *)(w + part + 16),
-                             (double *)(w + part), ctx->n_sms, ctx->stream));
   double sum = 0.0;
-  CU(cudaMemcpyAsync(&sum, w + part, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
+  st = reduce_sum_device(ctx, (const float *)ctx->scratch.p, n, ctx->stream, &sum, nullptr);
+  if (st != SMMC_OK) return st;
+  *mean_out = (float)(sum / (double)n);
+  return SMMC_OK;
+}
+
+smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t device, void *stream, float *mean_out,
+                                    float *kernel_ms) {
+  if (!vec_dev || !mean_out || n <= 0)
+    return fail(SMMC_ERR_INVALID_ARG, "reduce_mean_device: need n > 0 and non-null pointers");
+  if (reinterpret_cast<uintptr_t>(vec_dev) & 3u) return fail(SMMC_ERR_INVALID_ARG, "reduce_mean_device: pointer must be 4-byte aligned");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  double sum = 0.0;
+  st = reduce_sum_device(ctx, vec_dev, n, (cudaStream_t)stream, &sum, kernel_ms);
+  if (st != SMMC_OK) return st;
   *mean_out = (float)(sum / (double)n);
   return SMMC_OK;
 }
@@ -1052,6 +1084,8 @@ void smmc_shutdown(void) {
       cudaEventDestroy(c.ev0[i]);
       cudaEventDestroy(c.ev1[i]);
     }
+    cudaEventDestroy(c.red0);
+    cudaEventDestroy(c.red1);
     c.ev_head = 0;
     cudaStreamDestroy(c.stream);
     c.ready = false;

@@ -3,6 +3,9 @@
 // smmc_mc_kernel.cuh, instantiated per RNG mode in smmc_mc_{compat,bootstrap,gaussian,sobol}.cu.
 //
 // Replaces compute_sum_kernel / impl_vector_add_gpu (reference src/simulations.cu:249-267, src/gpu.cu:8-14).
+#include <cstdlib>
+#include <cstring>
+
 #include "smmc_kernels.cuh"
 
 #include "../../include/smmc.h"
@@ -175,22 +178,11 @@ __global__ void debug_philox_kernel(const uint32_t *ctr, PhiloxKeys keys, int n,
   for (int j = 0; j < 4; j++) out[4 * t + j] = w[j];
 }
 
-// ---- reduce_mean / vector_add ------------------------------------------------------------------------------------
-// single-pass sum: float4 grid-stride loads, fp64 accumulation, block partials + last-block-done merge
-__global__ void __launch_bounds__(512) reduce_sum_kernel(const float *__restrict__ v, int64_t n, double *partials,
-                                                         unsigned int *ticket, double *sum_out) {
-  double acc = 0.0;
-  const int64_t n4 = n >> 2;
-  const float4 *v4 = reinterpret_cast<const float4 *>(v);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    const float4 q = __ldg(v4 + i);
-    acc += ((double)q.x + (double)q.y) + ((double)q.z + (double)q.w);
-  }
-  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) acc += (double)v[i];
+// block -> grid stage of the sum: warp shuffle, block partial, last-block-done merge in block order (deterministic bits)
+__device__ __forceinline__ void reduce_sum_epilogue(double acc, double *partials, unsigned int *ticket, double *sum_out) {
 #pragma unroll
   for (int st = 16; st >= 1; st >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, st);
-  __shared__ double ws[16];
+  __shared__ double ws[32];
   __shared__ bool last;
   if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = acc;
   __syncthreads();
@@ -208,6 +200,108 @@ __global__ void __launch_bounds__(512) reduce_sum_kernel(const float *__restrict
     for (unsigned g = 0; g < gridDim.x; g++) t += __ldcg(partials + g);
     *sum_out = t;
   }
+}
+
+// ---- reduce_mean / vector_add ------------------------------------------------------------------------------------
+// Single-pass sum of n floats (replaces the reference's multi-launch strided compute_sum_kernel, src/simulations.cu:249-341).
+// HBM-bound: 4 B per element and nothing else.  Streaming 16-byte loads (ld.global.cs: read once, evict first), four
+// independent loads and fp64 accumulators per thread per iteration (148 x 4 CTAs x 512 threads x 64 B = 19 MB in flight),
+// any 4-byte-aligned pointer (scalar head up to the first 16-byte boundary), block partials + last-block-done merge in
+// block order (deterministic bits).
+__global__ void __launch_bounds__(512) reduce_sum_kernel(const float *__restrict__ v, int64_t n, double *partials,
+                                                         unsigned int *ticket, double *sum_out) {
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t head = (int64_t)(((16u - (uint32_t)(reinterpret_cast<uintptr_t>(v) & 15u)) & 15u) >> 2);
+  if (head > n) head = n;
+#ifndef SMMC_RED_UNROLL
+#define SMMC_RED_UNROLL 2
+#endif
+#ifndef SMMC_RED_LD
+#define SMMC_RED_LD __ldcs
+#endif
+  constexpr int U = SMMC_RED_UNROLL;
+  double a[U];
+#pragma unroll
+  for (int k = 0; k < U; k++) a[k] = 0.0;
+  if (gtid < head) a[0] += (double)v[gtid];
+  const float4 *v4 = reinterpret_cast<const float4 *>(v + head);
+  const int64_t n4 = (n - head) >> 2;
+  int64_t i = gtid;
+  for (; i + (U - 1) * stride < n4; i += U * stride) {
+    float4 q[U];
+#pragma unroll
+    for (int k = 0; k < U; k++) q[k] = SMMC_RED_LD(v4 + i + k * stride);
+#pragma unroll
+    for (int k = 0; k < U; k++) a[k] += ((double)q[k].x + (double)q[k].y) + ((double)q[k].z + (double)q[k].w);
+  }
+  for (; i < n4; i += stride) {
+    const float4 q = SMMC_RED_LD(v4 + i);
+    a[0] += ((double)q.x + (double)q.y) + ((double)q.z + (double)q.w);
+  }
+  double acc = 0.0;
+#pragma unroll
+  for (int k = 0; k < U; k++) acc += a[k];
+  for (int64_t t = head + (n4 << 2) + gtid; t < n; t += stride) acc += (double)v[t];
+  reduce_sum_epilogue(acc, partials, ticket, sum_out);
+}
+
+// The same sum for large inputs, B200-style: every CTA streams its 32 KB chunks through a 3-stage shared-memory ring
+// filled by TMA bulk copies (cp.async.bulk + mbarrier complete_tx; UBLKCP in SASS), 2 CTAs per SM = 192 KB of loads in
+// flight per SM that cost no registers and no LSU address instructions; the threads read the landed chunk with
+// conflict-free LDS.128 and accumulate in fp64.  Chunk c of the 16-byte-aligned middle part goes to CTA c % grid; the
+// unaligned head (< 4 floats) and the tail (< one chunk) are read with plain loads.
+constexpr int kRedThreads = 512;
+constexpr int kRedStages = 3;
+constexpr int kRedChunkFloats = 8192;  // 32 KB
+constexpr size_t kRedSmemBytes = 128 + (size_t)kRedStages * kRedChunkFloats * 4;
+
+__global__ void __launch_bounds__(kRedThreads, 2) reduce_sum_tma_kernel(const float *__restrict__ v, int64_t n, double *partials,
+                                                                        unsigned int *ticket, double *sum_out) {
+  extern __shared__ __align__(128) unsigned char red_smem[];
+  uint64_t *bar = reinterpret_cast<uint64_t *>(red_smem);
+  float4 *buf = reinterpret_cast<float4 *>(red_smem + 128);
+  const int tid = threadIdx.x;
+  const int64_t G = gridDim.x, b = blockIdx.x;
+  int64_t head = (int64_t)(((16u - (uint32_t)(reinterpret_cast<uintptr_t>(v) & 15u)) & 15u) >> 2);
+  if (head > n) head = n;
+  const float *mid = v + head;
+  const int64_t n_chunks = (n - head) / kRedChunkFloats;
+  const int64_t my = n_chunks > b ? (n_chunks - b + G - 1) / G : 0;  // chunks b, b + G, ...
+  if (tid == 0) {
+    for (int s = 0; s < kRedStages; s++) mbar_init(bar + s, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int64_t k = 0; k < my && k < kRedStages; k++) {
+      mbar_arrive_expect_tx(bar + k, kRedChunkFloats * 4);
+      tma_bulk_g2s(buf + k * (kRedChunkFloats / 4), mid + (b + k * G) * kRedChunkFloats, kRedChunkFloats * 4, bar + k);
+    }
+  }
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  for (int64_t k = 0; k < my; k++) {
+    const int s = (int)(k % kRedStages);
+    mbar_wait(bar + s, (uint32_t)((k / kRedStages) & 1));
+    const float4 *src = buf + s * (kRedChunkFloats / 4);
+    const float4 q0 = src[tid], q1 = src[tid + kRedThreads], q2 = src[tid + 2 * kRedThreads], q3 = src[tid + 3 * kRedThreads];
+    a0 += ((double)q0.x + (double)q0.y) + ((double)q0.z + (double)q0.w);
+    a1 += ((double)q1.x + (double)q1.y) + ((double)q1.z + (double)q1.w);
+    a2 += ((double)q2.x + (double)q2.y) + ((double)q2.z + (double)q2.w);
+    a3 += ((double)q3.x + (double)q3.y) + ((double)q3.z + (double)q3.w);
+    __syncthreads();  // every thread has read stage s: it can be refilled
+    if (tid == 0 && k + kRedStages < my) {
+      mbar_arrive_expect_tx(bar + s, kRedChunkFloats * 4);
+      tma_bulk_g2s(buf + s * (kRedChunkFloats / 4), mid + (b + (k + kRedStages) * G) * kRedChunkFloats, kRedChunkFloats * 4,
+                   bar + s);
+    }
+  }
+  double acc = (a0 + a1) + (a2 + a3);
+  // head and tail (fewer than 4 + 8192 floats in total): plain loads, grid-strided
+  const int64_t gtid = b * kRedThreads + tid, stride = G * kRedThreads;
+  if (gtid < head) acc += (double)v[gtid];
+  for (int64_t t = head + n_chunks * kRedChunkFloats + gtid; t < n; t += stride) acc += (double)v[t];
+  reduce_sum_epilogue(acc, partials, ticket, sum_out);
 }
 
 __global__ void vector_add_kernel(float *__restrict__ out, const float *__restrict__ a, const float *__restrict__ b,
@@ -309,7 +403,16 @@ cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n,
 
 cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
                               double *sum_dev, int n_sms, cudaStream_t s) {
-  reduce_sum_kernel<<<n_sms * 4, 512, 0, s>>>(v_dev, n, partials_dev, ticket_dev, sum_dev);
+  // >= 4 chunks per CTA: the TMA-pipelined kernel (2 CTAs per SM); smaller inputs: plain streaming loads
+  const char *force = getenv("SMMC_REDUCE");  // development knob: "tma" / "ldg"
+  const bool big = n >= (int64_t)n_sms * 2 * 4 * kRedChunkFloats;
+  if ((big && !(force && !strcmp(force, "ldg"))) || (force && !strcmp(force, "tma"))) {
+    cudaError_t e = cudaFuncSetAttribute(reduce_sum_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRedSmemBytes);
+    if (e != cudaSuccess) return e;
+    reduce_sum_tma_kernel<<<n_sms * 2, kRedThreads, kRedSmemBytes, s>>>(v_dev, n, partials_dev, ticket_dev, sum_dev);
+  } else {
+    reduce_sum_kernel<<<n_sms * 4, 512, 0, s>>>(v_dev, n, partials_dev, ticket_dev, sum_dev);
+  }
   return cudaGetLastError();
 }
 

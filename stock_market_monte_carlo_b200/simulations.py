@@ -250,6 +250,15 @@ def reduce_mean_gpu(vec, n):
     return float(out.value)
 
 
+def reduce_mean_device(ptr, n, device=0, stream=0):
+    """Mean of n floats resident on `device` (e.g. a torch tensor's data_ptr()); returns (mean, kernel_ms): the
+    single-pass HBM-bound reduction behind reduce_mean_gpu without the host round trip."""
+    lib = N.load()
+    out, ms = C.c_float(), C.c_float()
+    N.check(lib.smmc_reduce_mean_device(int(ptr), int(n), int(device), int(stream) or None, C.byref(out), C.byref(ms)))
+    return float(out.value), float(ms.value)
+
+
 def vector_add(out, a, b, n):
     """reference src/gpu.cpp:7-15 (host loop)."""
     out[:n] = np.asarray(a[:n], dtype=np.float32) + np.asarray(b[:n], dtype=np.float32)

@@ -255,6 +255,27 @@ def test_callable_from_a_worker_thread(S, table):
     assert np.array_equal(totals.array, ref.finals)
 
 
+def test_reduce_mean_device_pointer(S):
+    """smmc_reduce_mean_device: device-resident input, any 4-byte alignment, 64-bit counts, exact fp64 accumulation"""
+    import torch
+    rng = np.random.default_rng(5)
+    h = (rng.standard_normal(3_000_003) * 1000.0 + 5000.0).astype(np.float32)
+    d = torch.from_numpy(h).cuda()
+    import os
+    try:
+        for kernel in ("ldg", "tma"):  # plain streaming loads / the TMA-pipelined kernel (forced here; by size otherwise)
+            os.environ["SMMC_REDUCE"] = kernel
+            for off, n in ((0, h.size), (1, h.size - 1), (2, 1), (3, 4097), (5, 2_000_000), (0, 8192 * 296 + 5), (3, 8192 * 300 + 1)):
+                got, ms = S.reduce_mean_device(d.data_ptr() + 4 * off, n)
+                assert got == np.float32(h[off:off + n].astype(np.float64).mean()), (kernel, off, n)
+                assert ms > 0.0
+    finally:
+        os.environ.pop("SMMC_REDUCE", None)
+    big = torch.full((1 << 28,), 1.5, dtype=torch.float32, device="cuda")  # 1 GiB: larger than L2
+    got, ms = S.reduce_mean_device(big.data_ptr(), big.numel(), stream=torch.cuda.current_stream().cuda_stream)
+    assert got == 1.5
+
+
 def test_reduce_mean_and_vector_add(S):
     rng = np.random.default_rng(0)
     for n in (1, 3, 1000, 1_000_003, 20_000_000):

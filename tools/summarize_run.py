@@ -42,10 +42,15 @@ tot = sum(sum(v) for v in agg.values())
 for k, v in agg.items():
     print(f"{len(v):3d} x {k[:90]:90s} avg {sum(v) / len(v):10.1f} us  share {100 * sum(v) / tot:5.2f}%")
 traffic = {}
-for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian", "sobol_bootstrap"]:
+try:  # keep entries of captures that are not part of this run (e.g. reduce_mean)
+    traffic = dict(json.load(open("profiles/ncu_traffic.json"))["bytes_per_launch"])
+except Exception:
+    pass
+for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian", "sobol_bootstrap", "reduce_mean"]:
     if not os.path.exists(f"{G}/prof_{m}.ncu-rep"):
         continue
-    print(f"\n## ncu --set full --clock-control none: python tools/run_one.py {m} (the bench launch: 100M x 360; sobol 5M x 1000)")
+    print(f"\n## ncu --set full --clock-control none: " + ("python bench.py --workload reduce_mean (1 GiB of floats)" if m == "reduce_mean" else
+          f"python tools/run_one.py {m} (the bench launch: 100M x 360; sobol 5M x 1000)"))
     sys.stdout.flush()
     subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "ncu_summary.py"), f"{G}/prof_{m}.ncu-rep"])
     raw = subprocess.run(["ncu", "-i", f"{G}/prof_{m}.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
