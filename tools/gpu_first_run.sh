@@ -10,6 +10,7 @@ python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "ben
 for w in c3 c3compat c4 c4boot; do
   python bench.py --workload $w --steps 30 --no-cpu-baseline > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; cat gpurun_out/bench_$w.json
 done
+python bench.py --workload reduce_mean > gpurun_out/bench_reduce_mean.json 2> gpurun_out/bench_reduce_mean.err; cat gpurun_out/bench_reduce_mean.json
 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2>&1; cat gpurun_out/bench_ref.json
 # ---- ncu: launch list of the bench command, then one full capture of the top kernel per mode
 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain_bench.log 2>&1 &&
@@ -25,4 +26,7 @@ for m in sobol_gaussian sobol_bootstrap; do
   ncu --set full --clock-control none --import-source on -k regex:mc_kernel -s 1 -c 1 -f -o gpurun_out/prof_$m \
       python tools/run_one.py $m 5000000 1000 > gpurun_out/ncu_$m.log 2>&1
 done
+python bench.py --workload reduce_mean --steps 5 --warmup 3 > gpurun_out/plain_reduce_mean.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:reduce_sum_tma -s 2 -c 1 -f -o gpurun_out/prof_reduce_mean \
+    python bench.py --workload reduce_mean --steps 5 --warmup 3 > gpurun_out/ncu_reduce_mean.log 2>&1
 ls -la gpurun_out

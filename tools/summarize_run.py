@@ -26,6 +26,11 @@ for w in ["c2", "c3", "c3compat", "c4", "c4boot"]:
         print("   cpu_baseline:", d["cpu_baseline"])
     if d.get("extras"):
         print("   extras:", d["extras"])
+if os.path.exists(f"{G}/bench_reduce_mean.json"):
+    d = json.loads(open(f"{G}/bench_reduce_mean.json").read().strip().splitlines()[-1])
+    r = d["roofline"]
+    print(f"reduce_mean value {d['value']:.4e} elements/s  kernel_ms {r['kernel_ms']:.5f}  {r['achieved']:.1f} GB/s of {r['peak']} (hbm, measured copy)  "
+          f"frac {r['frac']:.3f}  traffic {r.get('traffic')} vs algorithmic {r.get('algorithmic_bytes')}  e2e {d['e2e']['value']:.4e} elements/s  exact {d['result']['exact']}")
 d = json.loads(open(f"{G}/bench_ref.json").read().strip().splitlines()[-1])
 print("--impl reference:", d["value"], d["cpu_baseline"])
 print("\n## ncu launch list of: python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e  (gpu__time_duration.sum)")
