@@ -1,7 +1,7 @@
 """Same-box reference number: the reference's own kernels (src/simulations.cu unmodified, compiled for sm_100a into
 oracle/_ref/libref_gpu.so) on config C3's shape, next to this build's BOOTSTRAP_COMPAT on the same inputs.
-Development / profiling driver (run it under `ncu --metrics gpu__time_duration.sum` for kernel-only times).
-usage: python tools/ref_gpu_time.py [N] [P]"""
+Checker-side timing driver (lives under tests/: only tests may call into oracle/) (run it under `ncu --metrics gpu__time_duration.sum` for kernel-only times).
+usage: python tests/ref_gpu_time.py [N] [P]"""
 import os
 import sys
 import time
