@@ -436,8 +436,13 @@ def main():
     extras = None
     if world == 1 and not args.no_e2e and not sobol:
         q, q_ms = S.quantiles(mode, B, P, initial_capital=V0, returns=table, seed=seed, device=local, return_ms=True, **GAUSS)
+        _, q_f, q_extra_ms = S.simulate_with_quantiles(mode, B, P, initial_capital=V0, returns=table, seed=seed, device=local,
+                                                       hist_bins=HIST_BINS, hist_range=wl["hist_range"], target=V0,
+                                                       want_block_partials=wl["block_partials"], **GAUSS)
         extras = {"quartiles_min_q1_med_q3_max": [float(x) for x in q], "quartiles_device_ms": q_ms,
-                  "quartiles_how": "smmc_quantiles: 3 replays of the workload, 11+11+10-bit radix select on ordered keys; exact"}
+                  "quartiles_how": "smmc_quantiles: 3 replays of the workload, 11+11+10-bit radix select on ordered keys; exact",
+                  "quartiles_riding_along_extra_ms": q_extra_ms, "quartiles_riding_along_equal": bool(np.array_equal(q, q_f)),
+                  "quartiles_riding_along_how": "smmc_run_select: the first select pass shares the statistics launch; 2 extra replays"}
 
     if rank != 0:
         if world > 1:

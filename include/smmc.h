@@ -186,6 +186,10 @@ smmc_status smmc_select_begin(smmc_select_state *st, int32_t n_targets, const ui
  * is asynchronous on cfg->stream and rows >= the number produced are zeroed.  Counters are exact and
  * SUM-reducible across shards. */
 smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *st, uint64_t *hist);
+/* smmc_run with the FIRST select pass riding along: the same launch that produces the statistics / histogram / partials /
+ * finals of `cfg` also builds the first 11-bit digit histogram (st->bits_done must be 0), so statistics + order statistics
+ * cost three replays instead of four.  hist as in smmc_select_pass (host); host pointers only. */
+smmc_status smmc_run_select(const smmc_config *cfg, smmc_result *out, const smmc_select_state *st, uint64_t *hist);
 /* Consume the (globally summed) HOST histogram of the pass just run: fixes the next 11/11/10 key bits per target. */
 smmc_status smmc_select_advance(smmc_select_state *st, const uint64_t *hist);
 /* After the last pass (bits_done == 32): the order statistics themselves. */

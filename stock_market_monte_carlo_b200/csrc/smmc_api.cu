@@ -788,6 +788,35 @@ smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *ss
   return SMMC_OK;
 }
 
+smmc_status smmc_run_select(const smmc_config *cfg, smmc_result *out, const smmc_select_state *sst, uint64_t *hist) {
+  smmc_status st = validate(cfg, out);
+  if (st != SMMC_OK) return st;
+  if (!hist) return fail(SMMC_ERR_INVALID_ARG, "run_select: null histogram");
+  if (cfg->flags & (SMMC_FLAG_DEVICE_POINTERS | SMMC_FLAG_NO_SYNC))
+    return fail(SMMC_ERR_INVALID_ARG, "run_select: host pointers only (use smmc_run + smmc_select_pass with device pointers)");
+  SelectPass sp;
+  st = make_select_pass(sst, &sp);
+  if (st != SMMC_OK) return st;
+  if (sst->bits_done != 0) return fail(SMMC_ERR_INVALID_ARG, "run_select: only the first pass can ride along (bits_done = %d)", sst->bits_done);
+  Context *ctx = nullptr;
+  st = get_context(cfg->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  Pending pd;
+  st = enqueue(cfg, out, ctx, &pd, &sp);
+  if (st != SMMC_OK) return st;
+  out->gpu_launches = pd.launches;
+  std::vector<double> stats((size_t)pd.stats_len);
+  float ms = 0.0f;
+  memset(hist, 0, (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS * sizeof(uint64_t));
+  CU(cudaMemcpyAsync(hist, pd.sel_dev, (size_t)pd.sel_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, pd.stream));
+  st = collect(pd, out, stats.data(), &ms);
+  if (st != SMMC_OK) return st;
+  out->device_ms = ms;
+  return smmc_stats_finalize(stats.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count,
+                             &out->mean, &out->m2, out->hist);
+}
+
 smmc_status smmc_select_advance(smmc_select_state *st, const uint64_t *hist) {
   if (!st || !hist) return fail(SMMC_ERR_INVALID_ARG, "select_advance: null argument");
   SelectPass sp;
@@ -1051,7 +1080,7 @@ smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int3
 }
 
 const char *smmc_last_error(void) { return g_err; }
-const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 1)"; }
+const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 2)"; }
 int32_t smmc_device_count(void) { return probe_devices(); }
 
 void smmc_shutdown(void) {

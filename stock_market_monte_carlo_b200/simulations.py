@@ -79,6 +79,7 @@ class Result:
     block_means: Optional[np.ndarray] = None
     block_vars: Optional[np.ndarray] = None
     hist: Optional[np.ndarray] = None
+    select_hist: Optional[np.ndarray] = None  # first radix-select digit histogram (simulate(select=...))
     device_ms: float = 0.0
     gpu_launches: int = 0
 
@@ -138,9 +139,11 @@ def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=
 
 def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
              gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
-             want_finals=False, want_block_partials=False, device=0, n_gpus=1, **withdrawals) -> Result:
+             want_finals=False, want_block_partials=False, device=0, n_gpus=1, select=None, **withdrawals) -> Result:
     """One blocking run through `smmc_run` / `smmc_run_multi` with HOST buffers (the call a user makes).
-    withdrawals: withdraw_fixed=, withdraw_pct=, withdraw_pct_schedule= (include/smmc.h, ABI 2)."""
+    withdrawals: withdraw_fixed=, withdraw_pct=, withdraw_pct_schedule= (include/smmc.h, ABI 2).
+    select: a fresh SelectState -- the first radix-select pass rides along (`smmc_run_select`, one GPU) and its digit
+    histogram is returned as Result.select_hist (see simulate_with_quantiles)."""
     lib = N.load()
     cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset,
                             gauss_mean, gauss_std, target, hist_bins, hist_range, device, **withdrawals)
@@ -158,7 +161,12 @@ def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=Non
     if hist_bins:
         out.hist = np.zeros(int(hist_bins) + 2, dtype=np.uint64)
         res.hist = out.hist.ctypes.data
-    if n_gpus == 1:
+    if select is not None:
+        if n_gpus != 1:
+            raise ValueError("select rides along on one GPU only; use quantiles(..., n_gpus=) or distributed.quantiles_sharded")
+        out.select_hist = np.zeros(N.SELECT_MAX_TARGETS * N.SELECT_BINS, dtype=np.uint64)
+        N.check(lib.smmc_run_select(C.byref(cfg), C.byref(res), C.byref(select.st), out.select_hist.ctypes.data))
+    elif n_gpus == 1:
         N.check(lib.smmc_run(C.byref(cfg), C.byref(res)))
     else:
         N.check(lib.smmc_run_multi(C.byref(cfg), int(n_gpus), C.byref(res)))
@@ -297,6 +305,26 @@ def quantiles(mode, n_simulations, n_periods, ranks=None, initial_capital=1000.0
     N.check(lib.smmc_quantiles(C.byref(cfg), int(n_gpus), int(r.size), r.ctypes.data, out.ctypes.data, C.byref(ms)))
     del keep
     return (out, float(ms.value)) if return_ms else out
+
+
+def simulate_with_quantiles(mode, n_simulations, n_periods, ranks=None, **kw):
+    """Statistics AND exact order statistics of one run in three replays instead of four: the first radix-select pass
+    rides along with the statistics launch (`smmc_run_select`), two more replays fix the remaining key bits.
+    Returns (Result, values, device_ms of the two extra replays); kw as for simulate()."""
+    st = SelectState(quartile_ranks(n_simulations) if ranks is None else ranks)
+    r = simulate(mode, n_simulations, n_periods, select=st, **kw)
+    st.advance(r.select_hist)
+    skw = {k: v for k, v in kw.items() if k not in ("target", "hist_bins", "hist_range", "want_finals", "want_block_partials", "n_gpus")}
+    cfg, keep = make_config(mode, n_simulations, n_periods, kw.get("initial_capital", 1000.0), kw.get("returns"),
+                            kw.get("seed", 0), kw.get("stream_offset", 0), kw.get("gauss_mean", 0.5),
+                            kw.get("gauss_std", 10.0 / 12.0), device=kw.get("device", 0),
+                            **{k: v for k, v in skw.items() if k.startswith("withdraw")})
+    extra_ms = 0.0
+    while not st.done:
+        st.advance(st.run_pass(cfg))
+        extra_ms += float(kernel_times(kw.get("device", 0), 1)[-1])
+    del keep
+    return r, st.values(), extra_ms
 
 
 def update_quartiles(quartiles, mode, n_simulations, n_periods, **kw):

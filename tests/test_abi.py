@@ -150,7 +150,8 @@ def test_new_entry_points_fail_loudly_without_a_device(S, table):
     for call in (lambda: S.quantiles("gaussian", 1000, 12),
                  lambda: S.trajectories("bootstrap", 10, 12, returns=table),
                  lambda: S.SelectState([0]).run_pass(S.make_config("gaussian", 1000, 12)[0]),
-                 lambda: S.reduce_mean_device(0x1000, 10)):
+                 lambda: S.reduce_mean_device(0x1000, 10),
+                 lambda: S.simulate("gaussian", 1000, 12, select=S.SelectState([0]))):
         with pytest.raises(S.SmmcError) as e:
             call()
         assert e.value.status == 2 and "no CPU fallback" in str(e.value)
@@ -165,6 +166,7 @@ def test_new_entry_points_validate_before_probing(S, table):
         lambda: S.trajectories("gaussian", 4, 12, stream_offset=3),
         lambda: S.plan_launch("gaussian", 100, 12, select_targets=9),
         lambda: S.plan_launch("gaussian", 100, 12, n_sms=0),
+        lambda: S.simulate("gaussian", 1000, -1, select=S.SelectState([0])),
         lambda: S.reduce_mean_device(0, 10),          # null pointer
         lambda: S.reduce_mean_device(0x1000, 0),      # n <= 0
         lambda: S.reduce_mean_device(0x1002, 10),     # not 4-byte aligned

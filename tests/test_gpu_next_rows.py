@@ -286,3 +286,23 @@ def test_fused_benchmark_program_prints_the_reference_programs_statistics(S, O, 
                          check=True).stdout
     g = S.simulate("gaussian", 100_000, 120, seed=7)
     assert abs(float(re.search(r"mean: ([\d.]+)", out).group(1)) - g.mean) < 0.006
+
+@pytest.mark.parametrize("mode", ALL_MODES)
+def test_first_select_pass_rides_along(S, table, mode):
+    """smmc_run_select: statistics + quartiles in three replays -- the statistics are bit-identical to smmc_run's, the
+    order statistics to smmc_quantiles' (and so to the sorted finals)"""
+    kw = mode_kwargs(mode, table)
+    N, P = 300_001, 45
+    full = dict(hist_bins=64, hist_range=(0.0, 20_000.0), want_block_partials=True, want_finals=True, **kw)
+    plain = S.simulate(mode, N, P, **full)
+    r, q, extra_ms = S.simulate_with_quantiles(mode, N, P, **full)
+    assert (r.count, r.below_count, r.mean, r.m2) == (plain.count, plain.below_count, plain.mean, plain.m2)
+    assert np.array_equal(r.hist, plain.hist) and np.array_equal(r.finals, plain.finals)
+    assert np.array_equal(r.block_means, plain.block_means) and np.array_equal(r.block_vars, plain.block_vars)
+    assert int(r.select_hist[:2048].sum()) == N and not r.select_hist[2048:].any()
+    assert np.array_equal(q, np.sort(plain.finals)[S.quartile_ranks(N)])
+    assert np.array_equal(q, S.quantiles(mode, N, P, **kw))
+    assert extra_ms > 0.0
+    ranks = [5, 5, N - 2]
+    _, q2, _ = S.simulate_with_quantiles(mode, N, P, ranks=ranks, **kw)
+    assert np.array_equal(q2, np.sort(plain.finals)[ranks])
