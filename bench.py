@@ -236,7 +236,7 @@ def run_reduce_mean(args):
         raise SystemExit("bench.py needs a B200: the product has no CPU fallback")
     torch.cuda.set_device(0)
     n = args.paths or (1 << 28)
-    steps, warm = (args.steps or 50), max(args.warmup, 3)
+    steps, warm = (args.steps or 2000), max(args.warmup, 3)  # ~0.2 ms per step: long enough for the 100 ms clock samples
     bufs = [torch.full((n,), 1.0 + 0.25 * i, dtype=torch.float32, device="cuda") for i in range(2)]  # alternate: 2 GiB > L2
     stream = torch.cuda.current_stream().cuda_stream
     for i in range(warm):
@@ -280,6 +280,57 @@ def run_reduce_mean(args):
     return 0
 
 
+def run_vector_add(args):
+    """out = a + b over 2^27 device-resident floats per vector (3 x 512 MiB per step, larger than L2) through
+    smmc_vector_add_device.  Algorithmic traffic: 12 bytes per element (two reads, one write)."""
+    import torch
+    import stock_market_monte_carlo_b200 as S
+    if S.load().smmc_device_count() < 1:
+        raise SystemExit("bench.py needs a B200: the product has no CPU fallback")
+    torch.cuda.set_device(0)
+    n = args.paths or (1 << 27)
+    steps, warm = (args.steps or 2000), max(args.warmup, 3)  # ~0.2 ms per step: long enough for the 100 ms clock samples
+    a = torch.full((n,), 1.25, dtype=torch.float32, device="cuda")
+    b = torch.full((n,), 2.5, dtype=torch.float32, device="cuda")
+    out = torch.empty_like(a)
+    stream = torch.cuda.current_stream().cuda_stream
+    for _ in range(warm):
+        S.vector_add_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, stream=stream)
+    sampler = ClockSampler([0])
+    sampler.begin()
+    ms = [S.vector_add_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, stream=stream) for _ in range(steps)]
+    sampler.end()
+    clocks = sampler.stop()
+    ok = bool(torch.all(out == 3.75).item())
+    ha, hb = torch.ones(1 << 24).numpy(), torch.ones(1 << 24).numpy()
+    ho = ha.copy()
+    S.vector_add_gpu(ho, ha, hb, ha.size)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        S.vector_add_gpu(ho, ha, hb, ha.size)
+    e2e_s = (time.perf_counter() - t0) / 3
+    peaks = measured_peaks()
+    peak = float(peaks.get("hbm_gbs") or 6400.0)
+    k_ms = sum(ms) / len(ms)
+    gbs = 12.0 * n / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": "elements/sec (vector_add_gpu, device-timed)", "value": n / (k_ms * 1e-3), "unit": "elements/s", "n_gpus": 1,
+        "steps": steps, "warmup": warm, "ms_per_step": k_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"vector_add_gpu over {n} device-resident floats per vector ({12 * n / 2**30:.2f} GiB of traffic)",
+                   "l2": "1.5 GiB touched per step: larger than L2"},
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                     "traffic": ncu_traffic("vector_add") if n == (1 << 27) else None, "algorithmic_bytes": 12 * n, "kernel": "smmc::vector_add_kernel", "kernel_ms": k_ms, "bytes_per_element": 12,
+                     "peak_source": ("MEASURED_PEAKS.json hbm_gbs (copy: read + write bytes)" if peaks.get("hbm_gbs")
+                                     else "fallback 6400 GB/s (B200_PROFILING.md)")},
+        "e2e": {"value": ha.size / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(2 * ha.nbytes),
+                "d2h_bytes_per_step": int(ha.nbytes), "api": "vector_add_gpu(host arrays) -> smmc_vector_add: pageable H2D x2 + kernel + D2H"},
+        "gpu_launches": steps, "clocks": clocks, "result": {"exact": ok},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 # ---- the GPU arm --------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -287,13 +338,15 @@ def main():
     ap.add_argument("--steps", type=int, default=0, help="timed steps (default 100; 5 for the 1.8 s steps of c5)")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["reduce_mean"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["reduce_mean", "vector_add"])
     ap.add_argument("--paths", type=int, default=0, help="override paths per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     if args.workload == "reduce_mean":
         return run_reduce_mean(args)
+    if args.workload == "vector_add":
+        return run_vector_add(args)
     wl = dict(WORKLOADS[args.workload])
     if args.paths:
         wl["paths"] = args.paths

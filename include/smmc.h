@@ -154,6 +154,11 @@ smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t dev
                                     float *kernel_ms);
 /* out = a + b on the device (reference vector_add_gpu, src/gpu.cu:17-47). Host pointers. */
 smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device);
+/* The same over DEVICE-resident vectors (any 4-byte alignment; 16-byte aligned pointers take the vector path), on `stream`
+ * (NULL = legacy default stream); blocks until done.  kernel_ms (nullable): CUDA-event duration of the kernel, which is
+ * HBM-bound at 12 bytes per element. */
+smmc_status smmc_vector_add_device(float *out_dev, const float *a_dev, const float *b_dev, int64_t n, int32_t device,
+                                   void *stream, float *kernel_ms);
 
 /* ---- exact order statistics of the finals without writing them to HBM ------------------- */
 

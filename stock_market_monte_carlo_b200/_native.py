@@ -107,7 +107,7 @@ class SmmcError(RuntimeError):
 
 # every symbol include/smmc.h declares (tests check the library exports exactly these)
 C_ABI_SYMBOLS = [
-    "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_vector_add",
+    "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_vector_add", "smmc_vector_add_device",
     "smmc_debug_draws", "smmc_debug_philox", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
@@ -138,6 +138,8 @@ def load():
     lib.smmc_stats_finalize.restype = C.c_int
     lib.smmc_run_select.argtypes = [P(SmmcConfig), P(SmmcResult), P(SmmcSelectState), C.c_void_p]
     lib.smmc_run_select.restype = C.c_int
+    lib.smmc_vector_add_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, P(C.c_float)]
+    lib.smmc_vector_add_device.restype = C.c_int
     lib.smmc_reduce_mean.argtypes = [C.c_void_p, C.c_int64, C.c_int32, P(C.c_float)]
     lib.smmc_reduce_mean.restype = C.c_int
     lib.smmc_reduce_mean_device.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, P(C.c_float), P(C.c_float)]

@@ -760,9 +760,28 @@ smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t 
   float *da = (float *)ctx->scratch.p, *db = da + n, *dout = db + n;
   CU(cudaMemcpyAsync(da, a, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
   CU(cudaMemcpyAsync(db, b, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
-  CU(smmc::launch_vector_add(dout, da, db, n, ctx->stream));
+  CU(smmc::launch_vector_add(dout, da, db, n, ctx->n_sms, ctx->stream));
   CU(cudaMemcpyAsync(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  return SMMC_OK;
+}
+
+smmc_status smmc_vector_add_device(float *out_dev, const float *a_dev, const float *b_dev, int64_t n, int32_t device,
+                                   void *stream, float *kernel_ms) {
+  if (n < 0 || (n > 0 && (!out_dev || !a_dev || !b_dev))) return fail(SMMC_ERR_INVALID_ARG, "vector_add_device: bad arguments");
+  if ((reinterpret_cast<uintptr_t>(out_dev) | reinterpret_cast<uintptr_t>(a_dev) | reinterpret_cast<uintptr_t>(b_dev)) & 3u)
+    return fail(SMMC_ERR_INVALID_ARG, "vector_add_device: pointers must be 4-byte aligned");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(cudaSetDevice(device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (kernel_ms) CU(cudaEventRecord(ctx->red0, s));
+  CU(smmc::launch_vector_add(out_dev, a_dev, b_dev, n, ctx->n_sms, s));
+  if (kernel_ms) CU(cudaEventRecord(ctx->red1, s));
+  CU(cudaStreamSynchronize(s));
+  if (kernel_ms) CU(cudaEventElapsedTime(kernel_ms, ctx->red0, ctx->red1));
   return SMMC_OK;
 }
 

@@ -119,6 +119,6 @@ cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n,
 // small reference entry points
 cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
                               double *sum_dev, int n_sms, cudaStream_t s);
-cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, cudaStream_t s);
+cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, int n_sms, cudaStream_t s);
 
 }  // namespace smmc

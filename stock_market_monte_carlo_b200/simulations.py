@@ -267,6 +267,15 @@ def reduce_mean_device(ptr, n, device=0, stream=0):
     return float(out.value), float(ms.value)
 
 
+def vector_add_device(out_ptr, a_ptr, b_ptr, n, device=0, stream=0):
+    """out = a + b over device-resident float vectors (data_ptr()s); returns the kernel's CUDA-event time in ms."""
+    lib = N.load()
+    ms = C.c_float()
+    N.check(lib.smmc_vector_add_device(int(out_ptr), int(a_ptr), int(b_ptr), int(n), int(device), int(stream) or None,
+                                       C.byref(ms)))
+    return float(ms.value)
+
+
 def vector_add(out, a, b, n):
     """reference src/gpu.cpp:7-15 (host loop)."""
     out[:n] = np.asarray(a[:n], dtype=np.float32) + np.asarray(b[:n], dtype=np.float32)

@@ -151,6 +151,7 @@ def test_new_entry_points_fail_loudly_without_a_device(S, table):
                  lambda: S.trajectories("bootstrap", 10, 12, returns=table),
                  lambda: S.SelectState([0]).run_pass(S.make_config("gaussian", 1000, 12)[0]),
                  lambda: S.reduce_mean_device(0x1000, 10),
+                 lambda: S.vector_add_device(0x1000, 0x2000, 0x3000, 10),
                  lambda: S.simulate("gaussian", 1000, 12, select=S.SelectState([0]))):
         with pytest.raises(S.SmmcError) as e:
             call()
@@ -167,6 +168,8 @@ def test_new_entry_points_validate_before_probing(S, table):
         lambda: S.plan_launch("gaussian", 100, 12, select_targets=9),
         lambda: S.plan_launch("gaussian", 100, 12, n_sms=0),
         lambda: S.simulate("gaussian", 1000, -1, select=S.SelectState([0])),
+        lambda: S.vector_add_device(0, 0x1000, 0x1000, 10),
+        lambda: S.vector_add_device(0x1000, 0x1002, 0x1000, 10),
         lambda: S.reduce_mean_device(0, 10),          # null pointer
         lambda: S.reduce_mean_device(0x1000, 0),      # n <= 0
         lambda: S.reduce_mean_device(0x1002, 10),     # not 4-byte aligned

@@ -276,6 +276,20 @@ def test_reduce_mean_device_pointer(S):
     assert got == 1.5
 
 
+def test_vector_add_device_pointer(S):
+    """smmc_vector_add_device: vector path (16-byte aligned), scalar path (misaligned views), tails"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(3)
+    a = torch.randn(1_000_003, device="cuda", generator=g)
+    b = torch.randn(1_000_003, device="cuda", generator=g)
+    out = torch.empty_like(a)
+    for off, n in ((0, a.numel()), (0, 4096), (0, 5), (1, 999_999), (3, 1), (2, 123_457)):
+        out.zero_()
+        ms = S.vector_add_device(out.data_ptr() + 4 * off, a.data_ptr() + 4 * off, b.data_ptr() + 4 * off, n)
+        assert torch.equal(out[off:off + n], a[off:off + n] + b[off:off + n]) and ms > 0.0
+        assert not out[off + n:].any() and not out[:off].any()
+
+
 def test_reduce_mean_and_vector_add(S):
     rng = np.random.default_rng(0)
     for n in (1, 3, 1000, 1_000_003, 20_000_000):

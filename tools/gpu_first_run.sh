@@ -11,6 +11,7 @@ for w in c3 c3compat c4 c4boot; do
   python bench.py --workload $w --steps 30 --no-cpu-baseline > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; cat gpurun_out/bench_$w.json
 done
 python bench.py --workload reduce_mean > gpurun_out/bench_reduce_mean.json 2> gpurun_out/bench_reduce_mean.err; cat gpurun_out/bench_reduce_mean.json
+python bench.py --workload vector_add > gpurun_out/bench_vector_add.json 2> gpurun_out/bench_vector_add.err; cat gpurun_out/bench_vector_add.json
 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2>&1; cat gpurun_out/bench_ref.json
 # ---- ncu: launch list of the bench command, then one full capture of the top kernel per mode
 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain_bench.log 2>&1 &&

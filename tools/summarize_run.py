@@ -26,11 +26,14 @@ for w in ["c2", "c3", "c3compat", "c4", "c4boot"]:
         print("   cpu_baseline:", d["cpu_baseline"])
     if d.get("extras"):
         print("   extras:", d["extras"])
-if os.path.exists(f"{G}/bench_reduce_mean.json"):
-    d = json.loads(open(f"{G}/bench_reduce_mean.json").read().strip().splitlines()[-1])
+for aux in ("reduce_mean", "vector_add"):
+    if not os.path.exists(f"{G}/bench_{aux}.json"):
+        continue
+    d = json.loads(open(f"{G}/bench_{aux}.json").read().strip().splitlines()[-1])
     r = d["roofline"]
-    print(f"reduce_mean value {d['value']:.4e} elements/s  kernel_ms {r['kernel_ms']:.5f}  {r['achieved']:.1f} GB/s of {r['peak']} (hbm, measured copy)  "
-          f"frac {r['frac']:.3f}  traffic {r.get('traffic')} vs algorithmic {r.get('algorithmic_bytes')}  e2e {d['e2e']['value']:.4e} elements/s  exact {d['result']['exact']}")
+    print(f"{aux} value {d['value']:.4e} elements/s  kernel_ms {r['kernel_ms']:.5f}  {r['achieved']:.1f} GB/s of {r['peak']} (hbm, measured copy)  "
+          f"frac {r['frac']:.3f}  traffic {r.get('traffic')} vs algorithmic {r.get('algorithmic_bytes')}  e2e {d['e2e']['value']:.4e} elements/s  exact {d['result']['exact']}  "
+          f"sm_mhz {d['clocks']['sm_mhz']} {d['clocks']['reasons']}")
 d = json.loads(open(f"{G}/bench_ref.json").read().strip().splitlines()[-1])
 print("--impl reference:", d["value"], d["cpu_baseline"])
 print("\n## ncu launch list of: python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e  (gpu__time_duration.sum)")
@@ -51,10 +54,10 @@ try:  # keep entries of captures that are not part of this run (e.g. reduce_mean
     traffic = dict(json.load(open("profiles/ncu_traffic.json"))["bytes_per_launch"])
 except Exception:
     pass
-for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian", "sobol_bootstrap", "reduce_mean"]:
+for m in ["gaussian", "bootstrap", "bootstrap_compat", "sobol_gaussian", "sobol_bootstrap", "reduce_mean", "vector_add"]:
     if not os.path.exists(f"{G}/prof_{m}.ncu-rep"):
         continue
-    print(f"\n## ncu --set full --clock-control none: " + ("python bench.py --workload reduce_mean (1 GiB of floats)" if m == "reduce_mean" else
+    print(f"\n## ncu --set full --clock-control none: " + (f"python bench.py --workload {m}" if m in ("reduce_mean", "vector_add") else
           f"python tools/run_one.py {m} (the bench launch: 100M x 360; sobol 5M x 1000)"))
     sys.stdout.flush()
     subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "ncu_summary.py"), f"{G}/prof_{m}.ncu-rep"])
