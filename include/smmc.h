@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SMMC_ABI_VERSION 2
+#define SMMC_ABI_VERSION 3
 #define SMMC_BLOCK 256          /* logical block = THREADS_PER_BLOCK of the reference (src/simulations.cu:17) */
 #define SMMC_MAX_HIST_BINS 4096
 
@@ -91,6 +91,13 @@ typedef struct smmc_config {
   float withdraw_pct;          /* percent of the value taken out every period */
   const float *withdraw_pct_schedule; /* optional [n_periods] percent per period (overrides withdraw_pct);
                                          always a HOST pointer, copied by the call */
+  /* ---- ABI 3: round count of the counter-based generator of BOOTSTRAP / GAUSSIAN (part of the stream contract).
+   * 0 or 10 = Philox4x32-10 (default; the Random123 recommendation).  7 = Philox4x32-7, the smallest round count that
+   * Salmon et al. (SC'11, table 2) report as Crush-resistant and for which Random123 publishes known-answer vectors:
+   * an explicit opt-in that trades the safety margin for ~30 % less generator work.  Other values are rejected.
+   * Ignored by BOOTSTRAP_COMPAT (reference stream) and the Sobol modes (their digital shift always uses 10 rounds). */
+  int32_t philox_rounds;
+  int32_t reserved0;           /* must be 0 */
 } smmc_config;
 
 /* Device-side reduced statistics, laid out as doubles so that ONE sum-allreduce (ncclFloat64) over
@@ -250,6 +257,16 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
 smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *out);
 /* Philox4x32-10 block function on the device: out[4*i..] = philox(ctr[4*i..], key[0..1]) for i < n. */
 smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t n, int32_t device, uint32_t *out);
+/* The same with `rounds` in {7, 10} (smmc_config.philox_rounds): the device code behind both stream contracts. */
+smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, int32_t rounds, int32_t n, int32_t device,
+                                     uint32_t *out);
+/* Test hook: selects among the compiled variants of a kernel (all variants of a mode produce the same draws; the tests use
+ * this to prove it).  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
+ * (reduce_mean kernel: 1 = streaming loads, 2 = TMA ring), "gauss_tbl" (GAUSSIAN: 4-bit mask of the Box-Muller pairs of a
+ * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0|1), "sobol_unroll",
+ * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch).  value < 0 (or 0 where 0 is not a choice)
+ * restores the default; key NULL resets everything.  Process-wide; nothing in the library reads the environment. */
+smmc_status smmc_debug_set_variant(const char *key, int32_t value);
 
 /* ---- housekeeping ---------------------------------------------------------------------------------------- */
 

@@ -41,6 +41,8 @@ def load():
     lib.orc_compat_index.restype = C.c_int32
     lib.orc_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.orc_philox4x32_10.restype = None
+    lib.orc_philox4x32.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    lib.orc_philox4x32.restype = None
     lib.orc_sobol_set_table.argtypes = [C.c_void_p, C.c_int32]
     lib.orc_sobol_point.argtypes = [C.c_uint64, C.c_int32]
     lib.orc_sobol_point.restype = C.c_uint32
@@ -101,9 +103,10 @@ def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=Non
     return out
 
 
-def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0):
+def draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0, philox_rounds=0):
     lib = load()
-    cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset)
+    cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset,
+                            philox_rounds=philox_rounds)
     out = np.zeros((int(n_paths), int(n_periods)), dtype=np.uint32)
     if lib.orc_draws(C.byref(cfg), int(n_paths), out.ctypes.data) != 0:
         raise ValueError("oracle rejected the configuration")
@@ -164,13 +167,13 @@ def sobol_gauss_pairs(xr, xa, mean_pct=0.0, std_pct=100.0):
     return g
 
 
-def philox(ctr, key):
+def philox(ctr, key, rounds=10):
     lib = load()
     ctr = np.ascontiguousarray(np.asarray(ctr, dtype=np.uint32).reshape(-1, 4))
     key = np.ascontiguousarray(np.asarray(key, dtype=np.uint32).reshape(2))
     out = np.zeros_like(ctr)
     for i in range(ctr.shape[0]):
-        lib.orc_philox4x32_10(ctr[i].ctypes.data, key.ctypes.data, out[i].ctypes.data)
+        lib.orc_philox4x32(ctr[i].ctypes.data, key.ctypes.data, int(rounds), out[i].ctypes.data)
     return out
 
 

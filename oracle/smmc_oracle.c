@@ -68,10 +68,12 @@ int32_t orc_compat_index(uint32_t state, int32_t n_returns) {
 #define PHILOX_W0 0x9E3779B9u
 #define PHILOX_W1 0xBB67AE85u
 
-void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+/* Philox4x32-R: R = 10 is the default of every native mode; R = 7 (smmc_config.philox_rounds) is the smallest round count
+ * Salmon et al. report as Crush-resistant; Random123 publishes known-answer vectors for both (checked in tests/). */
+void orc_philox4x32(const uint32_t ctr[4], const uint32_t key[2], int rounds, uint32_t out[4]) {
   uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
   uint32_t k0 = key[0], k1 = key[1];
-  for (int r = 0; r < 10; r++) {
+  for (int r = 0; r < rounds; r++) {
     uint64_t p0 = (uint64_t)PHILOX_M0 * c0;
     uint64_t p1 = (uint64_t)PHILOX_M1 * c2;
     uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
@@ -84,6 +86,8 @@ void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t ou
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { orc_philox4x32(ctr, key, 10, out); }
+
 /* stream contract of the native modes:
  * counter = (q, path_lo, domain tag, path_hi), key = (seed_lo, seed_hi); call q serves months 6q..6q+5
  * (bootstrap: one 21/22-bit field per month) or 8q..8q+7 (gaussian: one 32-bit word per Box-Muller pair). */
@@ -91,11 +95,15 @@ void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t ou
 #define TAG_GAUSSIAN 0x47415553u  /* "GAUS" */
 #define TAG_SOBOL_SHIFT 0x534F424Cu /* "SOBL" */
 
-static void stream_words(uint64_t path, uint32_t q, uint32_t tag, uint64_t seed, uint32_t w[4]) {
+static void stream_words_r(uint64_t path, uint32_t q, uint32_t tag, uint64_t seed, int rounds, uint32_t w[4]) {
   uint32_t ctr[4] = {q, (uint32_t)path, tag, (uint32_t)(path >> 32)};
   uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
-  orc_philox4x32_10(ctr, key, w);
+  orc_philox4x32(ctr, key, rounds, w);
 }
+static void stream_words(uint64_t path, uint32_t q, uint32_t tag, uint64_t seed, uint32_t w[4]) {
+  stream_words_r(path, q, tag, seed, 10, w);
+}
+static int rounds_of(const smmc_config *cfg) { return cfg->philox_rounds == 7 ? 7 : 10; }
 
 /* six bit fields of one call: f0..f3 = low 21 bits of w0..w3; f4 = w0[31:21]:w1[31:21]; f5 = w2[31:21]:w3[31:21] */
 static uint32_t field_of(const uint32_t w[4], int j) {
@@ -298,7 +306,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
       uint32_t w[4];
       for (int m = 0; m < P; m++) {
         int j = m % 6;
-        if (j == 0) stream_words(path, (uint32_t)(m / 6), TAG_BOOTSTRAP, cfg->seed, w);
+        if (j == 0) stream_words_r(path, (uint32_t)(m / 6), TAG_BOOTSTRAP, cfg->seed, rounds_of(cfg), w);
         uint32_t idx = boot_index(w, j, (uint32_t)n);
         if (draws) draws[m] = idx;
         total = apply_flow(rc, fmaf(total, rc->tbl[idx], total), m);
@@ -311,7 +319,7 @@ static float simulate_path_full(const run_consts *rc, uint64_t path, uint32_t *d
       float g[2];
       for (int m = 0; m < P; m++) {
         int j = m % 8;
-        if (j == 0) stream_words(path, (uint32_t)(m / 8), TAG_GAUSSIAN, cfg->seed, w);
+        if (j == 0) stream_words_r(path, (uint32_t)(m / 8), TAG_GAUSSIAN, cfg->seed, rounds_of(cfg), w);
         if ((j & 1) == 0) gauss_pair(w[j >> 1], rc->gc, &g[0], &g[1]);
         if (draws) draws[m] = (j & 1) ? w[j >> 1] * 0x9E3779B1u : (w[j >> 1] & 0xFFFFFu); /* radius field | hashed angle word */
         total = apply_flow(rc, total * g[j & 1], m);

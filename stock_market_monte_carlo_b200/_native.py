@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SMMC_LIB") or os.path.join(_HERE, "lib", "libsmmc.so")  # SMMC_LIB: development override
 
-SMMC_ABI_VERSION = 2
+SMMC_ABI_VERSION = 3
 SMMC_BLOCK = 256
 SMMC_STATS_HEADER = 6
 SMMC_MAX_HIST_BINS = 4096
@@ -57,6 +57,8 @@ class SmmcConfig(C.Structure):
         ("withdraw_fixed", C.c_float),
         ("withdraw_pct", C.c_float),
         ("withdraw_pct_schedule", C.c_void_p),
+        ("philox_rounds", C.c_int32),
+        ("reserved0", C.c_int32),
     ]
 
 
@@ -108,7 +110,7 @@ class SmmcError(RuntimeError):
 # every symbol include/smmc.h declares (tests check the library exports exactly these)
 C_ABI_SYMBOLS = [
     "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_vector_add", "smmc_vector_add_device",
-    "smmc_debug_draws", "smmc_debug_philox", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
+    "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
 ]
@@ -150,6 +152,10 @@ def load():
     lib.smmc_debug_draws.restype = C.c_int
     lib.smmc_debug_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     lib.smmc_debug_philox.restype = C.c_int
+    lib.smmc_debug_philox_rounds.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    lib.smmc_debug_philox_rounds.restype = C.c_int
+    lib.smmc_debug_set_variant.argtypes = [C.c_char_p, C.c_int32]
+    lib.smmc_debug_set_variant.restype = C.c_int
     lib.smmc_kernel_times.argtypes = [C.c_int32, C.c_void_p, C.c_int32, P(C.c_int32)]
     lib.smmc_kernel_times.restype = C.c_int
     lib.smmc_select_begin.argtypes = [P(SmmcSelectState), C.c_int32, C.c_void_p]

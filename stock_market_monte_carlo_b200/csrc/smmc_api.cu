@@ -48,6 +48,28 @@ smmc_status set_error(smmc_status st, const char *fmt, ...) {
 
 namespace {
 
+// Every entry point may switch the current device; the caller's choice is restored on every return path.
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() {
+    if (cudaGetDevice(&prev) != cudaSuccess) {
+      cudaGetLastError();
+      prev = -1;
+    }
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// kernel-variant selection of the test hook smmc_debug_set_variant (never the environment)
+smmc::Variant g_variant;
+std::mutex g_variant_mu;
+smmc::Variant current_variant() {
+  std::lock_guard<std::mutex> lk(g_variant_mu);
+  return g_variant;
+}
+
 #define CU(call)                                                                                       \
   do {                                                                                                 \
     cudaError_t e__ = (call);                                                                          \
@@ -87,11 +109,28 @@ struct Context {
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
   cudaEvent_t red0 = nullptr, red1 = nullptr;  // around the reduce_mean kernel (smmc_reduce_mean_device)
-  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_lo, sobol_hi, sobol_full, sobol_shift, selhist, flow;
-  std::vector<float> flow_host;  // keep-fractions of the last withdrawal schedule uploaded
-  int sobol_periods = -1;      // (periods, seed) the cached sobol_lo / sobol_hi were built for
-  uint64_t sobol_seed = 0;
+  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_full, sobol_shift, selhist, sincos;
+  bool sincos_ready = false;
   bool sobol_full_ready = false;
+  // Small host-built tables (withdrawal schedule, per-launch Sobol tables) are cached by content in a ring of device
+  // versions: an unchanged table costs no upload at all; a changed one goes into the next slot, ordered behind the last
+  // kernel that read that slot by a stream-side event wait -- the host never blocks (SMMC_FLAG_NO_SYNC stays asynchronous).
+  static constexpr int kVersions = 4;
+  struct Versioned {
+    DevBuf dev[kVersions];
+    void *pinned[kVersions] = {};
+    size_t pinned_cap[kVersions] = {};
+    cudaEvent_t copied[kVersions] = {}, last_read[kVersions] = {};
+    bool read_pending[kVersions] = {};
+    std::vector<unsigned char> content[kVersions];
+    uint64_t tag[kVersions] = {};
+    int next = 0;
+  } flow_v, sobol_v;
+  // cross-stream ordering of the cached workspace: every launch records `last_use` on its stream; a launch on a different
+  // stream waits for it (stream-side) before touching the shared buffers
+  cudaEvent_t last_use = nullptr;
+  cudaStream_t last_stream = nullptr;
+  bool has_last_use = false;
   double *stats_host = nullptr;  // pinned
   size_t stats_host_cap = 0;
   std::mutex mu;
@@ -140,6 +179,8 @@ smmc_status get_context(int device, Context **out) {
     }
     CU(cudaEventCreate(&c.red0));
     CU(cudaEventCreate(&c.red1));
+    CU(cudaEventCreateWithFlags(&c.last_use, cudaEventDisableTiming));
+    c.has_last_use = false;
     c.device = device;
     c.n_sms = sms;
     c.smem_optin = (size_t)optin;
@@ -157,13 +198,15 @@ bool has_withdrawals(const smmc_config *cfg) {
 }
 bool is_sobol(int mode) { return mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN; }
 
-smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
+smmc_status validate(const smmc_config *cfg, const smmc_result *out, bool read_table = true) {
   if (!cfg || !out) return fail(SMMC_ERR_INVALID_ARG, "null config/result");
   if (cfg->abi_version != SMMC_ABI_VERSION)
     return fail(SMMC_ERR_INVALID_ARG, "abi_version %u != %u", cfg->abi_version, SMMC_ABI_VERSION);
   if (cfg->mode < SMMC_MODE_BOOTSTRAP_COMPAT || cfg->mode > SMMC_MODE_SOBOL_GAUSSIAN)
     return fail(SMMC_ERR_INVALID_ARG, "unknown mode %d", cfg->mode);
   if (cfg->n_simulations < 0) return fail(SMMC_ERR_INVALID_ARG, "n_simulations < 0");
+  if (cfg->n_simulations > (1ll << 38))  // per-CTA 32-bit histogram / digit counters: 2^38 / #SMs < 2^32
+    return fail(SMMC_ERR_INVALID_ARG, "n_simulations per call must be <= 2^38; split the run by stream_offset");
   if (cfg->n_periods < 0) return fail(SMMC_ERR_INVALID_ARG, "n_periods < 0");
   if (cfg->stream_offset % SMMC_BLOCK) return fail(SMMC_ERR_INVALID_ARG, "stream_offset must be a multiple of %d", SMMC_BLOCK);
   if (is_bootstrap(cfg->mode)) {
@@ -181,20 +224,23 @@ smmc_status validate(const smmc_config *cfg, const smmc_result *out) {
   if (cfg->hist_bins > 0 && !(cfg->hist_hi > cfg->hist_lo)) return fail(SMMC_ERR_INVALID_ARG, "hist_hi must be > hist_lo");
   if (!std::isfinite(cfg->withdraw_fixed) || !std::isfinite(cfg->withdraw_pct))
     return fail(SMMC_ERR_INVALID_ARG, "withdraw_fixed / withdraw_pct must be finite");
+  if (!std::isfinite(cfg->initial_capital)) return fail(SMMC_ERR_INVALID_ARG, "initial_capital must be finite");
+  if ((cfg->mode == SMMC_MODE_GAUSSIAN || cfg->mode == SMMC_MODE_SOBOL_GAUSSIAN) &&
+      (!std::isfinite(cfg->gauss_mean) || !std::isfinite(cfg->gauss_std)))
+    return fail(SMMC_ERR_INVALID_ARG, "gauss_mean / gauss_std must be finite");
+  if (cfg->philox_rounds != 0 && cfg->philox_rounds != 7 && cfg->philox_rounds != 10)
+    return fail(SMMC_ERR_INVALID_ARG, "philox_rounds must be 0 (= 10), 7 or 10");
+  if (read_table && is_bootstrap(cfg->mode) && !(cfg->flags & SMMC_FLAG_DEVICE_POINTERS)) {
+    // a NaN / inf in the table would poison every path; reject it here (device-pointer tables are the caller's business:
+    // the sorted-table kernel still assigns every rank exactly once)
+    for (int i = 0; i < cfg->n_returns; i++)
+      if (!std::isfinite(cfg->returns[i])) return fail(SMMC_ERR_INVALID_ARG, "returns[%d] is not finite", i);
+  }
   if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !(cfg->flags & SMMC_FLAG_DEVICE_POINTERS))
     return fail(SMMC_ERR_INVALID_ARG, "SMMC_FLAG_NO_SYNC requires SMMC_FLAG_DEVICE_POINTERS");
   if ((cfg->flags & SMMC_FLAG_NO_SYNC) && !out->stats_dev)
     return fail(SMMC_ERR_INVALID_ARG, "SMMC_FLAG_NO_SYNC requires stats_dev");
   return SMMC_OK;
-}
-
-int variant_from_env() {
-  const char *v = getenv("SMMC_ILP");
-  return v ? atoi(v) : 0;
-}
-int warps_from_env() {  // development knob: force the warps per CTA (0 = plan_warps)
-  const char *v = getenv("SMMC_WARPS");
-  return v ? atoi(v) : 0;
 }
 
 smmc::PhiloxKeys make_keys(uint64_t seed) {
@@ -209,6 +255,20 @@ smmc::PhiloxKeys make_keys(uint64_t seed) {
   return k;
 }
 
+// does this configuration take sin/cos from the shared-memory table?  A function of (mode, variant hook) only -- never of
+// what else has to fit into shared memory -- so that every launch of a configuration (statistics, select replays, shards,
+// chunks) computes bit-identical paths.
+bool uses_sincos_table(int mode, const smmc::Variant &v) {
+  if (mode == SMMC_MODE_GAUSSIAN) return (v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::kGaussTblDefault) != 0;
+  if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0;
+  return false;
+}
+int gauss_table_mask(int mode, const smmc::Variant &v) {
+  if (mode == SMMC_MODE_GAUSSIAN) return v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::kGaussTblDefault;
+  if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0 ? 0xF : 0;
+  return 0;
+}
+
 // the RNG-stream / arithmetic constants of a config (shared by the introspection and trajectory kernels; enqueue()
 // sets the same fields for the simulation kernel)
 void fill_stream_params(const smmc_config *cfg, smmc::KParams *p) {
@@ -217,6 +277,8 @@ void fill_stream_params(const smmc_config *cfg, smmc::KParams *p) {
   p->n_returns = cfg->n_returns;
   p->compat_seed = (uint32_t)cfg->seed;
   p->keys = make_keys(cfg->seed);
+  p->philox_rounds = cfg->philox_rounds == 7 ? 7 : 10;
+  p->gauss_tbl_mask = gauss_table_mask(cfg->mode, current_variant());
   const float mu = cfg->gauss_mean * 0.01f, sigma = cfg->gauss_std * 0.01f;
   p->gc.a = 1.0f + mu;
   p->gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
@@ -260,32 +322,112 @@ uint32_t sobol_shift_host(int m, uint64_t seed) {
   return w[m & 3];
 }
 
-// (Re)build the per-launch Sobol tables for (n_periods, seed) on `st`; cached per context.
-smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream_t st, smmc::KParams *p) {
+// ---- content-cached, versioned uploads (Context::Versioned) ---------------------------------------------------------
+// Returns the slot that holds (tag, host[0..bytes)) on the device, uploading on `st` if no slot does.  host == nullptr
+// only looks up by tag (-1 = not cached).
+int versioned_find(const Context::Versioned &v, uint64_t tag, const void *host, size_t bytes) {
+  for (int i = 0; i < Context::kVersions; i++) {
+    if (v.content[i].empty() || v.tag[i] != tag) continue;
+    if (!host) return i;
+    if (v.content[i].size() == bytes && memcmp(v.content[i].data(), host, bytes) == 0) return i;
+  }
+  return -1;
+}
+
+smmc_status versioned_upload(Context::Versioned &v, uint64_t tag, const void *host, size_t bytes, cudaStream_t st, int *slot_out) {
+  int slot = versioned_find(v, tag, host, bytes);
+  if (slot < 0) {
+    slot = v.next;
+    v.next = (v.next + 1) % Context::kVersions;
+    if (!v.copied[slot]) {
+      CU(cudaEventCreateWithFlags(&v.copied[slot], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&v.last_read[slot], cudaEventDisableTiming));
+    } else {
+      // the staging copy of this slot was enqueued kVersions uploads ago: normally long complete (host-side wait only if not)
+      CU(cudaEventSynchronize(v.copied[slot]));
+    }
+    if (v.read_pending[slot]) CU(cudaStreamWaitEvent(st, v.last_read[slot], 0));  // kernels still reading the old version
+    if (v.pinned_cap[slot] < bytes) {
+      if (v.pinned[slot]) cudaFreeHost(v.pinned[slot]);
+      v.pinned[slot] = nullptr;
+      v.pinned_cap[slot] = 0;
+      CU(cudaMallocHost(&v.pinned[slot], bytes));
+      v.pinned_cap[slot] = bytes;
+    }
+    CU(v.dev[slot].reserve(bytes));
+    memcpy(v.pinned[slot], host, bytes);
+    CU(cudaMemcpyAsync(v.dev[slot].p, v.pinned[slot], bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(v.copied[slot], st));
+    v.content[slot].assign((const unsigned char *)host, (const unsigned char *)host + bytes);
+    v.tag[slot] = tag;
+    v.read_pending[slot] = false;
+  }
+  *slot_out = slot;
+  return SMMC_OK;
+}
+
+// call after the kernel that reads slot `slot` has been launched on `st`
+smmc_status versioned_mark_read(Context::Versioned &v, int slot, cudaStream_t st) {
+  if (slot < 0) return SMMC_OK;
+  CU(cudaEventRecord(v.last_read[slot], st));
+  v.read_pending[slot] = true;
+  return SMMC_OK;
+}
+
+void versioned_release(Context::Versioned &v) {
+  for (int i = 0; i < Context::kVersions; i++) {
+    v.dev[i].release();
+    if (v.pinned[i]) cudaFreeHost(v.pinned[i]);
+    v.pinned[i] = nullptr;
+    v.pinned_cap[i] = 0;
+    if (v.copied[i]) cudaEventDestroy(v.copied[i]);
+    if (v.last_read[i]) cudaEventDestroy(v.last_read[i]);
+    v.copied[i] = v.last_read[i] = nullptr;
+    v.read_pending[i] = false;
+    v.content[i].clear();
+    v.tag[i] = 0;
+  }
+  v.next = 0;
+}
+
+// The per-launch Sobol tables for (n_periods, seed): [P_pad][8] low direction numbers, then [98][P_pad] (KParams::sobol_hi).  Cached by (n_periods, seed); nothing synchronises.
+smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream_t st, smmc::KParams *p, int *slot_out) {
   const int ppad = (n_periods + 31) & ~31;
   const uint32_t *V = smmc::sobol_table();
+  *slot_out = -1;
   if (n_periods > smmc::sobol_table_dims()) return fail(SMMC_ERR_INVALID_ARG, "Sobol modes support at most %d periods", smmc::sobol_table_dims());
-  if (ppad > 0 && (ctx->sobol_periods != n_periods || ctx->sobol_seed != seed)) {
-    std::vector<uint32_t> lo((size_t)ppad * 8, 0u), hi((size_t)26 * ppad, 0u);
-    for (int m = 0; m < n_periods; m++) {
-      for (int k = 0; k < 8; k++) lo[(size_t)m * 8 + k] = V[(size_t)m * 32 + k];
-      for (int k = 0; k < 24; k++) hi[(size_t)k * ppad + m] = V[(size_t)m * 32 + 8 + k];
-      hi[(size_t)24 * ppad + m] = V[(size_t)m * 32 + 7];
-      hi[(size_t)25 * ppad + m] = sobol_shift_host(m, seed);
-    }
-    CU(ctx->sobol_lo.reserve(lo.size() * 4));
-    CU(ctx->sobol_hi.reserve(hi.size() * 4));
-    CU(cudaStreamSynchronize(st));  // a previous launch on this stream may still read the cached tables
-    CU(cudaMemcpyAsync(ctx->sobol_lo.p, lo.data(), lo.size() * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(ctx->sobol_hi.p, hi.data(), hi.size() * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaStreamSynchronize(st));  // lo/hi are stack-lifetime host vectors
-    ctx->sobol_periods = n_periods;
-    ctx->sobol_seed = seed;
-  }
-  p->sobol_lo = (const uint32_t *)ctx->sobol_lo.p;
-  p->sobol_hi = (const uint32_t *)ctx->sobol_hi.p;
   p->sobol_ppad = ppad;
   p->sobol_lo_bytes = (uint32_t)ppad * 32u;
+  if (ppad == 0) return SMMC_OK;
+  const uint64_t tag = (seed * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)n_periods << 1) ^ 1ull;
+  int slot = versioned_find(ctx->sobol_v, tag, nullptr, 0);
+  if (slot < 0) {
+    std::vector<uint32_t> buf((size_t)ppad * 8 + (size_t)smmc::kSobolHiRows * ppad + 2, 0u);
+    uint32_t *lo = buf.data(), *hi = buf.data() + (size_t)ppad * 8;
+    for (int m = 0; m < n_periods; m++) {
+      const uint32_t *Vm = V + (size_t)m * 32;
+      for (int k = 0; k < 8; k++) lo[(size_t)m * 8 + k] = Vm[k];
+      const uint32_t sh = sobol_shift_host(m, seed);
+      hi[(size_t)0 * ppad + m] = sh;
+      hi[(size_t)1 * ppad + m] = sh ^ Vm[7];
+      for (int g = 0; g < 6; g++)
+        for (int c = 0; c < 16; c++) {
+          uint32_t x = 0;
+          for (int k = 0; k < 4; k++)
+            if ((c >> k) & 1) x ^= Vm[8 + 4 * g + k];
+          hi[(size_t)(2 + 16 * g + c) * ppad + m] = x;
+        }
+    }
+    // the exact (n_periods, seed) rides behind the tables so that a tag collision cannot alias two configurations
+    buf[buf.size() - 2] = (uint32_t)n_periods;
+    buf[buf.size() - 1] = (uint32_t)(seed ^ (seed >> 32));
+    smmc_status us = versioned_upload(ctx->sobol_v, tag, buf.data(), buf.size() * 4, st, &slot);
+    if (us != SMMC_OK) return us;
+  }
+  const uint32_t *dev = (const uint32_t *)ctx->sobol_v.dev[slot].p;
+  p->sobol_lo = dev;
+  p->sobol_hi = dev + (size_t)ppad * 8;
+  *slot_out = slot;
   return SMMC_OK;
 }
 
@@ -311,24 +453,25 @@ smmc_status prepare_sobol_full(Context *ctx, int n_periods, uint64_t seed, const
 }
 
 // Per-period keep-fractions q[m] = 1 - pct_m/100 on the device (withdrawal variant of the kernels); null when the config
-// asks for no withdrawals.
-smmc_status prepare_flow(Context *ctx, const smmc_config *cfg, cudaStream_t st, smmc::KParams *p) {
+// asks for no withdrawals.  Cached by content; nothing synchronises.
+smmc_status prepare_flow(Context *ctx, const smmc_config *cfg, cudaStream_t st, smmc::KParams *p, int *slot_out) {
   p->flow_q = nullptr;
   p->flow_w = 0.0f;
+  *slot_out = -1;
   if (!has_withdrawals(cfg)) return SMMC_OK;
   const int P = cfg->n_periods;
-  ctx->flow_host.resize((size_t)(P > 0 ? P : 1));
+  std::vector<float> q((size_t)(P > 0 ? P : 1), 1.0f);
   for (int m = 0; m < P; m++) {
     const float pct = cfg->withdraw_pct_schedule ? cfg->withdraw_pct_schedule[m] : cfg->withdraw_pct;
     if (!std::isfinite(pct)) return fail(SMMC_ERR_INVALID_ARG, "withdraw_pct_schedule[%d] is not finite", m);
-    ctx->flow_host[(size_t)m] = 1.0f - pct * 0.01f;
+    q[(size_t)m] = 1.0f - pct * 0.01f;
   }
-  if (P == 0) ctx->flow_host[0] = 1.0f;
-  CU(ctx->flow.reserve(ctx->flow_host.size() * 4));
-  CU(cudaStreamSynchronize(st));  // a previous launch on this stream may still read the cached schedule
-  CU(cudaMemcpyAsync(ctx->flow.p, ctx->flow_host.data(), ctx->flow_host.size() * 4, cudaMemcpyHostToDevice, st));
-  p->flow_q = (const float *)ctx->flow.p;
+  int slot = -1;
+  smmc_status us = versioned_upload(ctx->flow_v, 1, q.data(), q.size() * 4, st, &slot);
+  if (us != SMMC_OK) return us;
+  p->flow_q = (const float *)ctx->flow_v.dev[slot].p;
   p->flow_w = cfg->withdraw_fixed;
+  *slot_out = slot;
   return SMMC_OK;
 }
 
@@ -340,6 +483,12 @@ struct SelectPass {
   int prefix_shift = 32;
   uint32_t prefix[SMMC_SELECT_MAX_TARGETS] = {};
   unsigned long long *hist_dev = nullptr;  // caller's device buffer (DEVICE_POINTERS) or null = library workspace
+  // candidate collection riding along with this replay (second pass): see KParams
+  int cand_groups = 0;
+  uint32_t cand_prefix[SMMC_SELECT_MAX_TARGETS] = {};
+  uint32_t *cand_keys = nullptr;
+  unsigned long long *cand_cursor = nullptr;
+  unsigned long long cand_capacity = 0;
 };
 
 // digit width of the pass that starts with `bits_done` key bits known: 11, 11, 10
@@ -375,44 +524,70 @@ struct Pending {
   int ev_slot = 0;
 };
 
+// Cross-stream ordering of the per-device cached workspace (ctx->work / tbl / returns / sorted / stats / scratch ...):
+// before a call touches those buffers on `st`, it waits (stream-side, the host does not block) for the last call that used
+// them on a different stream; after its last enqueue it records the event again.
+smmc_status order_after_last_use(Context *ctx, cudaStream_t st) {
+  if (ctx->has_last_use && ctx->last_stream != st) CU(cudaStreamWaitEvent(st, ctx->last_use, 0));
+  return SMMC_OK;
+}
+smmc_status mark_last_use(Context *ctx, cudaStream_t st) {
+  CU(cudaEventRecord(ctx->last_use, st));
+  ctx->last_stream = st;
+  ctx->has_last_use = true;
+  return SMMC_OK;
+}
+
+// the (cos, sin) table of the Gaussian modes, built once per device
+smmc_status prepare_sincos(Context *ctx, cudaStream_t st) {
+  if (ctx->sincos_ready) return SMMC_OK;
+  CU(ctx->sincos.reserve(smmc::kSinCosBytes));
+  smmc::launch_sincos_table((float *)ctx->sincos.p, st);
+  CU(cudaGetLastError());
+  ctx->sincos_ready = true;
+  return SMMC_OK;
+}
+
+// where the launch's outputs go (device pointers); null = library workspace / not requested
+struct DeviceOutputs {
+  float *finals = nullptr, *bmeans = nullptr, *bvars = nullptr;
+  double *stats = nullptr;
+  bool want_finals = false, want_bmeans = false, want_bvars = false;  // host-pointer runs: allocate in the context cache
+};
+
 // Enqueue one shard [cfg->stream_offset, +N) on cfg->device.  Caller holds ctx->mu.
 smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx, Pending *pd,
-                    const SelectPass *sel = nullptr) {
+                    const SelectPass *sel = nullptr, const DeviceOutputs *dout = nullptr, cudaStream_t stream_override = nullptr) {
   CU(cudaSetDevice(ctx->device));
   const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
-  cudaStream_t st = devp ? (cudaStream_t)cfg->stream : ctx->stream;
+  cudaStream_t st = stream_override ? stream_override : (devp ? (cudaStream_t)cfg->stream : ctx->stream);
   const int64_t N = cfg->n_simulations;
   const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
   const int bins = cfg->hist_bins;
   const int slen = smmc_stats_len(bins);
-  const int variant = variant_from_env();
+  const smmc::Variant variant = current_variant();
+  const bool sincos = uses_sincos_table(cfg->mode, variant);
 
   smmc::LaunchInfo li;
-  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, has_withdrawals(cfg), N, ctx->n_sms,
-                         ctx->smem_optin, warps_from_env(), &li))
+  if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, has_withdrawals(cfg), sincos, N,
+                         ctx->n_sms, ctx->smem_optin, variant.warps, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries (+ histograms / schedules) does not fit in %zu bytes of shared memory",
                 cfg->n_returns, ctx->smem_optin);
 
+  {
+    smmc_status os = order_after_last_use(ctx, st);
+    if (os != SMMC_OK) return os;
+  }
+
   smmc::KParams p;
   memset(&p, 0, sizeof p);
+  fill_stream_params(cfg, &p);
   p.n_paths = N;
-  p.path0 = cfg->stream_offset;
-  p.n_periods = cfg->n_periods;
-  p.n_returns = cfg->n_returns;
-  p.compat_seed = (uint32_t)cfg->seed;
-  p.keys = make_keys(cfg->seed);
-  {
-    const float mu = cfg->gauss_mean * 0.01f, sigma = cfg->gauss_std * 0.01f;
-    p.gc.a = 1.0f + mu;
-    p.gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
-    p.sigma_sqrt2 = (float)(1.41421356237309504880 * (double)sigma);
-  }
-  p.one = 0x3F800000u;
-  p.v0 = cfg->initial_capital;
   p.target = cfg->target;
   p.hist_lo = cfg->hist_lo;
   p.hist_inv_w = bins > 0 ? (float)((double)bins / ((double)cfg->hist_hi - (double)cfg->hist_lo)) : 0.0f;
   p.hist_bins = bins;
+  p.rep4 = 4u;
   pd->launches = 0;
 
   // ---- table: upload (host pointers) and expand to the scaled, bank-private replicated layout
@@ -439,15 +614,15 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.tbl_rep = (const float *)ctx->tbl.p;
     p.tbl_bytes = tbl_bytes;
     p.rep4 = (uint32_t)li.rep * 4u;
-    p.idx_scale = (float)n * 2.3283064365386963e-10f;  // exact: n < 2^24
-    p.bc.c21 = (float)(4 * n);                          // exact: n < 2^21 (validated)
-    p.bc.k21 = (float)(8388608 - 4 * n);
-    p.bc.c22 = (float)(2 * n);
-    p.bc.k22 = (float)(8388608 - 2 * n);
     p.bc.row_shift = 2;
     while ((1u << p.bc.row_shift) < (uint32_t)li.rep * 4u) p.bc.row_shift++;
-  } else {
-    p.rep4 = 4u;
+  } else if (sincos) {
+    const bool fresh = !ctx->sincos_ready;
+    smmc_status ss = prepare_sincos(ctx, st);
+    if (ss != SMMC_OK) return ss;
+    if (fresh) pd->launches++;
+    p.tbl_rep = (const float *)ctx->sincos.p;
+    p.tbl_bytes = smmc::kSinCosBytes;
   }
 
   // ---- workspace: [cta_partials grid*4 doubles][hist_g (bins+2) u64][ticket u32 (+pad)]
@@ -460,18 +635,17 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   p.ticket = (unsigned int *)(w + part_bytes + hist_bytes);
   CU(cudaMemsetAsync(w + part_bytes, 0, hist_bytes + 16, st));
 
-  if (devp && out->stats_dev) {
-    p.stats = out->stats_dev;
-  } else {
-    CU(ctx->stats.reserve((size_t)slen * sizeof(double)));
-    p.stats = (double *)ctx->stats.p;
-  }
-
   // ---- outputs
-  if (devp) {
+  if (dout) {
+    p.finals = dout->finals;
+    p.bmeans = dout->bmeans;
+    p.bvars = dout->bvars;
+    p.stats = dout->stats;
+  } else if (devp) {
     p.finals = out->finals;
     p.bmeans = out->block_means;
     p.bvars = out->block_vars;
+    p.stats = out->stats_dev;
   } else {
     if (out->finals && N > 0) {
       CU(ctx->finals.reserve((size_t)N * 4));
@@ -486,14 +660,18 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
       p.bvars = (float *)ctx->bvars.p;
     }
   }
-
-  if (is_sobol(cfg->mode)) {
-    smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p);
-    if (sst != SMMC_OK) return sst;
+  if (!p.stats) {
+    CU(ctx->stats.reserve((size_t)slen * sizeof(double)));
+    p.stats = (double *)ctx->stats.p;
   }
 
+  int sobol_slot = -1, flow_slot = -1;
+  if (is_sobol(cfg->mode)) {
+    smmc_status sst = prepare_sobol(ctx, cfg->n_periods, cfg->seed, st, &p, &sobol_slot);
+    if (sst != SMMC_OK) return sst;
+  }
   {
-    smmc_status fst = prepare_flow(ctx, cfg, st, &p);
+    smmc_status fst = prepare_flow(ctx, cfg, st, &p, &flow_slot);
     if (fst != SMMC_OK) return fst;
   }
 
@@ -513,6 +691,12 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.sel_prefix_shift = sel->prefix_shift;
     for (int t = 0; t < SMMC_SELECT_MAX_TARGETS; t++) p.sel_prefix[t] = sel->prefix[t];
     p.sel_hist_g = hd;
+    p.cand_groups = sel->cand_groups;
+    for (int t = 0; t < SMMC_SELECT_MAX_TARGETS; t++) p.cand_prefix[t] = sel->cand_prefix[t];
+    p.cand_keys = sel->cand_keys;
+    p.cand_cursor = sel->cand_cursor;
+    p.cand_capacity = sel->cand_capacity;
+    if (sel->cand_groups > 0) CU(cudaMemsetAsync(sel->cand_cursor, 0, sizeof(unsigned long long), st));
     pd->sel_dev = hd;
     pd->sel_words = sel->targets * SMMC_SELECT_BINS;
   }
@@ -524,6 +708,18 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   ctx->ev_head++;
   pd->ev_slot = slot;
   pd->launches++;
+  if (sobol_slot >= 0) {
+    smmc_status ms = versioned_mark_read(ctx->sobol_v, sobol_slot, st);
+    if (ms != SMMC_OK) return ms;
+  }
+  if (flow_slot >= 0) {
+    smmc_status ms = versioned_mark_read(ctx->flow_v, flow_slot, st);
+    if (ms != SMMC_OK) return ms;
+  }
+  {
+    smmc_status ms = mark_last_use(ctx, st);
+    if (ms != SMMC_OK) return ms;
+  }
 
   pd->ctx = ctx;
   pd->stream = st;
@@ -706,7 +902,8 @@ smmc_status reduce_sum_device(Context *ctx, const float *v_dev, int64_t n, cudaS
   CU(cudaMemsetAsync(w + part, 0, 32, st));
   cudaEvent_t e0 = ctx->red0, e1 = ctx->red1;
   if (kernel_ms) CU(cudaEventRecord(e0, st));
-  CU(smmc::launch_reduce_sum(v_dev, n, (double *)w, (unsigned int *)(w + part + 16), (double *)(w + part), ctx->n_sms, st));
+  CU(smmc::launch_reduce_sum(v_dev, n, (double *)w, (unsigned int *)(w + part + 16), (double *)(w + part), ctx->n_sms,
+                             current_variant().reduce, st));
   if (kernel_ms) CU(cudaEventRecord(e1, st));
   CU(cudaMemcpyAsync(sum, w + part, sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -1022,9 +1219,17 @@ smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *va
   const size_t vbytes = (size_t)n_paths * (size_t)(P + 1) * 4, rbytes = returns_pct ? (size_t)n_paths * (size_t)P * 4 : 0;
   CU(ctx->scratch.reserve(vbytes + rbytes + 16));
   float *vd = (float *)ctx->scratch.p, *rd = rbytes ? vd + (size_t)n_paths * (P + 1) : nullptr;
-  st = prepare_flow(ctx, cfg, s, &p);
+  int flow_slot = -1;
+  st = prepare_flow(ctx, cfg, s, &p, &flow_slot);
   if (st != SMMC_OK) return st;
+  if (p.gauss_tbl_mask) {  // the Gaussian modes' sin/cos table (read from global memory here)
+    st = prepare_sincos(ctx, s);
+    if (st != SMMC_OK) return st;
+    p.tbl_rep = (const float *)ctx->sincos.p;
+  }
   CU(smmc::launch_trajectories(cfg->mode, p, n_paths, tbl, raw, full_dev, shift_dev, vd, rd, s));
+  st = versioned_mark_read(ctx->flow_v, flow_slot, s);
+  if (st != SMMC_OK) return st;
   CU(cudaMemcpyAsync(values, vd, vbytes, cudaMemcpyDeviceToHost, s));
   if (rbytes) CU(cudaMemcpyAsync(returns_pct, rd, rbytes, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamSynchronize(s));
@@ -1042,13 +1247,14 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
     c2 = *cfg;
     if (!c2.returns && c2.n_returns > 0) c2.returns = (const float *)(uintptr_t)16;  // planning never reads the table
   }
-  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
+  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy, false);
   if (st != SMMC_OK) return st;
   if (!plan || n_sms < 1 || select_targets < 0 || select_targets > SMMC_SELECT_MAX_TARGETS)
     return fail(SMMC_ERR_INVALID_ARG, "plan_launch: bad arguments");
   smmc::LaunchInfo li;
+  const smmc::Variant variant = current_variant();
   if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, has_withdrawals(cfg),
-                         cfg->n_simulations, n_sms, (size_t)smem_optin, warps_from_env(), &li))
+                         uses_sincos_table(cfg->mode, variant), cfg->n_simulations, n_sms, (size_t)smem_optin, variant.warps, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %llu bytes of shared memory", cfg->n_returns,
                 (unsigned long long)smem_optin);
   plan->grid = li.grid;
@@ -1062,7 +1268,13 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
 smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
-  smmc_status st = validate(cfg, &dummy);
+  smmc_config c2;
+  if (cfg) {
+    c2 = *cfg;
+    c2.n_simulations = n_paths;  // range checks (32-bit path ids, Sobol point indices) apply to the paths asked for
+    c2.hist_bins = 0;
+  }
+  smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
   if (st != SMMC_OK) return st;
   if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "debug_draws takes host pointers");
   if (n_paths < 0 || !outbuf) return fail(SMMC_ERR_INVALID_ARG, "debug_draws: bad arguments");
@@ -1089,7 +1301,13 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
 }
 
 smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t n, int32_t device, uint32_t *outbuf) {
+  return smmc_debug_philox_rounds(ctr, key, 10, n, device, outbuf);
+}
+
+smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, int32_t rounds, int32_t n, int32_t device,
+                                     uint32_t *outbuf) {
   if (!ctr || !key || !outbuf || n < 0) return fail(SMMC_ERR_INVALID_ARG, "debug_philox: bad arguments");
+  if (rounds != 7 && rounds != 10) return fail(SMMC_ERR_INVALID_ARG, "debug_philox: rounds must be 7 or 10");
   Context *ctx = nullptr;
   smmc_status st = get_context(device, &ctx);
   if (st != SMMC_OK) return st;
@@ -1099,9 +1317,27 @@ smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t 
   CU(ctx->scratch.reserve((size_t)n * 32));
   uint32_t *dc = (uint32_t *)ctx->scratch.p, *dout = dc + (size_t)n * 4;
   CU(cudaMemcpyAsync(dc, ctr, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
-  CU(smmc::launch_debug_philox(dc, make_keys((uint64_t)key[0] | ((uint64_t)key[1] << 32)), n, dout, ctx->stream));
+  CU(smmc::launch_debug_philox(dc, make_keys((uint64_t)key[0] | ((uint64_t)key[1] << 32)), rounds, n, dout, ctx->stream));
   CU(cudaMemcpyAsync(outbuf, dout, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  return SMMC_OK;
+}
+
+smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
+  std::lock_guard<std::mutex> lk(g_variant_mu);
+  if (!key) {
+    g_variant = smmc::Variant();
+    return SMMC_OK;
+  }
+  const smmc::Variant def;
+  if (!strcmp(key, "ilp")) g_variant.ilp = value > 0 ? value : def.ilp;
+  else if (!strcmp(key, "warps")) g_variant.warps = (value >= 1 && value <= smmc::kWarps) ? value : def.warps;
+  else if (!strcmp(key, "reduce")) g_variant.reduce = (value == 1 || value == 2) ? value : def.reduce;
+  else if (!strcmp(key, "gauss_tbl")) g_variant.gauss_tbl = (value >= 0 && value <= 15) ? value : def.gauss_tbl;
+  else if (!strcmp(key, "sobol_tbl")) g_variant.sobol_tbl = (value == 0 || value == 1) ? value : def.sobol_tbl;
+  else if (!strcmp(key, "sobol_unroll")) g_variant.sobol_unroll = value > 0 ? value : def.sobol_unroll;
+  else if (!strcmp(key, "finals_chunks")) g_variant.finals_chunks = value > 0 ? value : def.finals_chunks;
+  else return fail(SMMC_ERR_INVALID_ARG, "debug_set_variant: unknown key '%s'", key);
   return SMMC_OK;
 }
 
@@ -1135,12 +1371,16 @@ void smmc_shutdown(void) {
     cudaSetDevice(d);
     c.returns.release();
     c.sorted.release();
-    c.sobol_lo.release();
-    c.sobol_hi.release();
     c.sobol_full.release();
     c.sobol_shift.release();
-    c.sobol_periods = -1;
     c.sobol_full_ready = false;
+    c.sincos.release();
+    c.sincos_ready = false;
+    versioned_release(c.flow_v);
+    versioned_release(c.sobol_v);
+    if (c.last_use) cudaEventDestroy(c.last_use);
+    c.last_use = nullptr;
+    c.has_last_use = false;
     c.tbl.release();
     c.work.release();
     c.stats.release();
@@ -1149,7 +1389,6 @@ void smmc_shutdown(void) {
     c.bvars.release();
     c.scratch.release();
     c.selhist.release();
-    c.flow.release();
     if (c.stats_host) cudaFreeHost(c.stats_host);
     c.stats_host = nullptr;
     c.stats_host_cap = 0;

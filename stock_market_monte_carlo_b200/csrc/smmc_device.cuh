@@ -53,14 +53,23 @@ __device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_
   c2 = n2;
 }
 
-__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                              const PhiloxKeys &k, uint32_t (&out)[4]) {
+// ROUNDS = 10 is Philox4x32-10, the default of every native mode; ROUNDS = 7 is Philox4x32-7, the smallest round count the
+// SC'11 paper reports as Crush-resistant (its table 2) and for which Random123 ships known-answer vectors -- an explicit
+// opt-in of the stream contract (smmc_config.philox_rounds), never chosen silently.
+template <int ROUNDS>
+__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const PhiloxKeys &k,
+                                           uint32_t (&out)[4]) {
+  static_assert(ROUNDS >= 1 && ROUNDS <= 10, "PhiloxKeys holds ten round keys");
 #pragma unroll
-  for (int r = 0; r < 10; r++) philox_round(c0, c1, c2, c3, k.k0[r], k.k1[r]);
+  for (int r = 0; r < ROUNDS; r++) philox_round(c0, c1, c2, c3, k.k0[r], k.k1[r]);
   out[0] = c0;
   out[1] = c1;
   out[2] = c2;
   out[3] = c3;
+}
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              const PhiloxKeys &k, uint32_t (&out)[4]) {
+  philox4x32<10>(c0, c1, c2, c3, k, out);
 }
 
 // Stream contract of the native modes: counter = (q, path_lo, tag, path_hi), key = seed.
@@ -74,9 +83,16 @@ constexpr uint32_t kTagBootstrap = 0x424F4F54u;   // "BOOT"
 constexpr uint32_t kTagGaussian = 0x47415553u;    // "GAUS"
 constexpr uint32_t kTagSobolShift = 0x534F424Cu;  // "SOBL"
 
+template <int ROUNDS = 10>
 __device__ __forceinline__ void stream_words(uint32_t path_lo, uint32_t path_hi, uint32_t q, uint32_t tag,
                                              const PhiloxKeys &k, uint32_t (&w)[4]) {
-  philox4x32_10(q, path_lo, tag, path_hi, k, w);
+  philox4x32<ROUNDS>(q, path_lo, tag, path_hi, k, w);
+}
+// run-time round count (trajectory / introspection kernels: one thread per path, not performance-critical)
+__device__ __forceinline__ void stream_words_rt(int rounds, uint32_t path_lo, uint32_t path_hi, uint32_t q, uint32_t tag,
+                                                const PhiloxKeys &k, uint32_t (&w)[4]) {
+  if (rounds == 7) philox4x32<7>(q, path_lo, tag, path_hi, k, w);
+  else philox4x32<10>(q, path_lo, tag, path_hi, k, w);
 }
 
 // ---- MUFU wrappers ------------------------------------------------------------------------------------------
@@ -173,6 +189,46 @@ __device__ __forceinline__ void gauss_pair(uint32_t w, uint32_t one, const Gauss
   g1 = fmaf(rs, sin_approx(v), gc.a);
 }
 
+// ---- sin / cos of the Box-Muller angle from a shared-memory table (no MUFU) -------------------------------------------
+// The angle is 2 pi h / 2^32 for a 32-bit word h (mod 2 pi the same angle as the signed form above).  h = cell : low with a
+// 13-bit cell index and a 19-bit remainder:  theta = theta_c + beta,  theta_c = 2 pi (cell + 1/2) / 2^13 (cell centre),
+// beta = 2 pi (low - 2^18) / 2^32 in [-pi/2^13, pi/2^13).  The table holds (cos theta_c, sin theta_c) rounded from double;
+// one first-order rotation  cos = c - s beta,  sin = s + c beta  leaves a truncation error beta^2/2 <= 7.4e-8 (2.5e-8 on
+// average): the size of one float rounding near 1 and ~7 times smaller than the absolute error of MUFU.SIN/COS (2^-20.9),
+// so the two evaluations of the same contract differ by less than either differs from libm (the oracle).  beta comes from
+// the mantissa trick: m = 1 + low 2^-23 (one LOP3), beta = m kap + kap0 with kap = 2 pi 2^23 / 2^32, kap0 = -(1 + 2^-5) kap.
+// Cost: SHF + LOP3 (address) + LDS.64 + LOP3 + 3 FFMA instead of I2FP + FMUL + FMUL.RZ + 2 MUFU: the XU pipe (4 lanes per
+// clock per sub-partition, the binding pipe of the Gaussian modes) is relieved of half its work.  64 KB of shared memory.
+constexpr int kSinCosCells = 8192;
+constexpr uint32_t kSinCosBytes = kSinCosCells * 8u;
+constexpr float kSinCosKap = (float)(3.14159265358979323846 / 256.0);                       // 2 pi 2^23 / 2^32
+constexpr float kSinCosKap0 = (float)(-(1.0 + 1.0 / 32.0) * 3.14159265358979323846 / 256.0);  // -(1 + 2^-5) kap
+
+// Table layout: cell c lives at slot c ^ (c >> 9), i.e. the top four cell bits are XOR-ed into the bank-selecting bits.
+// In SOBOL_GAUSSIAN the 32 lanes of a warp hold points that differ only in the TOP five bits of the word (the direction
+// numbers of index bits 0..4), so a linear layout would put all 32 lanes in ONE bank (measured: 3.6x slower than MUFU);
+// with the swizzle the 16 lanes of each LDS.64 half-warp phase hit 16 different 8-byte bank pairs: conflict-free.
+// GAUSSIAN's hashed words are random either way.  Byte offset = ((h >> 16) ^ (h >> 25)) & 0xFFF8: two SHF + one LOP3.
+__host__ __device__ __forceinline__ uint32_t sincos_slot(uint32_t cell) { return cell ^ (cell >> 9); }
+
+__device__ __forceinline__ void sincos_tbl(uint32_t h, uint32_t one, const char *sc_tbl, float &cv, float &sv) {
+  const float2 cs = *reinterpret_cast<const float2 *>(sc_tbl + (((h >> 16) ^ (h >> 25)) & 0xFFF8u));
+  const float beta = fmaf(__uint_as_float((h & 0x7FFFFu) | one), kSinCosKap, kSinCosKap0);
+  cv = fmaf(-cs.y, beta, cs.x);
+  sv = fmaf(cs.x, beta, cs.y);
+}
+
+__device__ __forceinline__ void gauss_pair_tbl(uint32_t w, uint32_t one, const GaussConsts gc, const char *sc_tbl, float &g0,
+                                               float &g1) {
+  const float mr = __uint_as_float((w & 0xFFFFFu) | one);
+  const float u = fmaf(mr, 8.0f, -7.99999952316284179688f);
+  float cv, sv;
+  sincos_tbl(w * kAngleHash, one, sc_tbl, cv, sv);
+  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  g0 = fmaf(rs, cv, gc.a);
+  g1 = fmaf(rs, sv, gc.a);
+}
+
 // ---- SOBOL_GAUSSIAN: Box-Muller on dimension pairs --------------------------------------------------------------
 // Months 2k and 2k+1 (Sobol dimensions 2k, 2k+1) form one Box-Muller pair: the (digitally shifted) word of the even
 // dimension is the radius uniform, the word of the odd dimension the angle:
@@ -190,6 +246,16 @@ __device__ __forceinline__ void sobol_gauss_pair(uint32_t xr, uint32_t xa, const
   const float rs = sqrt_approx(lg2_approx(u) * gc.k);
   g0 = fmaf(rs, cos_approx(v), gc.a);
   g1 = fmaf(rs, sin_approx(v), gc.a);
+}
+
+__device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, uint32_t one, const GaussConsts gc,
+                                                     const char *sc_tbl, float &g0, float &g1) {
+  const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
+  float cv, sv;
+  sincos_tbl(xa, one, sc_tbl, cv, sv);
+  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  g0 = fmaf(rs, cv, gc.a);
+  g1 = fmaf(rs, sv, gc.a);
 }
 
 // ---- inverse normal CDF (SOBOL_GAUSSIAN, unpaired last month of an odd horizon) -----------------------------------

@@ -3,7 +3,6 @@
 // smmc_mc_kernel.cuh, instantiated per RNG mode in smmc_mc_{compat,bootstrap,gaussian,sobol}.cu.
 //
 // Replaces compute_sum_kernel / impl_vector_add_gpu (reference src/simulations.cu:249-267, src/gpu.cu:8-14).
-#include <cstdlib>
 #include <cstring>
 
 #include "smmc_kernels.cuh"
@@ -13,10 +12,10 @@
 namespace smmc {
 
 // per-mode launchers (smmc_mc_*.cu)
-cudaError_t launch_mc_compat(const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
-cudaError_t launch_mc_bootstrap(const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
-cudaError_t launch_mc_gaussian(const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
-cudaError_t launch_mc_sobol(int mode, const KParams &p, const LaunchInfo &li, cudaStream_t s);
+cudaError_t launch_mc_compat(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
+cudaError_t launch_mc_bootstrap(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
+cudaError_t launch_mc_gaussian(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
+cudaError_t launch_mc_sobol(int mode, const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
 
 namespace {
 
@@ -29,17 +28,31 @@ __global__ void prep_table_kernel(const float *__restrict__ src, int n, int rep,
   }
 }
 
-// stable rank sort, O(n^2): n is a table length (~1e3), once per call
+// stable rank sort, O(n^2): n is a table length (~1e3), once per call.  Ranks come from the order-preserving integer keys
+// (ordered_key: a total order, -0 < +0, NaNs beyond +-inf), so every rank 0..n-1 is assigned exactly once even for a table
+// with NaNs (device-pointer callers; the host-pointer path rejects non-finite returns in validate()).
 __global__ void sort_table_kernel(const float *__restrict__ src, int n, float *__restrict__ dst) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float v = src[i];
+    const uint32_t kv = ordered_key(v);
     int rank = 0;
     for (int j = 0; j < n; j++) {
-      const float u = __ldg(src + j);
-      rank += (u < v || (u == v && j < i)) ? 1 : 0;
+      const uint32_t ku = ordered_key(__ldg(src + j));
+      rank += (ku < kv || (ku == kv && j < i)) ? 1 : 0;
     }
     dst[rank] = v;
   }
+}
+
+// (cos, sin) of the cell centres 2 pi (i + 1/2) / kSinCosCells, evaluated in double and rounded once (sincos_tbl)
+__global__ void sincos_table_kernel(float *__restrict__ dst) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= kSinCosCells) return;
+  double sv, cv;
+  sincospi(2.0 * ((double)i + 0.5) / (double)kSinCosCells, &sv, &cv);
+  const uint32_t slot = sincos_slot((uint32_t)i);  // bank swizzle, see sincos_tbl
+  dst[2 * slot] = (float)cv;
+  dst[2 * slot + 1] = (float)sv;
 }
 
 // ---- trajectory mode ------------------------------------------------------------------------------------------------
@@ -76,7 +89,7 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
     for (int m = 0; m < P; m++) {
       const int j = m % kFieldsPerCall;
       if (j == 0) {
-        stream_words(plo, phi, (uint32_t)(m / kFieldsPerCall), kTagBootstrap, p.keys, w);
+        stream_words_rt(p.philox_rounds, plo, phi, (uint32_t)(m / kFieldsPerCall), kTagBootstrap, p.keys, w);
         field_mantissas(w, p.one, mt);
       }
       const float y = __fmaf_rz(__uint_as_float(mt[j]), j < 4 ? p.bc.c21 : p.bc.c22, j < 4 ? p.bc.k21 : p.bc.k22);
@@ -90,8 +103,11 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
     float g[2] = {1.0f, 1.0f};
     for (int m = 0; m < P; m++) {
       const int j = m % kGaussMonthsPerCall;
-      if (j == 0) stream_words(plo, phi, (uint32_t)(m / kGaussMonthsPerCall), kTagGaussian, p.keys, w);
-      if ((j & 1) == 0) gauss_pair(w[j >> 1], p.one, p.gc, g[0], g[1]);
+      if (j == 0) stream_words_rt(p.philox_rounds, plo, phi, (uint32_t)(m / kGaussMonthsPerCall), kTagGaussian, p.keys, w);
+      if ((j & 1) == 0) {  // the same evaluation of sin/cos as the statistics kernel's pair j/2 (table or MUFU)
+        if ((p.gauss_tbl_mask >> (j >> 1)) & 1) gauss_pair_tbl(w[j >> 1], p.one, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
+        else gauss_pair(w[j >> 1], p.one, p.gc, g[0], g[1]);
+      }
       const float gm = g[j & 1];
       tot = flow(__fmul_rn(tot, gm), m);
       v[m + 1] = tot;
@@ -114,8 +130,12 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
         if (rp) rp[m] = raw[idx];
       } else {  // Box-Muller on dimension pairs; an unpaired last month takes the inverse CDF (smmc_device.cuh)
         if ((m & 1) == 0) {
-          if (m + 1 < P) sobol_gauss_pair(x, word(m + 1), p.gc, g[0], g[1]);
-          else g[0] = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);
+          if (m + 1 < P) {
+            if (p.gauss_tbl_mask) sobol_gauss_pair_tbl(x, word(m + 1), p.one, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
+            else sobol_gauss_pair(x, word(m + 1), p.gc, g[0], g[1]);
+          } else {
+            g[0] = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);
+          }
         }
         const float gm = g[m & 1];
         tot = flow(__fmul_rn(tot, gm), m);
@@ -146,7 +166,7 @@ __global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, 
     for (int m = 0; m < p.n_periods; m++) {
       const int j = m % 6;
       if (j == 0) {
-        stream_words(plo, phi, (uint32_t)(m / 6), kTagBootstrap, p.keys, w);
+        stream_words_rt(p.philox_rounds, plo, phi, (uint32_t)(m / 6), kTagBootstrap, p.keys, w);
         field_mantissas(w, p.one, mt);
       }
       const float y = __fmaf_rz(__uint_as_float(mt[j]), j < 4 ? p.bc.c21 : p.bc.c22, j < 4 ? p.bc.k21 : p.bc.k22);
@@ -156,7 +176,7 @@ __global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, 
     uint32_t w[4];
     for (int m = 0; m < p.n_periods; m++) {
       const int j = m % 8;
-      if (j == 0) stream_words(plo, phi, (uint32_t)(m / 8), kTagGaussian, p.keys, w);
+      if (j == 0) stream_words_rt(p.philox_rounds, plo, phi, (uint32_t)(m / 8), kTagGaussian, p.keys, w);
       o[m] = (j & 1) ? w[j >> 1] * kAngleHash : (w[j >> 1] & 0xFFFFFu);
     }
   } else {  // Sobol modes: plain Gray-code evaluation over all 32 direction numbers of dimension m
@@ -170,12 +190,44 @@ __global__ void debug_draws_kernel(int mode, const __grid_constant__ KParams p, 
   }
 }
 
-__global__ void debug_philox_kernel(const uint32_t *ctr, PhiloxKeys keys, int n, uint32_t *out) {
+__global__ void debug_philox_kernel(const uint32_t *ctr, PhiloxKeys keys, int rounds, int n, uint32_t *out) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   uint32_t w[4];
-  philox4x32_10(ctr[4 * t + 0], ctr[4 * t + 1], ctr[4 * t + 2], ctr[4 * t + 3], keys, w);
+  if (rounds == 7) philox4x32<7>(ctr[4 * t + 0], ctr[4 * t + 1], ctr[4 * t + 2], ctr[4 * t + 3], keys, w);
+  else philox4x32<10>(ctr[4 * t + 0], ctr[4 * t + 1], ctr[4 * t + 2], ctr[4 * t + 3], keys, w);
   for (int j = 0; j < 4; j++) out[4 * t + j] = w[j];
+}
+
+// ---- radix select over collected candidate keys ---------------------------------------------------------------------
+// The second select replay appends the ordered keys under the targets' 11-bit prefixes to a buffer (mc_kernel epilogue);
+// the remaining key bits are resolved here over that buffer -- an HBM-bound pass of 4 B per key instead of a third
+// simulation replay.  Same histogram layout as the replay passes: hist[t][digit] over the keys matching prefix[t].
+struct CandParams {
+  int targets, digit_shift, prefix_shift;
+  uint32_t digit_mask;
+  uint32_t prefix[kSelectMaxTargets];
+};
+__global__ void __launch_bounds__(512) select_candidates_kernel(const uint32_t *__restrict__ keys,
+                                                                const unsigned long long *__restrict__ count_dev,
+                                                                unsigned long long capacity, CandParams cp,
+                                                                unsigned long long *__restrict__ hist) {
+  extern __shared__ unsigned int cand_s[];  // [targets][kSelectBins]
+  for (int i = threadIdx.x; i < cp.targets * kSelectBins; i += blockDim.x) cand_s[i] = 0u;
+  __syncthreads();
+  unsigned long long n = *count_dev;
+  if (n > capacity) n = capacity;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint32_t key = __ldcs(keys + i);
+    const uint32_t digit = (key >> cp.digit_shift) & cp.digit_mask;
+    const uint32_t pre = cp.prefix_shift >= 32 ? 0u : key >> cp.prefix_shift;
+    for (int t = 0; t < cp.targets; t++)
+      if (pre == cp.prefix[t]) atomicAdd(&cand_s[t * kSelectBins + digit], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cp.targets * kSelectBins; i += blockDim.x)
+    if (cand_s[i]) atomicAdd(&hist[i], (unsigned long long)cand_s[i]);
 }
 
 // block -> grid stage of the sum: warp shuffle, block partial, last-block-done merge in block order (deterministic bits)
@@ -355,9 +407,10 @@ int plan_warps(int64_t n_paths, int n_sms) {
   return best;
 }
 
-bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, int64_t n_paths,
-                 int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li) {
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, bool sincos,
+                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li) {
   const uint32_t sel_bytes = (uint32_t)sel_targets * kSelectBins * 4u;
+  if (withdrawals && (size_t)n_periods * 4u > smem_optin) return false;  // (size_t: n_periods * 4 must not wrap)
   const uint32_t flow_bytes = withdrawals ? (uint32_t)n_periods * 4u : 0u;
   const bool sobol = (mode == SMMC_MODE_SOBOL_BOOTSTRAP || mode == SMMC_MODE_SOBOL_GAUSSIAN);
   const uint32_t sob_bytes = sobol ? (uint32_t)(((n_periods + 31) & ~31) * 32) : 0u;
@@ -375,6 +428,8 @@ bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_
     }
     if (rep < 1) return false;
     li->rep = rep;
+  } else if (sincos && (mode == SMMC_MODE_GAUSSIAN || mode == SMMC_MODE_SOBOL_GAUSSIAN)) {
+    tbl_bytes = kSinCosBytes;
   }
   li->smem_bytes = smem_layout(hist_bins, sel_bytes, flow_bytes, sob_bytes, tbl_bytes).total;
   return li->smem_bytes <= smem_optin;
@@ -390,15 +445,33 @@ void launch_sort_table(const float *src, int n, float *dst, cudaStream_t s) {
   sort_table_kernel<<<(n + 127) / 128 > 1184 ? 1184 : (n + 127) / 128, 128, 0, s>>>(src, n, dst);
 }
 
-cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s) {
+cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s) {
   switch (mode) {
     case SMMC_MODE_SOBOL_BOOTSTRAP:
-    case SMMC_MODE_SOBOL_GAUSSIAN: return launch_mc_sobol(mode, p, li, s);
-    case SMMC_MODE_BOOTSTRAP_COMPAT: return launch_mc_compat(p, li, variant, s);
-    case SMMC_MODE_BOOTSTRAP: return launch_mc_bootstrap(p, li, variant, s);
-    case SMMC_MODE_GAUSSIAN: return launch_mc_gaussian(p, li, variant, s);
+    case SMMC_MODE_SOBOL_GAUSSIAN: return launch_mc_sobol(mode, p, li, v, s);
+    case SMMC_MODE_BOOTSTRAP_COMPAT: return launch_mc_compat(p, li, v, s);
+    case SMMC_MODE_BOOTSTRAP: return launch_mc_bootstrap(p, li, v, s);
+    case SMMC_MODE_GAUSSIAN: return launch_mc_gaussian(p, li, v, s);
     default: return cudaErrorInvalidValue;
   }
+}
+
+void launch_sincos_table(float *dst, cudaStream_t s) { sincos_table_kernel<<<kSinCosCells / 256, 256, 0, s>>>(dst); }
+
+cudaError_t launch_select_candidates(const uint32_t *keys_dev, const unsigned long long *count_dev, unsigned long long capacity,
+                                     int targets, int digit_shift, uint32_t digit_mask, int prefix_shift,
+                                     const uint32_t *prefix, unsigned long long *hist_dev, int n_sms, cudaStream_t s) {
+  CandParams cp;
+  cp.targets = targets;
+  cp.digit_shift = digit_shift;
+  cp.prefix_shift = prefix_shift;
+  cp.digit_mask = digit_mask;
+  for (int t = 0; t < kSelectMaxTargets; t++) cp.prefix[t] = prefix[t];
+  const size_t smem = (size_t)targets * kSelectBins * sizeof(unsigned int);
+  cudaError_t e = cudaFuncSetAttribute(select_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  select_candidates_kernel<<<n_sms * 2, 512, smem, s>>>(keys_dev, count_dev, capacity, cp, hist_dev);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, const uint32_t *sobol_full,
@@ -416,18 +489,27 @@ cudaError_t launch_trajectories(int mode, const KParams &p, int n_paths, const f
   return cudaGetLastError();
 }
 
-cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n, uint32_t *out_dev, cudaStream_t s) {
+cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int rounds, int n, uint32_t *out_dev, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  debug_philox_kernel<<<(n + 127) / 128, 128, 0, s>>>(ctr_dev, keys, n, out_dev);
+  debug_philox_kernel<<<(n + 127) / 128, 128, 0, s>>>(ctr_dev, keys, rounds, n, out_dev);
   return cudaGetLastError();
 }
 
-cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
-                              double *sum_dev, int n_sms, cudaStream_t s) {
+namespace {
+bool reduce_uses_tma(int64_t n, int n_sms, int which) {
   // >= 4 chunks per CTA: the TMA-pipelined kernel (2 CTAs per SM); smaller inputs: plain streaming loads
-  const char *force = getenv("SMMC_REDUCE");  // development knob: "tma" / "ldg"
   const bool big = n >= (int64_t)n_sms * 2 * 4 * kRedChunkFloats;
-  if ((big && !(force && !strcmp(force, "ldg"))) || (force && !strcmp(force, "tma"))) {
+  return which == 2 || (which != 1 && big);
+}
+}  // namespace
+
+const char *reduce_sum_kernel_name(int64_t n, int n_sms, int which) {
+  return reduce_uses_tma(n, n_sms, which) ? "smmc::reduce_sum_tma_kernel" : "smmc::reduce_sum_kernel";
+}
+
+cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
+                              double *sum_dev, int n_sms, int which, cudaStream_t s) {
+  if (reduce_uses_tma(n, n_sms, which)) {
     cudaError_t e = cudaFuncSetAttribute(reduce_sum_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRedSmemBytes);
     if (e != cudaSuccess) return e;
     reduce_sum_tma_kernel<<<n_sms * 2, kRedThreads, kRedSmemBytes, s>>>(v_dev, n, partials_dev, ticket_dev, sum_dev);

@@ -17,7 +17,8 @@ struct KParams {
   int32_t n_periods;     // P
   int32_t n_returns;     // n
   uint32_t compat_seed;  // added to the PCG seed input in BOOTSTRAP_COMPAT
-  // return table, scaled by 0.01f and replicated `rep` times per entry ([n+1][rep], entry n is a zero pad)
+  // return table, scaled by 0.01f and replicated `rep` times per entry ([n+1][rep], entry n is a zero pad);
+  // Gaussian modes: the (cos, sin) table of sincos_tbl() instead ([kSinCosCells][2], tbl_bytes = kSinCosBytes; 0 = MUFU sin/cos)
   const float *tbl_rep;
   uint32_t tbl_bytes;  // bytes to stage (multiple of 16)
   uint32_t rep4;       // rep * 4: bytes per table row
@@ -25,6 +26,7 @@ struct KParams {
   BootConsts bc;       // BOOTSTRAP: fma.rz index constants and the row shift
   uint32_t one;        // 0x3F800000, passed as a value the compiler cannot fold: keeps (w & mask) | one a single LOP3
   PhiloxKeys keys;
+  int32_t philox_rounds;  // 10 (default) or 7 (smmc_config.philox_rounds); the simulation kernel takes it as a template parameter
   GaussConsts gc;
   float sigma_sqrt2;  // SOBOL_GAUSSIAN: sqrt(2) * std/100
   float v0;
@@ -42,8 +44,9 @@ struct KParams {
   double *stats;               // [SMMC_STATS_HEADER + bins + 2]
   // Sobol (DESIGN.md "Sobol"): point index of path p is p + 256; month m is dimension m
   const uint32_t *sobol_lo;  // [P_pad][8]   direction numbers of index bits 0..7, month-major (staged to smem)
-  const uint32_t *sobol_hi;  // [26][P_pad]  rows 0..23: direction numbers of index bits 8..31 (bit-major);
-                             //              row 24: bit 7 again; row 25: digital shift per month (0 = plain)
+  const uint32_t *sobol_hi;  // [98][P_pad]  rows 0..1: digital shift per month (0 = plain), row 1 with the bit-7 direction
+                             //              number folded in (h odd); rows 2 + 16 g + c: XOR of the direction numbers
+                             //              of index bits 8 + 4 g + {set bits of c}, g < 6, c < 16
   int32_t sobol_ppad;        // P rounded up to a multiple of 32
   uint32_t sobol_lo_bytes;   // P_pad * 32
   // order-statistic search pass (smmc_select_pass): a radix-select digit histogram of the finals' ordered keys,
@@ -54,6 +57,15 @@ struct KParams {
   int32_t sel_prefix_shift;     // prefix = key >> sel_prefix_shift; 32 = first pass (every key matches)
   uint32_t sel_prefix[kSelectMaxTargets];
   unsigned long long *sel_hist_g;  // [sel_targets][bins], zeroed before launch
+  // candidate collection (second select pass): the ordered keys whose top 11 bits equal one of cand_prefix[] are appended
+  // to cand_keys (one atomicAdd on *cand_cursor per 256-path block); the remaining 21 key bits are then resolved over
+  // that buffer (select_candidates_kernel) instead of by a third replay.  Keys beyond cand_capacity are counted, not stored.
+  int32_t cand_groups;                     // 0 = do not collect
+  uint32_t cand_prefix[kSelectMaxTargets];  // distinct 11-bit prefixes
+  uint32_t *cand_keys;
+  unsigned long long *cand_cursor;  // zeroed before launch
+  unsigned long long cand_capacity;
+  int32_t gauss_tbl_mask;  // trajectory kernel: which Box-Muller pairs take sin/cos from the table (the mc kernel's TBL)
   // per-period withdrawals (null = none): value <- max(value * flow_q[m] - flow_w, 0) after month m's return
   const float *flow_q;  // [n_periods] keep-fractions 1 - pct_m/100 (device)
   float flow_w;         // fixed amount per period
@@ -67,16 +79,19 @@ constexpr int kThreads = SMMC_MAX_THREADS;
 constexpr int kWarps = kThreads / 32;
 
 // shared memory layout (dynamic):
-// [0,8) mbarrier | [16, 16+8*(bins+2)) histogram | warp partials | select-pass digit histograms (u32) |
+// [0,8) mbarrier | [16, 16+4*(bins+2)) histogram (u32 per CTA: a 64-bit shared-memory atomicAdd is a CAS loop, which the
+// 32 lanes of a warp hitting a handful of bins turn into 2.7 % of the C2 kernel; counts per CTA stay < 2^32 because
+// validate() caps a call at 2^38 paths) | warp partials | select-pass digit histograms (u32) |
 // Sobol low direction numbers | table (128-B aligned)
 struct SmemLayout {
   uint32_t hist_off, wp_off, sel_off, flow_off, sob_off, tbl_off, total;
 };
+// tbl_bytes: the return table (bootstrap modes) or the sin/cos table (Gaussian modes) -- a mode has one or the other
 __host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, uint32_t flow_bytes, uint32_t sob_bytes,
                                                   uint32_t tbl_bytes) {
   SmemLayout L;
   L.hist_off = 16;
-  L.wp_off = L.hist_off + 8u * (uint32_t)(bins + 2);
+  L.wp_off = (L.hist_off + 4u * (uint32_t)(bins + 2) + 7u) & ~7u;
   L.sel_off = (L.wp_off + 32u * kWarps + 15u) & ~15u;
   L.flow_off = (L.sel_off + sel_bytes + 15u) & ~15u;
   L.sob_off = (L.flow_off + flow_bytes + 127u) & ~127u;
@@ -85,6 +100,23 @@ __host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, 
   return L;
 }
 
+// Build-time choices that do not touch the contract (every choice computes the same draws):
+constexpr int kGaussTblDefault = 5;      // GAUSSIAN: pairs 0 and 2 of a call take sin/cos from the shared-memory table
+constexpr int kSobolUnrollDefault = 2;   // SOBOL_BOOTSTRAP month-loop unroll
+
+// Test / development hook (smmc_debug_set_variant): selects among the compiled kernel variants.  Zero / negative = default.
+// Never read from the environment: a drop-in library must not change kernels because of an environment variable.
+struct Variant {
+  int ilp = 0;           // paths per lane in flight (COMPAT / BOOTSTRAP: 2, 4, 8; GAUSSIAN: 4, 8)
+  int warps = 0;         // warps per CTA (1..32), 0 = plan_warps
+  int reduce = 0;        // reduce_mean kernel: 1 = plain streaming loads, 2 = TMA ring, 0 = by size
+  int gauss_tbl = -1;    // GAUSSIAN: table mask (0 = all MUFU), -1 = default
+  int sobol_tbl = -1;    // SOBOL_GAUSSIAN: 0 = MUFU sin/cos, 1 = table, -1 = default (table)
+  int sobol_unroll = 0;  // SOBOL_BOOTSTRAP month unroll (experiment builds), 0 = default
+  int finals_chunks = 0; // host-pointer finals pipeline: number of chunks (0 = automatic, 1 = one monolithic launch)
+};
+
+constexpr int kSobolHiRows = 98;   // rows of KParams::sobol_hi
 constexpr uint32_t kSobolSkip = 256;  // first Sobol point used; keeps 256-path blocks aligned to 256-point blocks
 
 struct LaunchInfo {
@@ -96,15 +128,18 @@ struct LaunchInfo {
 
 // Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
 // Also picks the warps per CTA for `n_paths` (warps_override in 1..32 forces it; 0 = automatic).
-bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, int64_t n_paths,
-                 int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li);
+// sincos: Gaussian modes stage the sin/cos table (kSinCosBytes) where the bootstrap modes stage the return table.
+bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, bool sincos,
+                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li);
 
 // Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
 void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);
 // dst = src sorted ascending (stable rank sort; SOBOL_BOOTSTRAP samples the empirical quantile function)
 void launch_sort_table(const float *src, int n, float *dst, cudaStream_t s);
 
-cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s);
+cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
+// fills dst[kSinCosCells][2] with (cos, sin) of the cell centres, correctly rounded from double (once per device)
+void launch_sincos_table(float *dst, cudaStream_t s);
 
 // introspection kernels (parity tests)
 // sobol_full: [n_dims][32] direction numbers (device), only read in the Sobol modes
@@ -114,11 +149,20 @@ cudaError_t launch_debug_draws(int mode, const KParams &p, int n_paths, const ui
 cudaError_t launch_trajectories(int mode, const KParams &p, int n_paths, const float *tbl, const float *raw,
                                 const uint32_t *sobol_full, const uint32_t *shift, float *values_dev, float *rets_dev,
                                 cudaStream_t s);
-cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int n, uint32_t *out_dev, cudaStream_t s);
+cudaError_t launch_debug_philox(const uint32_t *ctr_dev, PhiloxKeys keys, int rounds, int n, uint32_t *out_dev, cudaStream_t s);
+
+// digit histograms of the candidate keys collected by a select pass: hist[t][digit] over the keys whose top
+// (32 - prefix_shift) bits equal prefix[t]; n_keys is read from *count_dev (clamped to capacity) on the device
+cudaError_t launch_select_candidates(const uint32_t *keys_dev, const unsigned long long *count_dev, unsigned long long capacity,
+                                     int targets, int digit_shift, uint32_t digit_mask, int prefix_shift,
+                                     const uint32_t *prefix, unsigned long long *hist_dev, int n_sms, cudaStream_t s);
 
 // small reference entry points
+// which: 0 = by size, 1 = plain streaming loads, 2 = TMA ring (test hook)
 cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_dev, unsigned int *ticket_dev,
-                              double *sum_dev, int n_sms, cudaStream_t s);
+                              double *sum_dev, int n_sms, int which, cudaStream_t s);
+// name of the kernel launch_reduce_sum dispatches for (n, which) -- reported by the bench
+const char *reduce_sum_kernel_name(int64_t n, int n_sms, int which);
 cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, int n_sms, cudaStream_t s);
 
 }  // namespace smmc

@@ -1,13 +1,28 @@
-// GAUSSIAN instantiations of the fused kernel (Philox4x32-10 + Box-Muller, eight months per call).
+// GAUSSIAN instantiations of the fused kernel (Philox4x32-10 by default, Philox4x32-7 on request; Box-Muller, eight months
+// per call).  TBL (which pairs of a call take sin/cos from the shared-memory table) is a property of the build, not of
+// the contract: every mask evaluates the same angles (smmc_device.cuh, sincos_tbl).
 #include "smmc_mc_kernel.cuh"
 
 namespace smmc {
-cudaError_t launch_mc_gaussian(const KParams &p, const LaunchInfo &li, int variant, cudaStream_t s) {
-  switch (variant) {
-    case 1: return launch_one<SMMC_MODE_GAUSSIAN, 1>(p, li, s);
-    case 2: return launch_one<SMMC_MODE_GAUSSIAN, 2>(p, li, s);
-    case 4: return launch_one<SMMC_MODE_GAUSSIAN, 4>(p, li, s);
-    default: return launch_one<SMMC_MODE_GAUSSIAN, 8>(p, li, s);  // all eight paths of a lane at once: +1.1 % over 4 (measured)
+namespace {
+template <int ROUNDS>
+cudaError_t launch_rounds(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s) {
+  const int tbl = p.tbl_bytes ? (v.gauss_tbl >= 0 ? v.gauss_tbl : kGaussTblDefault) : 0;
+  switch (tbl) {
+    case 0: return v.ilp == 4 ? launch_one<SMMC_MODE_GAUSSIAN, 4, -1, ROUNDS, 0>(p, li, s)
+                              : launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 0>(p, li, s);
+#ifdef SMMC_EXPERIMENT
+    case 1: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 1>(p, li, s);
+    case 7: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 7>(p, li, s);
+    case 15: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 15>(p, li, s);
+#endif
+    default: return v.ilp == 4 ? launch_one<SMMC_MODE_GAUSSIAN, 4, -1, ROUNDS, kGaussTblDefault>(p, li, s)
+                               : launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, kGaussTblDefault>(p, li, s);
   }
+}
+}  // namespace
+
+cudaError_t launch_mc_gaussian(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s) {
+  return p.philox_rounds == 7 ? launch_rounds<7>(p, li, v, s) : launch_rounds<10>(p, li, v, s);
 }
 }  // namespace smmc

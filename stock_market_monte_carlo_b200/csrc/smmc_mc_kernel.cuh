@@ -90,13 +90,17 @@ __device__ __forceinline__ void run_compat(const KParams &p, const Flow<FLOW> &f
   }
 }
 
+// SOBOL_BOOTSTRAP draw: idx = mulhi(x, n) into the sorted table; row address by one IMAD.  (Tried in round 2: folding the
+// row stride into the multiplier -- mulhi(x, n rep4) + base as the IMAD.HI addend, then one LOP3 to mask in the lane's
+// column -- executes 7.3 instead of 8.9 instructions per path-month but runs 8 % SLOWER (1.880 vs 1.737 ms at C4): the
+// LOP3 sits on the ALU pipe between the multiply and the load of every draw, the IMAD it replaces does not.)
 __device__ __forceinline__ float boot_step(float tot, uint32_t w, uint32_t n, uint32_t rep4, uint32_t base) {
   const float r = lds_f32(__umulhi(w, n) * rep4 + base);  // idx = mulhi(w, n); row address by one IMAD
   return fmaf(tot, r, tot);
 }
 
 // months 6q..6q+5 of ILP paths: one Philox call each, six table gathers, six FFMAs
-template <int ILP, int SHIFT, bool FLOW>
+template <int ILP, int SHIFT, bool FLOW, int ROUNDS>
 __device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW> &fl, uint32_t base,
                                               const uint32_t (&plo)[ILP], uint32_t phi, float (&tot)[ILP]) {
   const BootConsts bc = p.bc;
@@ -107,7 +111,7 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW>
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4], m[6];
-      stream_words(plo[i], phi, (uint32_t)q, kTagBootstrap, p.keys, w);
+      stream_words<ROUNDS>(plo[i], phi, (uint32_t)q, kTagBootstrap, p.keys, w);
       field_mantissas(w, one, m);
 #pragma unroll
       for (int j = 0; j < 6; j++) {
@@ -121,7 +125,7 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW>
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4], m[6];
-      stream_words(plo[i], phi, (uint32_t)nq, kTagBootstrap, p.keys, w);
+      stream_words<ROUNDS>(plo[i], phi, (uint32_t)nq, kTagBootstrap, p.keys, w);
       field_mantissas(w, one, m);
 #pragma unroll
       for (int j = 0; j < 5; j++)
@@ -133,10 +137,19 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW>
   }
 }
 
-// months 8q..8q+7 of ILP paths: one Philox call each, four Box-Muller pairs
-template <int ILP, bool FLOW>
-__device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> &fl, const uint32_t (&plo)[ILP],
-                                             uint32_t phi, float (&tot)[ILP]) {
+// months 8q..8q+7 of ILP paths: one Philox call each, four Box-Muller pairs.  TBL is a 4-bit mask: pair j of a call takes
+// sin/cos from the shared-memory table (sincos_tbl, no MUFU) when bit j is set, from MUFU.SIN/COS otherwise -- the two
+// evaluate the same angle of the same contract (smmc_device.cuh); the mix balances the XU pipe against the FMA/ALU pipes.
+template <int TBL>
+__device__ __forceinline__ void gauss_pair_sel(int j, uint32_t w, uint32_t one, const GaussConsts gc, const char *sc_tbl,
+                                               float &g0, float &g1) {
+  if ((TBL >> j) & 1) gauss_pair_tbl(w, one, gc, sc_tbl, g0, g1);
+  else gauss_pair(w, one, gc, g0, g1);
+}
+
+template <int ILP, bool FLOW, int ROUNDS, int TBL>
+__device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> &fl, const char *sc_tbl,
+                                             const uint32_t (&plo)[ILP], uint32_t phi, float (&tot)[ILP]) {
   const GaussConsts gc = p.gc;
   const uint32_t one = p.one;
   const int nq = p.n_periods / kGaussMonthsPerCall;
@@ -145,11 +158,11 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
-      stream_words(plo[i], phi, (uint32_t)q, kTagGaussian, p.keys, w);
+      stream_words<ROUNDS>(plo[i], phi, (uint32_t)q, kTagGaussian, p.keys, w);
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float g0, g1;
-        gauss_pair(w[j], one, gc, g0, g1);
+        gauss_pair_sel<TBL>(j, w[j], one, gc, sc_tbl, g0, g1);
         const int m = q * kGaussMonthsPerCall + 2 * j;
         tot[i] = fl(__fmul_rn(fl(__fmul_rn(tot[i], g0), m), g1), m + 1);
       }
@@ -160,11 +173,11 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 #pragma unroll
     for (int i = 0; i < ILP; i++) {
       uint32_t w[4];
-      stream_words(plo[i], phi, (uint32_t)nq, kTagGaussian, p.keys, w);
+      stream_words<ROUNDS>(plo[i], phi, (uint32_t)nq, kTagGaussian, p.keys, w);
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float g0, g1;
-        gauss_pair(w[j], one, gc, g0, g1);
+        gauss_pair_sel<TBL>(j, w[j], one, gc, sc_tbl, g0, g1);
         const int m = nq * kGaussMonthsPerCall + 2 * j;
         if (2 * j < rem) tot[i] = fl(__fmul_rn(tot[i], g0), m);
         if (2 * j + 1 < rem) tot[i] = fl(__fmul_rn(tot[i], g1), m + 1);
@@ -179,9 +192,9 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 // h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
-template <int MODE, bool FLOW>
-__device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, uint32_t tbl_base, const uint4 *vlo,
-                                          uint32_t h, uint32_t lane, float (&tot)[8]) {
+template <int MODE, bool FLOW, int TBL, int UNROLL>
+__device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, const char *tbl, uint32_t lane_off,
+                                          const uint4 *vlo, uint32_t h, uint32_t lane, float (&tot)[8]) {
   const uint32_t mk0 = ((lane ^ (lane >> 1)) & 1u) ? 0xffffffffu : 0u;
   const uint32_t mk1 = (((lane >> 1) ^ (lane >> 2)) & 1u) ? 0xffffffffu : 0u;
   const uint32_t mk2 = (((lane >> 2) ^ (lane >> 3)) & 1u) ? 0xffffffffu : 0u;
@@ -190,16 +203,19 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   const uint32_t gh = h ^ (h >> 1);
   const int ppad = p.sobol_ppad;
   const uint32_t n = (uint32_t)p.n_returns, rep4 = p.rep4;
+  const uint32_t lane_base = smem_u32(tbl) + lane_off;  // shared-window address of this lane's table column
+  const uint32_t one = p.one;
   const GaussConsts gc = p.gc;
-  // warp-uniform part of month m0 + lane: every load is issued before the first is consumed (independent,
-  // predicated on the warp-uniform gray bits), and the next 32 months are fetched while the current 32 are computed
+  // warp-uniform part of month m0 + lane.  The host tabulates, per month, the XOR of the direction numbers of every 4-bit
+  // group of gray(h) (six groups x 16 combinations) and the two variants of (digital shift ^ [h odd] V[7]): seven
+  // independent, unconditional loads (L2-resident table) instead of 26 predicated ones behind 26 branches -- that was
+  // 0.6 of the 8.9 executed instructions per path-month in round 1.  The next 32 months are fetched while the current
+  // 32 are computed.
   auto block_part = [&](int m0) {
     const uint32_t *col = p.sobol_hi + m0 + lane;
-    uint32_t U = __ldg(col + 25 * ppad);
-    if (h & 1u) U ^= __ldg(col + 24 * ppad);
+    uint32_t U = __ldg(col + (h & 1u) * ppad);
 #pragma unroll
-    for (int k = 0; k < 24; k++)
-      if ((gh >> k) & 1u) U ^= __ldg(col + k * ppad);
+    for (int g = 0; g < 6; g++) U ^= __ldg(col + (2u + 16u * g + ((gh >> (4 * g)) & 15u)) * ppad);
     return U;
   };
   // the eight words of month m (one per path of the lane) from the broadcast block part Um
@@ -226,12 +242,12 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
     if (m0 + 32 < p.n_periods) U_next = block_part(m0 + 32);
     const int mend = (p.n_periods - m0) < 32 ? (p.n_periods - m0) : 32;
     if (MODE == SMMC_MODE_SOBOL_BOOTSTRAP) {
-#pragma unroll 2
+#pragma unroll UNROLL
       for (int mi = 0; mi < mend; mi++) {
         uint32_t x[8];
         month_words(m0 + mi, __shfl_sync(0xffffffffu, U, mi), x);
 #pragma unroll
-        for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], n, rep4, tbl_base), m0 + mi);
+        for (int j = 0; j < 8; j++) tot[j] = fl(boot_step(tot[j], x[j], n, rep4, lane_base), m0 + mi);
       }
     } else {
       // Box-Muller on dimension pairs (smmc_device.cuh): even month = radius word, odd month = angle word
@@ -243,7 +259,8 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
 #pragma unroll
         for (int j = 0; j < 8; j++) {
           float g0, g1;
-          sobol_gauss_pair(xr[j], xa[j], gc, g0, g1);
+          if (TBL) sobol_gauss_pair_tbl(xr[j], xa[j], one, gc, tbl, g0, g1);  // sin/cos from the shared-memory table
+          else sobol_gauss_pair(xr[j], xa[j], gc, g0, g1);
           tot[j] = fl(__fmul_rn(fl(__fmul_rn(tot[j], g0), m0 + mi), g1), m0 + mi + 1);
         }
       }
@@ -260,16 +277,22 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
 
 // ---- the fused persistent kernel ---------------------------------------------------------------------------------
 
-template <int MODE, int ILP, int SHIFT, bool FLOW>
+// MODE: smmc_mode.  ILP: paths of a lane in flight at once.  SHIFT: log2(row bytes) as an immediate (BOOTSTRAP), -1 = from
+// KParams.  FLOW: per-period withdrawals.  ROUNDS: Philox rounds (10 | 7).  TBL: Gaussian modes -- which Box-Muller pairs
+// take sin/cos from the shared-memory table (GAUSSIAN: 4-bit mask over the pairs of a call; SOBOL_GAUSSIAN: 0 | 1).
+// UNROLL: month-loop unroll of SOBOL_BOOTSTRAP.
+template <int MODE, int ILP, int SHIFT, bool FLOW, int ROUNDS, int TBL, int UNROLL>
 __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
+  constexpr bool kGauss = (MODE == SMMC_MODE_GAUSSIAN || MODE == SMMC_MODE_SOBOL_GAUSSIAN);
+  // "table" = the bank-private return table (bootstrap modes) or the sin/cos table (Gaussian modes with TBL != 0)
   constexpr bool kHasTable = (MODE == SMMC_MODE_BOOTSTRAP_COMPAT || MODE == SMMC_MODE_BOOTSTRAP ||
-                              MODE == SMMC_MODE_SOBOL_BOOTSTRAP);
+                              MODE == SMMC_MODE_SOBOL_BOOTSTRAP || (kGauss && TBL != 0));
   constexpr bool kSobol = (MODE == SMMC_MODE_SOBOL_BOOTSTRAP || MODE == SMMC_MODE_SOBOL_GAUSSIAN);
   const SmemLayout L = smem_layout(p.hist_bins, (uint32_t)p.sel_targets * kSelectBins * 4u, FLOW ? (uint32_t)p.n_periods * 4u : 0u,
                                    kSobol ? p.sobol_lo_bytes : 0u, kHasTable ? p.tbl_bytes : 0u);
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
-  unsigned long long *hist_s = reinterpret_cast<unsigned long long *>(smem + L.hist_off);
+  unsigned int *hist_s = reinterpret_cast<unsigned int *>(smem + L.hist_off);  // u32 per CTA (native smem atomics), u64 globally
   double *wp = reinterpret_cast<double *>(smem + L.wp_off);
   unsigned int *sel_s = reinterpret_cast<unsigned int *>(smem + L.sel_off);
   float *flow_s = reinterpret_cast<float *>(smem + L.flow_off);
@@ -300,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
                      (sb - o) < kChunk ? (sb - o) : kChunk, bar);
     }
   }
-  for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x) hist_s[i] = 0ull;
+  for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x) hist_s[i] = 0u;
   for (int i = tid; i < p.sel_targets * kSelectBins; i += (int)blockDim.x) sel_s[i] = 0u;
   if (FLOW)
     for (int i = tid; i < p.n_periods; i += (int)blockDim.x) flow_s[i] = __ldg(p.flow_q + i);
@@ -331,7 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     if (kSobol) {
 #pragma unroll
       for (int j = 0; j < kPathsPerLane; j++) x[j] = p.v0;
-      run_sobol<MODE, FLOW>(p, fl, lane_base, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
+      run_sobol<MODE, FLOW, TBL, UNROLL>(p, fl, tbl, lane_off, vlo, (uint32_t)((base + kSobolSkip) >> 8), lane, x);
     }
 #pragma unroll
     for (int s = 0; s < (kSobol ? 0 : kPathsPerLane); s += ILP) {
@@ -343,8 +366,8 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
         tot[i] = p.v0;
       }
       if (MODE == SMMC_MODE_BOOTSTRAP_COMPAT) run_compat<ILP, FLOW>(p, fl, lane_base, plo, tot);
-      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT, FLOW>(p, fl, boot_base, plo, phi, tot);
-      if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP, FLOW>(p, fl, plo, phi, tot);
+      if (MODE == SMMC_MODE_BOOTSTRAP) run_bootstrap<ILP, SHIFT, FLOW, ROUNDS>(p, fl, boot_base, plo, phi, tot);
+      if (MODE == SMMC_MODE_GAUSSIAN) run_gaussian<ILP, FLOW, ROUNDS, TBL>(p, fl, tbl, plo, phi, tot);
 #pragma unroll
       for (int i = 0; i < ILP; i++) x[s + i] = tot[i];
     }
@@ -357,7 +380,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
       if (valid[j]) {
         if (p.finals) p.finals[b * kBlock + j * 32 + lane] = x[j];
         below_lane += (x[j] < p.target) ? 1u : 0u;
-        if (p.hist_bins > 0) atomicAdd(&hist_s[hist_bin(x[j], p.hist_lo, p.hist_inv_w, p.hist_bins)], 1ull);
+        if (p.hist_bins > 0) atomicAdd(&hist_s[hist_bin(x[j], p.hist_lo, p.hist_inv_w, p.hist_bins)], 1u);
         if (p.sel_targets > 0) {  // radix-select pass: digit histogram of the keys under each target's prefix
           const uint32_t key = ordered_key(x[j]);
           const uint32_t digit = (key >> p.sel_digit_shift) & p.sel_digit_mask;
@@ -366,6 +389,33 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
             if (pre == p.sel_prefix[t]) atomicAdd(&sel_s[t * kSelectBins + digit], 1u);
         }
       }
+    }
+    if (p.cand_groups > 0) {  // second select pass: keep the keys under the targets' 11-bit prefixes (warp-uniform branch)
+      uint32_t match = 0;
+#pragma unroll
+      for (int j = 0; j < kPathsPerLane; j++) {
+        const uint32_t pre11 = ordered_key(x[j]) >> 21;
+        bool hit = false;
+        for (int g = 0; g < p.cand_groups; g++) hit = hit || (pre11 == p.cand_prefix[g]);
+        if (hit && valid[j]) match |= 1u << j;
+      }
+      const uint32_t cnt = (uint32_t)__popc(match);
+      uint32_t incl = cnt;  // inclusive warp scan of the per-lane counts: ONE global atomic per 256-path block
+#pragma unroll
+      for (int st = 1; st < 32; st <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, st);
+        if ((int)lane >= st) incl += o;
+      }
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      unsigned long long base_c = 0ull;
+      if (lane == 0 && total) base_c = atomicAdd(p.cand_cursor, (unsigned long long)total);
+      base_c = __shfl_sync(0xffffffffu, base_c, 0) + (incl - cnt);
+#pragma unroll
+      for (int j = 0; j < kPathsPerLane; j++)
+        if ((match >> j) & 1u) {
+          if (base_c < p.cand_capacity) p.cand_keys[base_c] = ordered_key(x[j]);
+          base_c++;
+        }
     }
 
     // ---- block mean / population variance in the reference's reduceBlock layout and reduction order
@@ -433,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     cp[3] = below;
   }
   for (int i = tid; i < p.hist_bins + 2; i += (int)blockDim.x)
-    if (hist_s[i]) atomicAdd(&p.hist_g[i], hist_s[i]);
+    if (hist_s[i]) atomicAdd(&p.hist_g[i], (unsigned long long)hist_s[i]);
   for (int i = tid; i < p.sel_targets * kSelectBins; i += (int)blockDim.x)
     if (sel_s[i]) atomicAdd(&p.sel_hist_g[i], (unsigned long long)sel_s[i]);
   __threadfence();
@@ -486,19 +536,20 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
     p.stats[SMMC_STATS_HEADER + i] = (double)__ldcg(&p.hist_g[i]);
 }
 
-template <int MODE, int ILP, int SHIFT, bool FLOW>
+template <int MODE, int ILP, int SHIFT, bool FLOW, int ROUNDS, int TBL, int UNROLL>
 cudaError_t launch_flow(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(mc_kernel<MODE, ILP, SHIFT, FLOW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)li.smem_bytes);
+  auto kern = mc_kernel<MODE, ILP, SHIFT, FLOW, ROUNDS, TBL, UNROLL>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)li.smem_bytes);
   if (e != cudaSuccess) return e;
-  mc_kernel<MODE, ILP, SHIFT, FLOW><<<li.grid, li.threads, li.smem_bytes, s>>>(p);
+  kern<<<li.grid, li.threads, li.smem_bytes, s>>>(p);
   return cudaGetLastError();
 }
 
 // the withdrawal variant is a separate instantiation: the default kernels carry no trace of it
-template <int MODE, int ILP, int SHIFT = -1>
+template <int MODE, int ILP, int SHIFT = -1, int ROUNDS = 10, int TBL = 0, int UNROLL = 2>
 cudaError_t launch_one(const KParams &p, const LaunchInfo &li, cudaStream_t s) {
-  return p.flow_q ? launch_flow<MODE, ILP, SHIFT, true>(p, li, s) : launch_flow<MODE, ILP, SHIFT, false>(p, li, s);
+  return p.flow_q ? launch_flow<MODE, ILP, SHIFT, true, ROUNDS, TBL, UNROLL>(p, li, s)
+                  : launch_flow<MODE, ILP, SHIFT, false, ROUNDS, TBL, UNROLL>(p, li, s);
 }
 
 }  // namespace

@@ -99,7 +99,7 @@ class Result:
 def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
                 gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None, device=0,
                 flags=0, stream=0, returns_ptr=None, n_returns=None, withdraw_fixed=0.0, withdraw_pct=0.0,
-                withdraw_pct_schedule=None):
+                withdraw_pct_schedule=None, philox_rounds=0):
     cfg = N.SmmcConfig()
     cfg.abi_version = N.SMMC_ABI_VERSION
     cfg.mode = N.MODES[mode] if isinstance(mode, str) else int(mode)
@@ -126,6 +126,7 @@ def make_config(mode, n_simulations, n_periods, initial_capital=1000.0, returns=
     cfg.device = int(device)
     cfg.flags = int(flags)
     cfg.stream = int(stream) if stream else None
+    cfg.philox_rounds = int(philox_rounds)
     cfg.withdraw_fixed = float(withdraw_fixed)
     cfg.withdraw_pct = float(withdraw_pct)
     if withdraw_pct_schedule is not None:
@@ -141,7 +142,7 @@ def simulate(mode, n_simulations, n_periods, initial_capital=1000.0, returns=Non
              gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None,
              want_finals=False, want_block_partials=False, device=0, n_gpus=1, select=None, **withdrawals) -> Result:
     """One blocking run through `smmc_run` / `smmc_run_multi` with HOST buffers (the call a user makes).
-    withdrawals: withdraw_fixed=, withdraw_pct=, withdraw_pct_schedule= (include/smmc.h, ABI 2).
+    withdrawals: withdraw_fixed=, withdraw_pct=, withdraw_pct_schedule= (include/smmc.h, ABI 2) and philox_rounds= (ABI 3).
     select: a fresh SelectState -- the first radix-select pass rides along (`smmc_run_select`, one GPU) and its digit
     histogram is returned as Result.select_hist (see simulate_with_quantiles)."""
     lib = N.load()
@@ -327,7 +328,7 @@ def simulate_with_quantiles(mode, n_simulations, n_periods, ranks=None, **kw):
     cfg, keep = make_config(mode, n_simulations, n_periods, kw.get("initial_capital", 1000.0), kw.get("returns"),
                             kw.get("seed", 0), kw.get("stream_offset", 0), kw.get("gauss_mean", 0.5),
                             kw.get("gauss_std", 10.0 / 12.0), device=kw.get("device", 0),
-                            **{k: v for k, v in skw.items() if k.startswith("withdraw")})
+                            **{k: v for k, v in skw.items() if k.startswith("withdraw") or k == "philox_rounds"})
     extra_ms = 0.0
     while not st.done:
         st.advance(st.run_pass(cfg))
@@ -431,20 +432,26 @@ def plan_launch(mode, n_simulations, n_periods, n_returns=0, hist_bins=0, select
     return int(plan.grid), int(plan.threads), int(plan.table_copies), int(plan.smem_bytes)
 
 
-def debug_draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0, device=0):
+def debug_draws(mode, n_paths, n_periods, returns=None, seed=0, stream_offset=0, device=0, philox_rounds=0):
     lib = N.load()
     cfg, keep = make_config(mode, n_paths, n_periods, returns=returns, seed=seed, stream_offset=stream_offset,
-                            device=device)
+                            device=device, philox_rounds=philox_rounds)
     out = np.zeros((int(n_paths), int(n_periods)), dtype=np.uint32)
     N.check(lib.smmc_debug_draws(C.byref(cfg), int(n_paths), out.ctypes.data))
     del keep
     return out
 
 
-def debug_philox(ctr, key, device=0):
+def debug_philox(ctr, key, device=0, rounds=10):
     lib = N.load()
     ctr = np.ascontiguousarray(np.asarray(ctr, dtype=np.uint32).reshape(-1, 4))
     key = np.ascontiguousarray(np.asarray(key, dtype=np.uint32).reshape(2))
     out = np.zeros_like(ctr)
-    N.check(lib.smmc_debug_philox(ctr.ctypes.data, key.ctypes.data, int(ctr.shape[0]), int(device), out.ctypes.data))
+    N.check(lib.smmc_debug_philox_rounds(ctr.ctypes.data, key.ctypes.data, int(rounds), int(ctr.shape[0]), int(device),
+                                         out.ctypes.data))
     return out
+
+
+def set_variant(key=None, value=-1):
+    """Test hook (`smmc_debug_set_variant`): pick a compiled kernel variant; set_variant() resets everything."""
+    N.check(N.load().smmc_debug_set_variant(key.encode() if key is not None else None, int(value)))

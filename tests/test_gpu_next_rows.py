@@ -163,18 +163,20 @@ def test_trajectory_file_roundtrip_through_reference_format(S, table, tmp_path):
 # ---- warps per CTA ---------------------------------------------------------------------------------------------------
 
 @pytest.mark.parametrize("mode", ALL_MODES)
-def test_results_do_not_depend_on_warps_per_cta(S, O, table, mode, monkeypatch):
+def test_results_do_not_depend_on_warps_per_cta(S, O, table, mode):
     kw = mode_kwargs(mode, table)
     N, P = 148 * 27 * 256 + 300, 12  # just over one wave of 27-warp CTAs
     base = S.simulate(mode, N, P, hist_bins=64, want_finals=True, want_block_partials=True, **kw)
-    for w in ("20", "27", "32"):
-        monkeypatch.setenv("SMMC_WARPS", w)
-        r = S.simulate(mode, N, P, hist_bins=64, want_finals=True, want_block_partials=True, **kw)
-        assert np.array_equal(r.finals.view(np.uint32), base.finals.view(np.uint32))
-        assert np.array_equal(r.block_means.view(np.uint32), base.block_means.view(np.uint32))
-        assert np.array_equal(r.hist, base.hist) and r.below_count == base.below_count
-        assert abs(r.mean - base.mean) <= 1e-12 * abs(base.mean) and abs(r.m2 - base.m2) <= 1e-9 * abs(base.m2)
-    monkeypatch.delenv("SMMC_WARPS")
+    try:
+        for w in (20, 27, 32):
+            S.set_variant("warps", w)
+            r = S.simulate(mode, N, P, hist_bins=64, want_finals=True, want_block_partials=True, **kw)
+            assert np.array_equal(r.finals.view(np.uint32), base.finals.view(np.uint32))
+            assert np.array_equal(r.block_means.view(np.uint32), base.block_means.view(np.uint32))
+            assert np.array_equal(r.hist, base.hist) and r.below_count == base.below_count
+            assert abs(r.mean - base.mean) <= 1e-12 * abs(base.mean) and abs(r.m2 - base.m2) <= 1e-9 * abs(base.m2)
+    finally:
+        S.set_variant()
 
 
 # ---- the C++ side of the same rows -----------------------------------------------------------------------------------

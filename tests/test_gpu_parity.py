@@ -189,10 +189,11 @@ def test_table_too_large_is_reported(S):
 
 
 def test_ilp_variants_agree(S, table):
+    """kernel variants are chosen through the test hook smmc_debug_set_variant (never the environment)"""
     base = {}
     try:
-        for ilp in ("1", "2", "4", "8"):
-            os.environ["SMMC_ILP"] = ilp
+        for ilp in (2, 4, 8):
+            S.set_variant("ilp", ilp)
             for mode in ("bootstrap_compat", "bootstrap", "gaussian"):
                 kw = mode_kwargs(mode, table)
                 r = S.simulate(mode, 10_000, 41, hist_bins=10, want_finals=True, **kw)
@@ -201,7 +202,20 @@ def test_ilp_variants_agree(S, table):
                 else:
                     base[mode] = r
     finally:
-        os.environ.pop("SMMC_ILP", None)
+        S.set_variant()
+
+
+def test_environment_does_not_select_kernels(S, table, monkeypatch):
+    """round-1 development knobs (SMMC_ILP / SMMC_WARPS / SMMC_REDUCE) are gone: the library never reads the environment"""
+    base = S.plan_launch("gaussian", 148 * 27 * 256 + 300, 12)
+    for k, v in (("SMMC_ILP", "2"), ("SMMC_WARPS", "20"), ("SMMC_REDUCE", "ldg")):
+        monkeypatch.setenv(k, v)
+    assert S.plan_launch("gaussian", 148 * 27 * 256 + 300, 12) == base
+    try:
+        S.set_variant("warps", 20)
+        assert S.plan_launch("gaussian", 148 * 27 * 256 + 300, 12)[1] == 20 * 32
+    finally:
+        S.set_variant()
 
 
 def test_histogram_range_target_and_seed(S, O, table):
@@ -261,16 +275,15 @@ def test_reduce_mean_device_pointer(S):
     rng = np.random.default_rng(5)
     h = (rng.standard_normal(3_000_003) * 1000.0 + 5000.0).astype(np.float32)
     d = torch.from_numpy(h).cuda()
-    import os
     try:
-        for kernel in ("ldg", "tma"):  # plain streaming loads / the TMA-pipelined kernel (forced here; by size otherwise)
-            os.environ["SMMC_REDUCE"] = kernel
+        for kernel in (1, 2):  # plain streaming loads / the TMA-pipelined kernel (forced here; by size otherwise)
+            S.set_variant("reduce", kernel)
             for off, n in ((0, h.size), (1, h.size - 1), (2, 1), (3, 4097), (5, 2_000_000), (0, 8192 * 296 + 5), (3, 8192 * 300 + 1)):
                 got, ms = S.reduce_mean_device(d.data_ptr() + 4 * off, n)
                 assert got == np.float32(h[off:off + n].astype(np.float64).mean()), (kernel, off, n)
                 assert ms > 0.0
     finally:
-        os.environ.pop("SMMC_REDUCE", None)
+        S.set_variant()
     big = torch.full((1 << 28,), 1.5, dtype=torch.float32, device="cuda")  # 1 GiB: larger than L2
     got, ms = S.reduce_mean_device(big.data_ptr(), big.numel(), stream=torch.cuda.current_stream().cuda_stream)
     assert got == 1.5
