@@ -137,6 +137,43 @@ smmc_status smmc_run(const smmc_config *cfg, smmc_result *out);
  * 0..n_gpus-1 and merges the partial statistics on the host.  Results are identical to a 1-GPU run of the same
  * config (histogram / counts bit-identical; mean/M2 to fp64 rounding). Host pointers only. */
 smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out);
+/* (statistics-only runs of smmc_run_multi merge on the DEVICES: one communicator per device from ncclCommInitAll, one
+ * grouped ncclAllReduce, one 864-byte download from device 0; runs that return all finals stream them through the host
+ * anyway and sum the per-chunk vectors there.) */
+
+/* ---- one rank per GPU: the collective behind the C ABI ---------------------------------------------------------
+ * The reference drives all GPUs from one host thread and re-runs the SAME paths on every device
+ * (src/simulations.cu:576-655, :621-622).  Here a job of one process (or thread) per GPU shards ONE global run by RNG
+ * offset and merges the O(KB) statistics vector with a single ncclAllReduce(ncclFloat64, ncclSum) enqueued on the
+ * same stream as the kernel: count / below / S1 / S2 / histogram are all sum-reducible and the integer fields are
+ * exact in fp64, so the merged histogram and counts are bit-identical for every number of ranks.  No per-path data
+ * ever crosses NVLink.  NCCL is bound at run time (dlopen of libnccl.so.2): when it is absent these entry points fail
+ * with SMMC_ERR_UNSUPPORTED -- there is no host-side stand-in. */
+typedef struct smmc_comm smmc_comm;     /* opaque: an ncclComm_t plus the rank's device */
+#define SMMC_COMM_ID_BYTES 128          /* = NCCL_UNIQUE_ID_BYTES */
+/* rank 0: ncclGetUniqueId into id[SMMC_COMM_ID_BYTES]; distribute the bytes to the other ranks by any means. */
+smmc_status smmc_comm_unique_id(void *id);
+/* every rank: ncclCommInitRank on `device` (collective call). */
+smmc_status smmc_comm_init_rank(const void *id, int32_t n_ranks, int32_t rank, int32_t device, smmc_comm **comm);
+/* wraps a communicator the application already owns (ncclComm_t as void*); not destroyed by smmc_comm_destroy. */
+smmc_status smmc_comm_adopt(void *nccl_comm, int32_t device, smmc_comm **comm);
+smmc_status smmc_comm_destroy(smmc_comm *comm);
+smmc_status smmc_comm_info(const smmc_comm *comm, int32_t *n_ranks, int32_t *rank, int32_t *device, int32_t *nccl_version);
+/* This rank's part of the GLOBAL run `cfg` (cfg->n_simulations, cfg->stream_offset describe the whole run; cfg->device
+ * is ignored in favour of the communicator's device): rank r simulates the r-th of n_ranks contiguous ranges of whole
+ * 256-path blocks (the partition of smmc_run_multi; smmc_rank_range reports it), then
+ *   kernel -> ncclAllReduce(statistics vector) on the same stream -> (unless NO_SYNC) download + finalize,
+ * so count / mean / m2 / below_count / hist in `out` describe the GLOBAL run on every rank.  finals / block_means /
+ * block_vars, when requested, cover this rank's own range only (they never travel).  Flags as for smmc_run: host
+ * pointers (blocking) by default; DEVICE_POINTERS [+ NO_SYNC] runs on cfg->stream, fully asynchronously with NO_SYNC
+ * (read the merged vector from out->stats_dev).  Collective: every rank must call it. */
+smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *comm);
+/* first path (relative to cfg->stream_offset) and number of paths of rank `rank` of `n_ranks` for a run of n paths */
+smmc_status smmc_rank_range(int64_t n_simulations, int32_t n_ranks, int32_t rank, int64_t *first, int64_t *count);
+/* Exact order statistics of the GLOBAL run, one rank per GPU: every rank replays its own range; the digit histograms
+ * (exact integers) are merged by ncclAllReduce(ncclUint64, ncclSum) per pass.  values[t] on every rank. Host pointers. */
+smmc_status smmc_quantiles_rank(const smmc_config *cfg, smmc_comm *comm, int32_t n_targets, const uint64_t *ranks,
+                                float *values, float *device_ms);
 
 /* CUDA-event durations (ms) of the simulation kernel of the most recent launches on `device` (oldest first, at
  * most 256 are kept), whichever entry point or flags enqueued them.  Blocks until those kernels have finished.
@@ -264,7 +301,7 @@ smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, i
  * this to prove it).  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
  * (reduce_mean kernel: 1 = streaming loads, 2 = TMA ring), "gauss_tbl" (GAUSSIAN: 4-bit mask of the Box-Muller pairs of a
  * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0|1), "sobol_unroll",
- * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch).  value < 0 (or 0 where 0 is not a choice)
+ * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch), "finals_threads" (its host copy-out threads).  value < 0 (or 0 where 0 is not a choice)
  * restores the default; key NULL resets everything.  Process-wide; nothing in the library reads the environment. */
 smmc_status smmc_debug_set_variant(const char *key, int32_t value);
 

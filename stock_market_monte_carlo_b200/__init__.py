@@ -7,7 +7,7 @@ from .simulations import (AtomicLong, FloatVector, Result, debug_draws, debug_ph
                           mc_simulations_gpu, mc_simulations_gpu_reduceBlock, reduce_mean_gpu, reduce_mean_device, simulate,
                           simulate_device, stats_len, vector_add, vector_add_gpu, vector_add_device, quantiles, quartile_ranks,
                           update_quartiles, simulate_with_quantiles, SelectState, trajectories, mc_simulations_keepdata, read_historical_returns,
-                          write_data_file, plan_launch, make_config, set_variant)
+                          write_data_file, plan_launch, make_config, set_variant, Comm, rank_range)
 from .data import synthetic_sp500_table
 
 __all__ = [
@@ -15,5 +15,5 @@ __all__ = [
     "finalize_stats", "kernel_times", "stats_len", "mc_simulations_gpu", "mc_simulations_gpu_reduceBlock", "reduce_mean_gpu", "reduce_mean_device",
     "vector_add", "vector_add_gpu", "vector_add_device", "debug_draws", "debug_philox", "synthetic_sp500_table", "quantiles", "quartile_ranks",
     "update_quartiles", "simulate_with_quantiles", "SelectState", "trajectories", "mc_simulations_keepdata", "read_historical_returns", "write_data_file",
-    "plan_launch", "make_config", "set_variant",
+    "plan_launch", "make_config", "set_variant", "Comm", "rank_range",
 ]

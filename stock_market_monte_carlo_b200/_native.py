@@ -113,7 +113,10 @@ C_ABI_SYMBOLS = [
     "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
+    "smmc_comm_unique_id", "smmc_comm_init_rank", "smmc_comm_adopt", "smmc_comm_destroy", "smmc_comm_info", "smmc_run_rank",
+    "smmc_rank_range", "smmc_quantiles_rank",
 ]
+COMM_ID_BYTES = 128
 
 _lib = None
 
@@ -176,6 +179,22 @@ def load():
     lib.smmc_write_data_file.restype = C.c_int
     lib.smmc_plan_launch.argtypes = [P(SmmcConfig), C.c_int32, C.c_int32, C.c_uint64, P(SmmcPlan)]
     lib.smmc_plan_launch.restype = C.c_int
+    lib.smmc_comm_unique_id.argtypes = [C.c_void_p]
+    lib.smmc_comm_unique_id.restype = C.c_int
+    lib.smmc_comm_init_rank.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, P(C.c_void_p)]
+    lib.smmc_comm_init_rank.restype = C.c_int
+    lib.smmc_comm_adopt.argtypes = [C.c_void_p, C.c_int32, P(C.c_void_p)]
+    lib.smmc_comm_adopt.restype = C.c_int
+    lib.smmc_comm_destroy.argtypes = [C.c_void_p]
+    lib.smmc_comm_destroy.restype = C.c_int
+    lib.smmc_comm_info.argtypes = [C.c_void_p, P(C.c_int32), P(C.c_int32), P(C.c_int32), P(C.c_int32)]
+    lib.smmc_comm_info.restype = C.c_int
+    lib.smmc_run_rank.argtypes = [P(SmmcConfig), P(SmmcResult), C.c_void_p]
+    lib.smmc_run_rank.restype = C.c_int
+    lib.smmc_rank_range.argtypes = [C.c_int64, C.c_int32, C.c_int32, P(C.c_int64), P(C.c_int64)]
+    lib.smmc_rank_range.restype = C.c_int
+    lib.smmc_quantiles_rank.argtypes = [P(SmmcConfig), C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, P(C.c_float)]
+    lib.smmc_quantiles_rank.restype = C.c_int
     lib.smmc_last_error.restype = C.c_char_p
     lib.smmc_version.restype = C.c_char_p
     lib.smmc_device_count.restype = C.c_int32

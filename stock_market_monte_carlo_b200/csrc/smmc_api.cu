@@ -9,12 +9,25 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#ifdef __linux__
+#include <sys/mman.h>
+#endif
+#include <atomic>
 #include <mutex>
 #include <thread>
 #include <vector>
 
 #include "../../include/smmc.h"
 #include "smmc_kernels.cuh"
+#include "smmc_nccl.h"
+
+// opaque in include/smmc.h
+struct smmc_comm {
+  smmc::NcclComm nccl = nullptr;
+  int n_ranks = 1, rank = 0, device = 0;
+  bool owned = false;
+};
 
 namespace smmc {
 const uint32_t *sobol_table();  // smmc_sobol_data.cpp
@@ -99,6 +112,14 @@ struct DevBuf {
 
 constexpr int kEventRing = 256;
 
+// everything that determines the paths of a select replay (validity key of the candidate buffer)
+struct CandFingerprint {
+  int32_t mode, periods, n_returns, rounds, tbl_mask, pad;
+  int64_t n;
+  uint64_t seed, offset, table, schedule;
+  float v0, gm, gs, wfixed, wpct, pad2;
+};
+
 struct Context {
   int device = -1;
   bool ready = false;
@@ -131,6 +152,23 @@ struct Context {
   cudaEvent_t last_use = nullptr;
   cudaStream_t last_stream = nullptr;
   bool has_last_use = false;
+  // candidate keys of the last second select replay (select_pass_enqueue)
+  DevBuf cand_keys, cand_cursor;
+  bool cand_valid = false;
+  CandFingerprint cand_fp;
+  int cand_groups = 0;
+  uint32_t cand_prefix[SMMC_SELECT_MAX_TARGETS] = {};
+  unsigned long long cand_capacity = 0;
+  // pipelined all-finals path (run_finals_pipelined): second stream for the downloads, pinned staging ring, chunk events
+  cudaStream_t copy_stream = nullptr;
+  static constexpr int kStageSlots = 3;   // pinned staging slots (host side of the D2H copies)
+  static constexpr int kChunkDepth = 8;   // kernel chunks enqueued ahead = device-side ring of chunk buffers
+  void *stage[kStageSlots] = {};
+  size_t stage_cap = 0;
+  DevBuf chunk_stats;                     // [kChunkDepth][stats_len] doubles
+  double *chunk_stats_host = nullptr;     // pinned, same shape
+  size_t chunk_stats_host_cap = 0;
+  cudaEvent_t kdone[kChunkDepth] = {}, cdone[kChunkDepth] = {}, sdone[kChunkDepth] = {};
   double *stats_host = nullptr;  // pinned
   size_t stats_host_cap = 0;
   std::mutex mu;
@@ -181,6 +219,12 @@ smmc_status get_context(int device, Context **out) {
     CU(cudaEventCreate(&c.red1));
     CU(cudaEventCreateWithFlags(&c.last_use, cudaEventDisableTiming));
     c.has_last_use = false;
+    CU(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < Context::kChunkDepth; i++) {
+      CU(cudaEventCreateWithFlags(&c.kdone[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&c.cdone[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&c.sdone[i], cudaEventDisableTiming));
+    }
     c.device = device;
     c.n_sms = sms;
     c.smem_optin = (size_t)optin;
@@ -555,12 +599,19 @@ struct DeviceOutputs {
   bool want_finals = false, want_bmeans = false, want_bvars = false;  // host-pointer runs: allocate in the context cache
 };
 
+// how a launch deviates from "one call = one launch with the caller's buffers"
+struct EnqueueOpts {
+  const DeviceOutputs *dout = nullptr;  // explicit device outputs (chunked / pipelined runs)
+  bool reuse_table = false;             // the scaled table of the previous launch on this context is still valid: skip upload + prep
+};
+
 // Enqueue one shard [cfg->stream_offset, +N) on cfg->device.  Caller holds ctx->mu.
 smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx, Pending *pd,
-                    const SelectPass *sel = nullptr, const DeviceOutputs *dout = nullptr, cudaStream_t stream_override = nullptr) {
+                    const SelectPass *sel = nullptr, const EnqueueOpts &opts = EnqueueOpts()) {
   CU(cudaSetDevice(ctx->device));
   const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
-  cudaStream_t st = stream_override ? stream_override : (devp ? (cudaStream_t)cfg->stream : ctx->stream);
+  const DeviceOutputs *dout = opts.dout;
+  cudaStream_t st = devp ? (cudaStream_t)cfg->stream : ctx->stream;
   const int64_t N = cfg->n_simulations;
   const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
   const int bins = cfg->hist_bins;
@@ -593,24 +644,26 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   // ---- table: upload (host pointers) and expand to the scaled, bank-private replicated layout
   if (is_bootstrap(cfg->mode)) {
     const int n = cfg->n_returns;
-    const float *src = cfg->returns;
-    if (!devp) {
-      CU(ctx->returns.reserve((size_t)n * 4));
-      CU(cudaMemcpyAsync(ctx->returns.p, cfg->returns, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-      src = (const float *)ctx->returns.p;
-    }
-    if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP) {  // quasi-random draws sample the SORTED table (quantile function)
-      CU(ctx->sorted.reserve((size_t)n * 4));
-      smmc::launch_sort_table(src, n, (float *)ctx->sorted.p, st);
+    const uint32_t tbl_bytes = (uint32_t)((((size_t)(n + 1) * li.rep * 4) + 15) & ~(size_t)15);
+    if (!opts.reuse_table) {
+      const float *src = cfg->returns;
+      if (!devp) {
+        CU(ctx->returns.reserve((size_t)n * 4));
+        CU(cudaMemcpyAsync(ctx->returns.p, cfg->returns, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        src = (const float *)ctx->returns.p;
+      }
+      if (cfg->mode == SMMC_MODE_SOBOL_BOOTSTRAP) {  // quasi-random draws sample the SORTED table (quantile function)
+        CU(ctx->sorted.reserve((size_t)n * 4));
+        smmc::launch_sort_table(src, n, (float *)ctx->sorted.p, st);
+        CU(cudaGetLastError());
+        pd->launches++;
+        src = (const float *)ctx->sorted.p;
+      }
+      CU(ctx->tbl.reserve(tbl_bytes));
+      smmc::launch_prep_table(src, n, li.rep, (float *)ctx->tbl.p, tbl_bytes / 4, st);
       CU(cudaGetLastError());
       pd->launches++;
-      src = (const float *)ctx->sorted.p;
     }
-    const uint32_t tbl_bytes = (uint32_t)((((size_t)(n + 1) * li.rep * 4) + 15) & ~(size_t)15);
-    CU(ctx->tbl.reserve(tbl_bytes));
-    smmc::launch_prep_table(src, n, li.rep, (float *)ctx->tbl.p, tbl_bytes / 4, st);
-    CU(cudaGetLastError());
-    pd->launches++;
     p.tbl_rep = (const float *)ctx->tbl.p;
     p.tbl_bytes = tbl_bytes;
     p.rep4 = (uint32_t)li.rep * 4u;
@@ -758,7 +811,8 @@ void prefault_output(void *ptr, size_t bytes) {
   for (auto &x : th) x.join();
 }
 
-smmc_status collect(const Pending &pd, const smmc_result *out, double *stats_host, float *device_ms) {
+// Issue the downloads of a shard's results into `out` (host pointers) and of its statistics vector (pinned).
+smmc_status collect_issue(const Pending &pd, const smmc_result *out) {
   Context *ctx = pd.ctx;
   CU(cudaSetDevice(ctx->device));
   if (ctx->stats_host_cap < (size_t)pd.stats_len) {
@@ -777,11 +831,555 @@ smmc_status collect(const Pending &pd, const smmc_result *out, double *stats_hos
     if (out->block_vars && pd.nb > 0)
       CU(cudaMemcpyAsync(out->block_vars, pd.bvars_dev, (size_t)pd.nb * 4, cudaMemcpyDeviceToHost, pd.stream));
   }
+  return SMMC_OK;
+}
+
+smmc_status collect_wait(const Pending &pd, double *stats_host, float *device_ms) {
+  Context *ctx = pd.ctx;
+  CU(cudaSetDevice(ctx->device));
   CU(cudaStreamSynchronize(pd.stream));
   memcpy(stats_host, ctx->stats_host, (size_t)pd.stats_len * sizeof(double));
   float ms = 0.0f;
   CU(cudaEventElapsedTime(&ms, ctx->ev0[pd.ev_slot], ctx->ev1[pd.ev_slot]));
   *device_ms = ms;
+  return SMMC_OK;
+}
+
+smmc_status collect(const Pending &pd, const smmc_result *out, double *stats_host, float *device_ms) {
+  smmc_status st = collect_issue(pd, out);
+  if (st != SMMC_OK) return st;
+  return collect_wait(pd, stats_host, device_ms);
+}
+
+// ---- shards: one contiguous, 256-aligned path range of a host-pointer run on one device ---------------------------------
+struct Shard {
+  Context *ctx = nullptr;
+  smmc_config cfg;              // stream_offset / n_simulations / device of this shard
+  float *finals = nullptr;      // host destinations (nullable)
+  float *bmeans = nullptr, *bvars = nullptr;
+};
+
+// Splits [0, N) of cfg over the given devices in whole 256-path blocks (the partition smmc_run_multi documents).
+void make_shards(const smmc_config *cfg, const smmc_result *out, const std::vector<Context *> &ctxs, std::vector<Shard> *shards) {
+  const int n_gpus = (int)ctxs.size();
+  const int64_t N = cfg->n_simulations;
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int64_t per = (nb + n_gpus - 1) / n_gpus;  // logical blocks per device
+  shards->assign((size_t)n_gpus, Shard());
+  for (int g = 0; g < n_gpus; g++) {
+    int64_t b0 = per * g, b1 = per * (g + 1);
+    if (b0 > nb) b0 = nb;
+    if (b1 > nb) b1 = nb;
+    int64_t p0 = b0 * SMMC_BLOCK, p1 = b1 * SMMC_BLOCK;
+    if (p1 > N) p1 = N;
+    if (p0 >= p1) p0 = p1 = 0;  // an empty shard keeps a block-aligned offset
+    Shard &sh = (*shards)[(size_t)g];
+    sh.ctx = ctxs[(size_t)g];
+    sh.cfg = *cfg;
+    sh.cfg.device = ctxs[(size_t)g]->device;
+    sh.cfg.stream_offset = cfg->stream_offset + (uint64_t)p0;
+    sh.cfg.n_simulations = p1 - p0;
+    sh.finals = out->finals ? out->finals + p0 : nullptr;
+    sh.bmeans = out->block_means ? out->block_means + b0 : nullptr;
+    sh.bvars = out->block_vars ? out->block_vars + b0 : nullptr;
+  }
+}
+
+// ---- the all-finals path, pipelined ------------------------------------------------------------------------------------
+// The reference's primary entry point (mc_simulations_gpu, src/simulations.cu:576-655) returns every final value: 4 bytes
+// per path over PCIe into pageable caller memory, which costs more than the simulation (10^8 x 360: 14 ms of kernel).
+// Each shard is cut into chunks of whole launch waves; the path id is the RNG offset, so a chunk is just a launch with
+// another stream_offset and every value is bit-identical to the monolithic launch.  Per device:
+//   compute stream: kernel(c) -> stats(c) D2H (864 B, pinned)           [kChunkDepth chunks ahead, device-side ring]
+//   copy stream:    wait kernel(c) -> finals(c) D2H into a pinned staging slot             [kStageSlots slots]
+//   host workers:   wait copy(c) -> memcpy slot -> caller's buffer (first touch of its pages included), slot freed
+// so the kernel of chunk c+1.. overlaps the download of chunk c and the host copy of chunk c-1.
+struct Chunk {
+  int shard = 0;
+  int64_t p0 = 0, n = 0;  // path range relative to the shard
+  int index = 0;          // chunk number within the shard
+};
+
+int64_t pipeline_chunk_paths(int64_t n_shard, int n_sms, int forced_chunks) {
+  const int64_t wave = (int64_t)n_sms * smmc::kWarps * SMMC_BLOCK;  // one full wave of 256-path blocks
+  const int want = forced_chunks > 1 ? forced_chunks : 16;
+  int64_t c = (n_shard + want - 1) / want;
+  c = (c + wave - 1) / wave * wave;                        // whole waves: only the last chunk has a ragged tail
+  const int64_t cmax = ((int64_t)16 << 20) / wave * wave;  // <= 64 MB of finals per staging slot
+  if (c > cmax && forced_chunks <= 1) c = cmax > 0 ? cmax : wave;
+  if (c < wave) c = wave;
+  return c;
+}
+
+constexpr int64_t kPipelineMinPaths = (int64_t)4 << 20;  // below 16 MB of finals the monolithic path is as fast
+
+// A large, freshly allocated destination buffer is first touched by the download threads: ask for transparent huge pages
+// on its 2 MB-aligned interior (a hint: no effect where THP is off), 512 times fewer page faults than 4 KB pages.
+void hint_huge_pages(void *ptr, size_t bytes) {
+#ifdef __linux__
+  constexpr uintptr_t kHuge = (uintptr_t)2 << 20;
+  if (!ptr || bytes < 4 * kHuge) return;
+  const uintptr_t a = (reinterpret_cast<uintptr_t>(ptr) + kHuge - 1) & ~(kHuge - 1);
+  const uintptr_t b = (reinterpret_cast<uintptr_t>(ptr) + bytes) & ~(kHuge - 1);
+  if (b > a) madvise(reinterpret_cast<void *>(a), b - a, MADV_HUGEPAGE);
+#else
+  (void)ptr;
+  (void)bytes;
+#endif
+}
+
+// Runs `shards` (host pointers, finals requested) through the chunk pipeline.  total: summed statistics vector (shard, chunk
+// order: deterministic).  Caller holds every shard's ctx->mu.
+smmc_status run_finals_pipelined(std::vector<Shard> &shards, const smmc_config *cfg, std::vector<double> *total, float *device_ms,
+                                 int *launches) {
+  const int slen = smmc_stats_len(cfg->hist_bins);
+  const smmc::Variant variant = current_variant();
+  const int S = (int)shards.size();
+  constexpr int kDepth = Context::kChunkDepth, kSlots = Context::kStageSlots;
+
+  // ---- chunk lists, interleaved over the shards so that every device makes progress
+  std::vector<std::vector<Chunk>> per((size_t)S);
+  std::vector<int64_t> csize((size_t)S, 0);
+  size_t most = 0;
+  for (int s = 0; s < S; s++) {
+    const int64_t n = shards[(size_t)s].cfg.n_simulations;
+    csize[(size_t)s] = pipeline_chunk_paths(n, shards[(size_t)s].ctx->n_sms, variant.finals_chunks);
+    for (int64_t p0 = 0; p0 < n; p0 += csize[(size_t)s]) {
+      Chunk c;
+      c.shard = s;
+      c.p0 = p0;
+      c.n = std::min(csize[(size_t)s], n - p0);
+      c.index = (int)per[(size_t)s].size();
+      per[(size_t)s].push_back(c);
+    }
+    most = std::max(most, per[(size_t)s].size());
+  }
+  std::vector<Chunk> order;
+  for (size_t i = 0; i < most; i++)
+    for (int s = 0; s < S; s++)
+      if (i < per[(size_t)s].size()) order.push_back(per[(size_t)s][i]);
+  const int G = (int)order.size();
+
+  // ---- per-device resources (grow-only, cached in the context)
+  std::vector<std::vector<double *>> stats_host((size_t)S);
+  for (int s = 0; s < S; s++) {
+    Shard &sh = shards[(size_t)s];
+    Context *ctx = sh.ctx;
+    const size_t nch = per[(size_t)s].size();
+    if (nch == 0) continue;
+    CU(cudaSetDevice(ctx->device));
+    const size_t cbytes = (size_t)csize[(size_t)s] * 4;
+    CU(ctx->finals.reserve(cbytes * kDepth));
+    if (ctx->stage_cap < cbytes) {
+      for (int i = 0; i < kSlots; i++) {
+        if (ctx->stage[i]) cudaFreeHost(ctx->stage[i]);
+        ctx->stage[i] = nullptr;
+      }
+      ctx->stage_cap = 0;
+      for (int i = 0; i < kSlots; i++) CU(cudaMallocHost(&ctx->stage[i], cbytes));
+      ctx->stage_cap = cbytes;
+    }
+    CU(ctx->chunk_stats.reserve((size_t)kDepth * slen * sizeof(double)));
+    const size_t need = nch * (size_t)slen;
+    if (ctx->chunk_stats_host_cap < need) {
+      if (ctx->chunk_stats_host) cudaFreeHost(ctx->chunk_stats_host);
+      ctx->chunk_stats_host = nullptr;
+      ctx->chunk_stats_host_cap = 0;
+      CU(cudaMallocHost(&ctx->chunk_stats_host, need * sizeof(double)));
+      ctx->chunk_stats_host_cap = need;
+    }
+    const int64_t nb = (sh.cfg.n_simulations + SMMC_BLOCK - 1) / SMMC_BLOCK;
+    if (sh.bmeans) CU(ctx->bmeans.reserve((size_t)nb * 4));
+    if (sh.bvars) CU(ctx->bvars.reserve((size_t)nb * 4));
+  }
+
+  // ---- host workers: staging slot -> caller's buffer
+  unsigned hw = std::thread::hardware_concurrency();
+  int T = hw >= 16 ? 8 : (hw >= 4 ? (int)hw / 2 : 1);
+  if (variant.finals_threads > 0) T = variant.finals_threads;
+  for (const Shard &sh : shards) hint_huge_pages(sh.finals, (size_t)sh.cfg.n_simulations * 4);
+  std::vector<std::atomic<int>> issued((size_t)G), out_done((size_t)G);
+  for (int g = 0; g < G; g++) {
+    issued[(size_t)g].store(0);
+    out_done[(size_t)g].store(0);
+  }
+  std::vector<cudaEvent_t> copied((size_t)G, nullptr);
+  std::atomic<int> abort_flag(0);
+  auto worker = [&](int t) {
+    for (int g = 0; g < G; g++) {
+      while (!issued[(size_t)g].load(std::memory_order_acquire)) {
+        if (abort_flag.load(std::memory_order_relaxed)) return;
+        std::this_thread::yield();
+      }
+      if (cudaEventSynchronize(copied[(size_t)g]) != cudaSuccess) {
+        abort_flag.store(1);
+        return;
+      }
+      const Chunk &c = order[(size_t)g];
+      const Shard &sh = shards[(size_t)c.shard];
+      const size_t bytes = (size_t)c.n * 4, lo = bytes * (size_t)t / (size_t)T & ~(size_t)63, hi = (t == T - 1) ? bytes : (bytes * (size_t)(t + 1) / (size_t)T & ~(size_t)63);
+      if (hi > lo)
+        memcpy(reinterpret_cast<char *>(sh.finals + c.p0) + lo, static_cast<const char *>(sh.ctx->stage[c.index % kSlots]) + lo, hi - lo);
+      out_done[(size_t)g].fetch_add(1, std::memory_order_release);
+    }
+  };
+  std::vector<std::thread> threads;
+  for (int t = 0; t < T; t++) threads.emplace_back(worker, t);
+  auto stop_workers = [&]() {
+    abort_flag.store(1);
+    for (auto &th : threads) th.join();
+  };
+
+  // ---- issue loop
+  std::vector<int> next_kernel((size_t)S, 0);
+  std::vector<int> gidx_of((size_t)S * most + 1, -1);  // (shard, chunk index) -> position in `order`
+  for (int g = 0; g < G; g++) gidx_of[(size_t)order[(size_t)g].shard * most + (size_t)order[(size_t)g].index] = g;
+  smmc_status rc = SMMC_OK;
+  *launches = 0;
+  auto enqueue_kernel = [&](int s, int i) -> smmc_status {
+    Shard &sh = shards[(size_t)s];
+    Context *ctx = sh.ctx;
+    const Chunk &c = per[(size_t)s][(size_t)i];
+    const int slot = i % kDepth;
+    CU(cudaSetDevice(ctx->device));
+    if (i == 0) CU(cudaEventRecord(ctx->red0, ctx->stream));
+    if (i >= kDepth) CU(cudaStreamWaitEvent(ctx->stream, ctx->cdone[slot], 0));  // ring slot: its previous chunk has been downloaded
+    smmc_config cc = sh.cfg;
+    cc.stream_offset = sh.cfg.stream_offset + (uint64_t)c.p0;
+    cc.n_simulations = c.n;
+    DeviceOutputs d;
+    d.finals = (float *)ctx->finals.p + (size_t)slot * (size_t)csize[(size_t)s];
+    d.bmeans = sh.bmeans ? (float *)ctx->bmeans.p + c.p0 / SMMC_BLOCK : nullptr;
+    d.bvars = sh.bvars ? (float *)ctx->bvars.p + c.p0 / SMMC_BLOCK : nullptr;
+    d.stats = (double *)ctx->chunk_stats.p + (size_t)slot * slen;
+    EnqueueOpts o;
+    o.dout = &d;
+    o.reuse_table = i > 0;
+    smmc_result dummy;
+    memset(&dummy, 0, sizeof dummy);
+    Pending pd;
+    smmc_status st = enqueue(&cc, &dummy, ctx, &pd, nullptr, o);
+    if (st != SMMC_OK) return st;
+    *launches += pd.launches;
+    CU(cudaEventRecord(ctx->kdone[slot], ctx->stream));
+    CU(cudaMemcpyAsync(ctx->chunk_stats_host + (size_t)i * slen, d.stats, (size_t)slen * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (i + 1 == (int)per[(size_t)s].size()) CU(cudaEventRecord(ctx->red1, ctx->stream));
+    return SMMC_OK;
+  };
+  for (int g = 0; g < G && rc == SMMC_OK; g++) {
+    const Chunk &c = order[(size_t)g];
+    const int s = c.shard, i = c.index;
+    Context *ctx = shards[(size_t)s].ctx;
+    const int nch = (int)per[(size_t)s].size();
+    while (rc == SMMC_OK && next_kernel[(size_t)s] < nch && next_kernel[(size_t)s] < i + kDepth) {
+      rc = enqueue_kernel(s, next_kernel[(size_t)s]);
+      next_kernel[(size_t)s]++;
+    }
+    if (rc != SMMC_OK) break;
+    if (i >= kSlots) {  // the staging slot is free once every worker has copied chunk i - kSlots out of it
+      const int gp = gidx_of[(size_t)s * most + (size_t)(i - kSlots)];
+      while (out_done[(size_t)gp].load(std::memory_order_acquire) < T) {
+        if (abort_flag.load()) break;
+        std::this_thread::yield();
+      }
+    }
+    cudaError_t e = cudaSetDevice(ctx->device);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, ctx->kdone[i % kDepth], 0);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(ctx->stage[i % kSlots], (float *)ctx->finals.p + (size_t)(i % kDepth) * (size_t)csize[(size_t)s], (size_t)c.n * 4,
+                          cudaMemcpyDeviceToHost, ctx->copy_stream);
+    if (e == cudaSuccess) e = cudaEventRecord(ctx->cdone[i % kDepth], ctx->copy_stream);
+    if (e != cudaSuccess || abort_flag.load()) {
+      rc = fail(SMMC_ERR_CUDA, "finals pipeline: %s", cudaGetErrorString(e));
+      break;
+    }
+    copied[(size_t)g] = ctx->cdone[i % kDepth];
+    issued[(size_t)g].store(1, std::memory_order_release);
+  }
+  if (rc != SMMC_OK) {
+    stop_workers();
+    for (int s = 0; s < S; s++) {
+      cudaSetDevice(shards[(size_t)s].ctx->device);
+      cudaStreamSynchronize(shards[(size_t)s].ctx->stream);
+      cudaStreamSynchronize(shards[(size_t)s].ctx->copy_stream);
+    }
+    return rc;
+  }
+  for (auto &th : threads) th.join();
+  if (abort_flag.load()) return fail(SMMC_ERR_CUDA, "finals pipeline: a download failed");
+
+  // ---- block partials, statistics, timing
+  total->assign((size_t)slen, 0.0);
+  *device_ms = 0.0f;
+  for (int s = 0; s < S; s++) {
+    Shard &sh = shards[(size_t)s];
+    Context *ctx = sh.ctx;
+    const int nch = (int)per[(size_t)s].size();
+    if (nch == 0) continue;
+    CU(cudaSetDevice(ctx->device));
+    const int64_t nb = (sh.cfg.n_simulations + SMMC_BLOCK - 1) / SMMC_BLOCK;
+    if (sh.bmeans) CU(cudaMemcpyAsync(sh.bmeans, ctx->bmeans.p, (size_t)nb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sh.bvars) CU(cudaMemcpyAsync(sh.bvars, ctx->bvars.p, (size_t)nb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_stream));
+    for (int i = 0; i < nch; i++)
+      for (int k = 0; k < slen; k++) (*total)[(size_t)k] += ctx->chunk_stats_host[(size_t)i * slen + k];
+    float ms = 0.0f;
+    CU(cudaEventElapsedTime(&ms, ctx->red0, ctx->red1));
+    if (ms > *device_ms) *device_ms = ms;
+  }
+  return SMMC_OK;
+}
+
+smmc_status multi_comms(int n_gpus, const std::vector<smmc::NcclComm> **out);
+smmc_status need_nccl(const smmc::NcclApi **api);
+
+// Host-pointer run of cfg over the devices of `ctxs` (1 = smmc_run, more = smmc_run_multi); caller holds every ctx->mu.
+smmc_status run_host(const smmc_config *cfg, const std::vector<Context *> &ctxs, smmc_result *out) {
+  std::vector<Shard> shards;
+  make_shards(cfg, out, ctxs, &shards);
+  const int slen = smmc_stats_len(cfg->hist_bins);
+  std::vector<double> total((size_t)slen, 0.0);
+  float ms_max = 0.0f;
+  int launches = 0;
+  const smmc::Variant variant = current_variant();
+  int64_t biggest = 0;
+  for (const Shard &sh : shards) biggest = std::max(biggest, (int64_t)sh.cfg.n_simulations);
+  if (out->finals && variant.finals_chunks != 1 && (biggest >= kPipelineMinPaths || variant.finals_chunks > 1)) {
+    smmc_status st = run_finals_pipelined(shards, cfg, &total, &ms_max, &launches);
+    if (st != SMMC_OK) return st;
+  } else {
+    // every device's launch is enqueued before anything waits, and every download is issued before any is awaited
+    std::vector<Pending> pend(shards.size());
+    std::vector<smmc_result> outs(shards.size(), *out);
+    smmc_status rc = SMMC_OK;
+    size_t launched = 0;
+    for (size_t g = 0; g < shards.size() && rc == SMMC_OK; g++) {
+      outs[g].finals = shards[g].finals;
+      outs[g].block_means = shards[g].bmeans;
+      outs[g].block_vars = shards[g].bvars;
+      rc = enqueue(&shards[g].cfg, &outs[g], shards[g].ctx, &pend[g]);
+      if (rc == SMMC_OK) launched++;
+    }
+    // several devices: ONE grouped ncclAllReduce of the statistics vectors, in place, each on its kernel's stream -- the
+    // merge happens on the devices (NVLink), and only device 0's 864 bytes are read back
+    const bool merged_on_device = shards.size() > 1 && rc == SMMC_OK;
+    if (merged_on_device) {
+      const std::vector<smmc::NcclComm> *comms = nullptr;
+      const smmc::NcclApi *api = nullptr;
+      rc = need_nccl(&api);
+      if (rc == SMMC_OK) rc = multi_comms((int)shards.size(), &comms);
+      if (rc == SMMC_OK) {
+        int r = api->GroupStart();
+        for (size_t g = 0; g < launched && r == 0; g++)
+          r = api->AllReduce(pend[g].stats_dev, pend[g].stats_dev, (size_t)slen, smmc::kNcclFloat64, smmc::kNcclSum, (*comms)[g], pend[g].stream);
+        const int r2 = api->GroupEnd();
+        if (r == 0) r = r2;
+        if (r != 0) rc = fail(SMMC_ERR_CUDA, "ncclAllReduce failed: %s", api->GetErrorString(r));
+      }
+    }
+    for (size_t g = 0; g < launched; g++) {
+      smmc_status s2 = collect_issue(pend[g], &outs[g]);
+      if (s2 != SMMC_OK && rc == SMMC_OK) rc = s2;
+    }
+    std::vector<double> part((size_t)slen);
+    for (size_t g = 0; g < launched; g++) {
+      float ms = 0.0f;
+      smmc_status s2 = collect_wait(pend[g], part.data(), &ms);
+      if (s2 != SMMC_OK && rc == SMMC_OK) rc = s2;
+      if (!merged_on_device || g == 0)
+        for (int i = 0; i < slen; i++) total[(size_t)i] += part[(size_t)i];
+      if (ms > ms_max) ms_max = ms;
+      launches += pend[g].launches;
+    }
+    if (rc != SMMC_OK) return rc;
+  }
+  out->device_ms = ms_max;
+  out->gpu_launches = launches;
+  return smmc_stats_finalize(total.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count, &out->mean,
+                             &out->m2, out->hist);
+}
+
+// ---- NCCL (bound at run time, smmc_nccl.h) -------------------------------------------------------------------------------
+#define NCCL_CALL(api, call)                                                                                            \
+  do {                                                                                                                  \
+    int r__ = (call);                                                                                                   \
+    if (r__ != 0) return fail(SMMC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, (api)->GetErrorString(r__), __FILE__, __LINE__); \
+  } while (0)
+
+smmc_status need_nccl(const smmc::NcclApi **api) {
+  *api = smmc::nccl_api();
+  if (!*api)
+    return fail(SMMC_ERR_UNSUPPORTED, "NCCL is not available (%s); the multi-GPU collective has no host-side stand-in", smmc::nccl_load_error());
+  return SMMC_OK;
+}
+
+// first block-aligned path and path count of shard `rank` of `n` (the partition of make_shards)
+void rank_range(int64_t N, int n, int rank, int64_t *first, int64_t *count) {
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int64_t per = (nb + n - 1) / n;
+  int64_t b0 = per * rank, b1 = per * (rank + 1);
+  if (b0 > nb) b0 = nb;
+  if (b1 > nb) b1 = nb;
+  int64_t p0 = b0 * SMMC_BLOCK, p1 = b1 * SMMC_BLOCK;
+  if (p1 > N) p1 = N;
+  if (p0 >= p1) p0 = p1 = 0;  // an empty shard keeps a block-aligned offset
+  *first = p0;
+  *count = p1 - p0;
+}
+
+// communicators of the single-process multi-GPU entry points (smmc_run_multi), one set per device count
+std::mutex g_multi_mu;
+std::vector<smmc::NcclComm> g_multi_comms[kMaxDevices + 1];
+
+smmc_status multi_comms(int n_gpus, const std::vector<smmc::NcclComm> **out) {
+  const smmc::NcclApi *api = nullptr;
+  smmc_status st = need_nccl(&api);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(g_multi_mu);
+  std::vector<smmc::NcclComm> &v = g_multi_comms[n_gpus];
+  if (v.empty()) {
+    std::vector<int> devs((size_t)n_gpus);
+    for (int g = 0; g < n_gpus; g++) devs[(size_t)g] = g;
+    std::vector<smmc::NcclComm> c((size_t)n_gpus, nullptr);
+    NCCL_CALL(api, api->CommInitAll(c.data(), n_gpus, devs.data()));
+    v = c;
+  }
+  *out = &v;
+  return SMMC_OK;
+}
+
+// ---- select passes: replay, or -- for the last 10 key bits -- a pass over the candidate keys of the previous replay --------
+// After the first pass fixes 11 key bits per target, the second replay also appends every key under one of the targets'
+// 11-bit prefixes to a device buffer (mc_kernel epilogue, one atomicAdd per 256-path block).  The third pass then reads
+// that buffer (4 B per candidate, HBM-bound, sub-millisecond at 10^8 paths) instead of replaying the simulation: exact
+// order statistics in two replays (one when the first rides along with the statistics launch).  The buffer is sized for
+// every path of the shard, so it cannot overflow; when that does not fit (budget below) the third replay runs as before.
+// Validity is checked, never assumed: the fingerprint covers every field that determines the paths.
+uint64_t fnv1a(const void *data, size_t bytes, uint64_t h = 1469598103934665603ull) {
+  const unsigned char *p = static_cast<const unsigned char *>(data);
+  for (size_t i = 0; i < bytes; i++) h = (h ^ p[i]) * 1099511628211ull;
+  return h;
+}
+
+CandFingerprint fingerprint_of(const smmc_config *cfg) {
+  CandFingerprint f;
+  memset(&f, 0, sizeof f);
+  f.mode = cfg->mode;
+  f.n = cfg->n_simulations;
+  f.periods = cfg->n_periods;
+  f.n_returns = cfg->n_returns;
+  f.seed = cfg->seed;
+  f.offset = cfg->stream_offset;
+  f.v0 = cfg->initial_capital;
+  f.gm = cfg->gauss_mean;
+  f.gs = cfg->gauss_std;
+  f.wfixed = cfg->withdraw_fixed;
+  f.wpct = cfg->withdraw_pct;
+  f.rounds = cfg->philox_rounds == 7 ? 7 : 10;
+  const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
+  if (is_bootstrap(cfg->mode))
+    f.table = devp ? (uint64_t)reinterpret_cast<uintptr_t>(cfg->returns) ^ 0x5555555555555555ull
+                   : fnv1a(cfg->returns, (size_t)cfg->n_returns * 4);
+  if (cfg->withdraw_pct_schedule) f.schedule = fnv1a(cfg->withdraw_pct_schedule, (size_t)cfg->n_periods * 4);
+  const smmc::Variant v = current_variant();
+  f.tbl_mask = gauss_table_mask(cfg->mode, v);
+  return f;
+}
+
+// Enqueues the select pass described by `sst` for the local shard `cfg` on ctx (caller holds ctx->mu).  hist_dev: the
+// caller's device histogram (DEVICE_POINTERS) or null = ctx->selhist.  *hist_out / *words_out: where the digit histograms
+// are on the device.  The kernel's events go into the context's ring (smmc_kernel_times) either way.
+smmc_status select_pass_enqueue(Context *ctx, const smmc_config *cfg, const smmc_select_state *sst, unsigned long long *hist_dev,
+                                cudaStream_t *stream_out, unsigned long long **hist_out, int *words_out, int *ev_slot_out,
+                                int *launches_out) {
+  SelectPass sp;
+  smmc_status st = make_select_pass(sst, &sp);
+  if (st != SMMC_OK) return st;
+  sp.hist_dev = hist_dev;
+  const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
+  cudaStream_t stream = devp ? (cudaStream_t)cfg->stream : ctx->stream;
+  const CandFingerprint fp = fingerprint_of(cfg);
+  CU(cudaSetDevice(ctx->device));
+
+  // ---- last pass over the candidates of the previous replay?
+  if (sst->bits_done == 22 && ctx->cand_valid && memcmp(&fp, &ctx->cand_fp, sizeof fp) == 0) {
+    bool covered = true;
+    for (int t = 0; t < sst->n_targets && covered; t++) {
+      bool hit = false;
+      for (int g = 0; g < ctx->cand_groups; g++) hit = hit || ((sst->prefix[t] >> 11) == ctx->cand_prefix[g]);
+      covered = hit;
+    }
+    if (covered) {
+      st = order_after_last_use(ctx, stream);
+      if (st != SMMC_OK) return st;
+      const size_t sel_bytes = (size_t)sp.targets * SMMC_SELECT_BINS * sizeof(unsigned long long);
+      unsigned long long *hd = hist_dev;
+      if (!hd) {
+        CU(ctx->selhist.reserve(sel_bytes));
+        hd = (unsigned long long *)ctx->selhist.p;
+      }
+      CU(cudaMemsetAsync(hd, 0, sel_bytes, stream));
+      const int slot = (int)(ctx->ev_head % kEventRing);
+      CU(cudaEventRecord(ctx->ev0[slot], stream));
+      CU(smmc::launch_select_candidates((const uint32_t *)ctx->cand_keys.p, (const unsigned long long *)ctx->cand_cursor.p,
+                                        ctx->cand_capacity, sp.targets, sp.digit_shift, sp.digit_mask, sp.prefix_shift, sp.prefix, hd,
+                                        ctx->n_sms, stream));
+      CU(cudaEventRecord(ctx->ev1[slot], stream));
+      ctx->ev_head++;
+      st = mark_last_use(ctx, stream);
+      if (st != SMMC_OK) return st;
+      *stream_out = stream;
+      *hist_out = hd;
+      *words_out = sp.targets * SMMC_SELECT_BINS;
+      *ev_slot_out = slot;
+      *launches_out = 1;
+      return SMMC_OK;
+    }
+  }
+
+  // ---- a replay; the second one (11 bits known) collects the candidates for the third
+  ctx->cand_valid = false;
+  bool collecting = false;
+  if (sst->bits_done == 11 && cfg->n_simulations > 0 && current_variant().select_candidates != 0) {
+    size_t free_b = 0, total_b = 0;
+    const size_t need = (size_t)cfg->n_simulations * 4;
+    const bool have = ctx->cand_keys.cap >= need;
+    if (have || (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && need <= free_b / 2 && need <= ((size_t)8 << 30))) {
+      if (ctx->cand_keys.reserve(need) == cudaSuccess && ctx->cand_cursor.reserve(16) == cudaSuccess) {
+        int groups = 0;
+        for (int t = 0; t < sst->n_targets; t++) {
+          bool seen = false;
+          for (int g = 0; g < groups; g++) seen = seen || (sp.cand_prefix[g] == sst->prefix[t]);
+          if (!seen) sp.cand_prefix[groups++] = sst->prefix[t];
+        }
+        sp.cand_groups = groups;
+        sp.cand_keys = (uint32_t *)ctx->cand_keys.p;
+        sp.cand_cursor = (unsigned long long *)ctx->cand_cursor.p;
+        sp.cand_capacity = (unsigned long long)cfg->n_simulations;
+        collecting = true;
+      } else {
+        cudaGetLastError();  // out of memory: no candidates, the third pass replays
+      }
+    }
+  }
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  Pending pd;
+  st = enqueue(cfg, &dummy, ctx, &pd, &sp);
+  if (st != SMMC_OK) return st;
+  if (collecting) {
+    ctx->cand_valid = true;
+    ctx->cand_fp = fp;
+    ctx->cand_groups = sp.cand_groups;
+    for (int g = 0; g < SMMC_SELECT_MAX_TARGETS; g++) ctx->cand_prefix[g] = sp.cand_prefix[g];
+    ctx->cand_capacity = sp.cand_capacity;
+  }
+  *stream_out = pd.stream;
+  *hist_out = pd.sel_dev;
+  *words_out = pd.sel_words;
+  *ev_slot_out = pd.ev_slot;
+  *launches_out = pd.launches;
   return SMMC_OK;
 }
 
@@ -814,12 +1412,14 @@ smmc_status smmc_stats_finalize(const double *stats, int32_t hist_bins, float in
 }
 
 smmc_status smmc_run(const smmc_config *cfg, smmc_result *out) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_status st = validate(cfg, out);
   if (st != SMMC_OK) return st;
   Context *ctx = nullptr;
   st = get_context(cfg->device, &ctx);
   if (st != SMMC_OK) return st;
   std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!(cfg->flags & SMMC_FLAG_DEVICE_POINTERS)) return run_host(cfg, std::vector<Context *>(1, ctx), out);
   Pending pd;
   st = enqueue(cfg, out, ctx, &pd);
   if (st != SMMC_OK) return st;
@@ -835,6 +1435,7 @@ smmc_status smmc_run(const smmc_config *cfg, smmc_result *out) {
 }
 
 smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_status st = validate(cfg, out);
   if (st != SMMC_OK) return st;
   if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "smmc_run_multi takes host pointers");
@@ -842,55 +1443,147 @@ smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out)
   if (ndev <= 0) return fail(SMMC_ERR_NO_DEVICE, "no CUDA device of compute capability 10.x (sm_100a) is visible; this library has no CPU fallback");
   if (n_gpus < 1 || n_gpus > ndev) return fail(SMMC_ERR_INVALID_ARG, "n_gpus %d out of range [1,%d]", n_gpus, ndev);
   if (n_gpus == 1) return smmc_run(cfg, out);
-
-  const int64_t N = cfg->n_simulations;
-  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
-  const int64_t per = (nb + n_gpus - 1) / n_gpus;  // logical blocks per device
-  std::vector<Pending> pend((size_t)n_gpus);
-  std::vector<smmc_config> cfgs((size_t)n_gpus, *cfg);
-  std::vector<smmc_result> outs((size_t)n_gpus, *out);
   std::vector<Context *> ctxs((size_t)n_gpus, nullptr);
   for (int g = 0; g < n_gpus; g++) {
-    st = get_context(g, &ctxs[g]);
+    st = get_context(g, &ctxs[(size_t)g]);
     if (st != SMMC_OK) return st;
   }
-  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.lock();
-  smmc_status rc = SMMC_OK;
-  int launched = 0;
-  for (int g = 0; g < n_gpus && rc == SMMC_OK; g++) {
-    int64_t b0 = per * g, b1 = per * (g + 1);
-    if (b0 > nb) b0 = nb;
-    if (b1 > nb) b1 = nb;
-    const int64_t p0 = b0 * SMMC_BLOCK;
-    int64_t p1 = b1 * SMMC_BLOCK;
-    if (p1 > N) p1 = N;
-    cfgs[g].device = g;
-    cfgs[g].stream_offset = cfg->stream_offset + (uint64_t)p0;
-    cfgs[g].n_simulations = p1 - p0;
-    outs[g].finals = out->finals ? out->finals + p0 : nullptr;
-    outs[g].block_means = out->block_means ? out->block_means + b0 : nullptr;
-    outs[g].block_vars = out->block_vars ? out->block_vars + b0 : nullptr;
-    rc = enqueue(&cfgs[g], &outs[g], ctxs[g], &pend[g]);
-    if (rc == SMMC_OK) launched++;
+  for (int g = 0; g < n_gpus; g++) ctxs[(size_t)g]->mu.lock();
+  st = run_host(cfg, ctxs, out);
+  for (int g = 0; g < n_gpus; g++) ctxs[(size_t)g]->mu.unlock();
+  return st;
+}
+
+// ---- one rank per GPU ------------------------------------------------------------------------------------------------------
+
+smmc_status smmc_comm_unique_id(void *id) {
+  if (!id) return fail(SMMC_ERR_INVALID_ARG, "comm_unique_id: null buffer");
+  const smmc::NcclApi *api = nullptr;
+  smmc_status st = need_nccl(&api);
+  if (st != SMMC_OK) return st;
+  smmc::NcclUniqueId uid;
+  NCCL_CALL(api, api->GetUniqueId(&uid));
+  static_assert(sizeof uid == SMMC_COMM_ID_BYTES, "NCCL_UNIQUE_ID_BYTES");
+  memcpy(id, &uid, sizeof uid);
+  return SMMC_OK;
+}
+
+smmc_status smmc_comm_init_rank(const void *id, int32_t n_ranks, int32_t rank, int32_t device, smmc_comm **comm) {
+  DeviceGuard device_guard;
+  if (!id || !comm || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(SMMC_ERR_INVALID_ARG, "comm_init_rank: bad arguments");
+  const smmc::NcclApi *api = nullptr;
+  smmc_status st = need_nccl(&api);
+  if (st != SMMC_OK) return st;
+  Context *ctx = nullptr;
+  st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  CU(cudaSetDevice(device));
+  smmc::NcclUniqueId uid;
+  memcpy(&uid, id, sizeof uid);
+  smmc::NcclComm c = nullptr;
+  NCCL_CALL(api, api->CommInitRank(&c, n_ranks, uid, rank));
+  smmc_comm *out = new smmc_comm;
+  out->nccl = c;
+  out->n_ranks = n_ranks;
+  out->rank = rank;
+  out->device = device;
+  out->owned = true;
+  *comm = out;
+  int ver = 0;
+  api->GetVersion(&ver);
+  // one line per rank on stderr (stdout stays free for the caller's own output, e.g. bench.py's JSON line)
+  fprintf(stderr, "smmc: NCCL %d communicator ready: rank %d nranks %d cudaDev %d\n", ver, rank, n_ranks, device);
+  return SMMC_OK;
+}
+
+smmc_status smmc_comm_adopt(void *nccl_comm, int32_t device, smmc_comm **comm) {
+  if (!nccl_comm || !comm) return fail(SMMC_ERR_INVALID_ARG, "comm_adopt: null argument");
+  const smmc::NcclApi *api = nullptr;
+  smmc_status st = need_nccl(&api);
+  if (st != SMMC_OK) return st;
+  Context *ctx = nullptr;
+  st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  int n = 0, r = 0;
+  NCCL_CALL(api, api->CommCount((smmc::NcclComm)nccl_comm, &n));
+  NCCL_CALL(api, api->CommUserRank((smmc::NcclComm)nccl_comm, &r));
+  smmc_comm *out = new smmc_comm;
+  out->nccl = (smmc::NcclComm)nccl_comm;
+  out->n_ranks = n;
+  out->rank = r;
+  out->device = device;
+  out->owned = false;
+  *comm = out;
+  return SMMC_OK;
+}
+
+smmc_status smmc_comm_destroy(smmc_comm *comm) {
+  if (!comm) return SMMC_OK;
+  if (comm->owned && comm->nccl) {
+    const smmc::NcclApi *api = smmc::nccl_api();
+    if (api) api->CommDestroy(comm->nccl);
   }
-  const int slen = smmc_stats_len(cfg->hist_bins);
-  std::vector<double> total((size_t)slen, 0.0), part((size_t)slen);
-  float ms_max = 0.0f;
-  int launches = 0;
-  for (int g = 0; g < launched; g++) {
-    float ms = 0.0f;
-    smmc_status s2 = collect(pend[g], &outs[g], part.data(), &ms);
-    if (s2 != SMMC_OK && rc == SMMC_OK) rc = s2;
-    for (int i = 0; i < slen; i++) total[i] += part[i];  // rank order: deterministic
-    if (ms > ms_max) ms_max = ms;
-    launches += pend[g].launches;
+  delete comm;
+  return SMMC_OK;
+}
+
+smmc_status smmc_comm_info(const smmc_comm *comm, int32_t *n_ranks, int32_t *rank, int32_t *device, int32_t *nccl_version) {
+  if (!comm) return fail(SMMC_ERR_INVALID_ARG, "comm_info: null communicator");
+  if (n_ranks) *n_ranks = comm->n_ranks;
+  if (rank) *rank = comm->rank;
+  if (device) *device = comm->device;
+  if (nccl_version) {
+    int v = 0;
+    const smmc::NcclApi *api = smmc::nccl_api();
+    if (api) api->GetVersion(&v);
+    *nccl_version = v;
   }
-  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.unlock();
-  if (rc != SMMC_OK) return rc;
-  out->device_ms = ms_max;
-  out->gpu_launches = launches;
-  return smmc_stats_finalize(total.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count,
-                             &out->mean, &out->m2, out->hist);
+  return SMMC_OK;
+}
+
+smmc_status smmc_rank_range(int64_t n_simulations, int32_t n_ranks, int32_t rank, int64_t *first, int64_t *count) {
+  if (n_simulations < 0 || n_ranks < 1 || rank < 0 || rank >= n_ranks || !first || !count)
+    return fail(SMMC_ERR_INVALID_ARG, "rank_range: bad arguments");
+  rank_range(n_simulations, n_ranks, rank, first, count);
+  return SMMC_OK;
+}
+
+smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *comm) {
+  DeviceGuard device_guard;
+  smmc_status st = validate(cfg, out);
+  if (st != SMMC_OK) return st;
+  if (!comm) return fail(SMMC_ERR_INVALID_ARG, "run_rank: null communicator");
+  const smmc::NcclApi *api = nullptr;
+  st = need_nccl(&api);
+  if (st != SMMC_OK) return st;
+  Context *ctx = nullptr;
+  st = get_context(comm->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  smmc_config c2 = *cfg;
+  int64_t first = 0, count = 0;
+  rank_range(cfg->n_simulations, comm->n_ranks, comm->rank, &first, &count);
+  c2.device = comm->device;
+  c2.stream_offset = cfg->stream_offset + (uint64_t)first;
+  c2.n_simulations = count;
+  st = validate(&c2, out, false);  // 32-bit id limits of COMPAT / Sobol apply to the shard as well
+  if (st != SMMC_OK) return st;
+  Pending pd;
+  st = enqueue(&c2, out, ctx, &pd);
+  if (st != SMMC_OK) return st;
+  out->gpu_launches = pd.launches;
+  // the ONE collective of the path: O(KB), on the kernel's stream (stream order = data dependency)
+  NCCL_CALL(api, api->AllReduce(pd.stats_dev, pd.stats_dev, (size_t)pd.stats_len, smmc::kNcclFloat64, smmc::kNcclSum, comm->nccl, pd.stream));
+  st = mark_last_use(ctx, pd.stream);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_NO_SYNC) return SMMC_OK;
+  std::vector<double> stats((size_t)pd.stats_len);
+  float ms = 0.0f;
+  st = collect(pd, out, stats.data(), &ms);
+  if (st != SMMC_OK) return st;
+  out->device_ms = ms;
+  return smmc_stats_finalize(stats.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count, &out->mean,
+                             &out->m2, out->hist);
 }
 
 namespace {
@@ -913,6 +1606,7 @@ smmc_status reduce_sum_device(Context *ctx, const float *v_dev, int64_t n, cudaS
 }  // namespace
 
 smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float *mean_out) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (!vec || !mean_out || n <= 0) return fail(SMMC_ERR_INVALID_ARG, "reduce_mean: need n > 0 and non-null pointers");
   Context *ctx = nullptr;
   smmc_status st = get_context(device, &ctx);
@@ -930,6 +1624,7 @@ smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float 
 
 smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t device, void *stream, float *mean_out,
                                     float *kernel_ms) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (!vec_dev || !mean_out || n <= 0)
     return fail(SMMC_ERR_INVALID_ARG, "reduce_mean_device: need n > 0 and non-null pointers");
   if (reinterpret_cast<uintptr_t>(vec_dev) & 3u) return fail(SMMC_ERR_INVALID_ARG, "reduce_mean_device: pointer must be 4-byte aligned");
@@ -946,6 +1641,7 @@ smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t dev
 }
 
 smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (n < 0 || (n > 0 && (!out || !a || !b))) return fail(SMMC_ERR_INVALID_ARG, "vector_add: bad arguments");
   Context *ctx = nullptr;
   smmc_status st = get_context(device, &ctx);
@@ -965,6 +1661,7 @@ smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t 
 
 smmc_status smmc_vector_add_device(float *out_dev, const float *a_dev, const float *b_dev, int64_t n, int32_t device,
                                    void *stream, float *kernel_ms) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (n < 0 || (n > 0 && (!out_dev || !a_dev || !b_dev))) return fail(SMMC_ERR_INVALID_ARG, "vector_add_device: bad arguments");
   if ((reinterpret_cast<uintptr_t>(out_dev) | reinterpret_cast<uintptr_t>(a_dev) | reinterpret_cast<uintptr_t>(b_dev)) & 3u)
     return fail(SMMC_ERR_INVALID_ARG, "vector_add_device: pointers must be 4-byte aligned");
@@ -994,6 +1691,7 @@ smmc_status smmc_select_begin(smmc_select_state *st, int32_t n_targets, const ui
 }
 
 smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *sst, uint64_t *hist) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
   if (!hist) return fail(SMMC_ERR_INVALID_ARG, "select_pass: null histogram");
@@ -1005,8 +1703,8 @@ smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *ss
   }
   smmc_status st = validate(cfg ? &c2 : nullptr, &dummy);
   if (st != SMMC_OK) return st;
-  SelectPass sp;
-  st = make_select_pass(sst, &sp);
+  SelectPass probe;
+  st = make_select_pass(sst, &probe);
   if (st != SMMC_OK) return st;
   Context *ctx = nullptr;
   st = get_context(cfg->device, &ctx);
@@ -1014,22 +1712,24 @@ smmc_status smmc_select_pass(const smmc_config *cfg, const smmc_select_state *ss
   std::lock_guard<std::mutex> lk(ctx->mu);
   const bool devp = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) != 0;
   const size_t all_bytes = (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS * sizeof(uint64_t);
-  Pending pd;
+  cudaStream_t stream = nullptr;
+  unsigned long long *hd = nullptr;
+  int words = 0, slot = 0, launches = 0;
   if (devp) {
     CU(cudaSetDevice(cfg->device));
     CU(cudaMemsetAsync(hist, 0, all_bytes, (cudaStream_t)cfg->stream));
-    sp.hist_dev = (unsigned long long *)hist;
-    return enqueue(&c2, &dummy, ctx, &pd, &sp);  // asynchronous on cfg->stream
+    return select_pass_enqueue(ctx, &c2, sst, (unsigned long long *)hist, &stream, &hd, &words, &slot, &launches);  // asynchronous
   }
-  st = enqueue(&c2, &dummy, ctx, &pd, &sp);
+  st = select_pass_enqueue(ctx, &c2, sst, nullptr, &stream, &hd, &words, &slot, &launches);
   if (st != SMMC_OK) return st;
   memset(hist, 0, all_bytes);
-  CU(cudaMemcpyAsync(hist, pd.sel_dev, (size_t)pd.sel_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, pd.stream));
-  CU(cudaStreamSynchronize(pd.stream));
+  CU(cudaMemcpyAsync(hist, hd, (size_t)words * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+  CU(cudaStreamSynchronize(stream));
   return SMMC_OK;
 }
 
 smmc_status smmc_run_select(const smmc_config *cfg, smmc_result *out, const smmc_select_state *sst, uint64_t *hist) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_status st = validate(cfg, out);
   if (st != SMMC_OK) return st;
   if (!hist) return fail(SMMC_ERR_INVALID_ARG, "run_select: null histogram");
@@ -1092,8 +1792,65 @@ smmc_status smmc_select_values(const smmc_select_state *st, float *values) {
   return SMMC_OK;
 }
 
+namespace {
+// The select loop shared by smmc_quantiles (devices of this process) and smmc_quantiles_rank (one rank of a job): per pass,
+// every local shard enqueues its replay / candidate pass, the digit histograms are merged -- ncclAllReduce(ncclUint64) on
+// the devices when more than one shard or rank takes part -- and ONE histogram is downloaded.  Caller holds the ctx locks.
+smmc_status select_loop(std::vector<Shard> &shards, const std::vector<smmc::NcclComm> *comms, smmc_select_state *sel, float *ms_total) {
+  const smmc::NcclApi *api = nullptr;
+  if (comms) {
+    smmc_status st = need_nccl(&api);
+    if (st != SMMC_OK) return st;
+  }
+  const size_t words_all = (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS;
+  std::vector<uint64_t> total(words_all);
+  *ms_total = 0.0f;
+  const size_t S = shards.size();
+  while (sel->bits_done < 32) {
+    std::vector<cudaStream_t> streams(S, nullptr);
+    std::vector<unsigned long long *> hd(S, nullptr);
+    std::vector<int> words(S, 0), slots(S, 0);
+    for (size_t g = 0; g < S; g++) {
+      int launches = 0;
+      smmc_config c2 = shards[g].cfg;
+      c2.hist_bins = 0;
+      smmc_status st = select_pass_enqueue(shards[g].ctx, &c2, sel, nullptr, &streams[g], &hd[g], &words[g], &slots[g], &launches);
+      if (st != SMMC_OK) return st;
+    }
+    if (comms) {
+      NCCL_CALL(api, api->GroupStart());
+      for (size_t g = 0; g < S; g++) {
+        int r = api->AllReduce(hd[g], hd[g], (size_t)words[g], smmc::kNcclUint64, smmc::kNcclSum, (*comms)[g], streams[g]);
+        if (r != 0) {
+          api->GroupEnd();
+          return fail(SMMC_ERR_CUDA, "ncclAllReduce failed: %s", api->GetErrorString(r));
+        }
+      }
+      NCCL_CALL(api, api->GroupEnd());
+    }
+    std::fill(total.begin(), total.end(), 0ull);
+    float ms_pass = 0.0f;
+    for (size_t g = 0; g < S; g++) {
+      Context *ctx = shards[g].ctx;
+      CU(cudaSetDevice(ctx->device));
+      if (g == 0)
+        CU(cudaMemcpyAsync(total.data(), hd[g], (size_t)words[g] * sizeof(uint64_t), cudaMemcpyDeviceToHost, streams[g]));
+      CU(cudaStreamSynchronize(streams[g]));
+      float ms = 0.0f;
+      CU(cudaEventElapsedTime(&ms, ctx->ev0[slots[g]], ctx->ev1[slots[g]]));
+      if (ms > ms_pass) ms_pass = ms;
+    }
+    *ms_total += ms_pass;
+    smmc_status st = smmc_select_advance(sel, total.data());
+    if (st != SMMC_OK) return st;
+  }
+  return SMMC_OK;
+}
+}  // namespace
+
 smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_targets, const uint64_t *ranks,
                            float *values, float *device_ms) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
   smmc_status st = validate(cfg, &dummy);
@@ -1109,61 +1866,58 @@ smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_tar
   const int ndev = probe_devices();
   if (ndev <= 0) return fail(SMMC_ERR_NO_DEVICE, "no CUDA device of compute capability 10.x (sm_100a) is visible; this library has no CPU fallback");
   if (n_gpus < 1 || n_gpus > ndev) return fail(SMMC_ERR_INVALID_ARG, "n_gpus %d out of range [1,%d]", n_gpus, ndev);
-
-  const int64_t N = cfg->n_simulations;
-  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
-  const int64_t per = (nb + n_gpus - 1) / n_gpus;
   std::vector<Context *> ctxs((size_t)n_gpus, nullptr);
   for (int g = 0; g < n_gpus; g++) {
-    st = get_context(g == 0 && n_gpus == 1 ? cfg->device : g, &ctxs[g]);
+    st = get_context(n_gpus == 1 ? cfg->device : g, &ctxs[(size_t)g]);
     if (st != SMMC_OK) return st;
   }
-  const size_t words = (size_t)SMMC_SELECT_MAX_TARGETS * SMMC_SELECT_BINS;
-  std::vector<uint64_t> total(words), part(words);
-  float ms_total = 0.0f;
-  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.lock();
-  smmc_status rc = SMMC_OK;
-  while (rc == SMMC_OK && sel.bits_done < 32) {
-    SelectPass sp;
-    rc = make_select_pass(&sel, &sp);
-    std::vector<Pending> pend((size_t)n_gpus);
-    int launched = 0;
-    for (int g = 0; g < n_gpus && rc == SMMC_OK; g++) {
-      int64_t b0 = per * g, b1 = per * (g + 1);
-      if (b0 > nb) b0 = nb;
-      if (b1 > nb) b1 = nb;
-      int64_t p1 = b1 * SMMC_BLOCK;
-      if (p1 > N) p1 = N;
-      smmc_config c2 = *cfg;
-      c2.hist_bins = 0;
-      c2.device = ctxs[g]->device;
-      c2.stream_offset = cfg->stream_offset + (uint64_t)(b0 * SMMC_BLOCK);
-      c2.n_simulations = p1 - b0 * SMMC_BLOCK;
-      rc = enqueue(&c2, &dummy, ctxs[g], &pend[g], &sp);
-      if (rc == SMMC_OK) launched++;
-    }
-    std::fill(total.begin(), total.end(), 0ull);
-    float ms_pass = 0.0f;
-    for (int g = 0; g < launched; g++) {
-      const Pending &pd = pend[g];
-      cudaError_t e = cudaSetDevice(pd.ctx->device);
-      if (e == cudaSuccess)
-        e = cudaMemcpyAsync(part.data(), pd.sel_dev, (size_t)pd.sel_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, pd.stream);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(pd.stream);
-      float ms = 0.0f;
-      if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, pd.ctx->ev0[pd.ev_slot], pd.ctx->ev1[pd.ev_slot]);
-      if (e != cudaSuccess) {
-        if (rc == SMMC_OK) rc = fail(SMMC_ERR_CUDA, "quantiles: %s", cudaGetErrorString(e));
-        continue;
-      }
-      for (int i = 0; i < pd.sel_words; i++) total[i] += part[i];
-      if (ms > ms_pass) ms_pass = ms;
-    }
-    ms_total += ms_pass;
-    if (rc == SMMC_OK) rc = smmc_select_advance(&sel, total.data());
+  const std::vector<smmc::NcclComm> *comms = nullptr;
+  if (n_gpus > 1) {
+    st = multi_comms(n_gpus, &comms);
+    if (st != SMMC_OK) return st;
   }
-  for (int g = 0; g < n_gpus; g++) ctxs[g]->mu.unlock();
-  if (rc != SMMC_OK) return rc;
+  std::vector<Shard> shards;
+  make_shards(cfg, &dummy, ctxs, &shards);
+  for (int g = 0; g < n_gpus; g++) ctxs[(size_t)g]->mu.lock();
+  float ms_total = 0.0f;
+  st = select_loop(shards, comms, &sel, &ms_total);
+  for (int g = 0; g < n_gpus; g++) ctxs[(size_t)g]->mu.unlock();
+  if (st != SMMC_OK) return st;
+  if (device_ms) *device_ms = ms_total;
+  return smmc_select_values(&sel, values);
+}
+
+smmc_status smmc_quantiles_rank(const smmc_config *cfg, smmc_comm *comm, int32_t n_targets, const uint64_t *ranks, float *values,
+                                float *device_ms) {
+  DeviceGuard device_guard;
+  smmc_result dummy;
+  memset(&dummy, 0, sizeof dummy);
+  smmc_status st = validate(cfg, &dummy);
+  if (st != SMMC_OK) return st;
+  if (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) return fail(SMMC_ERR_INVALID_ARG, "smmc_quantiles_rank takes host pointers");
+  if (!values || !comm) return fail(SMMC_ERR_INVALID_ARG, "quantiles_rank: null argument");
+  smmc_select_state sel;
+  st = smmc_select_begin(&sel, n_targets, ranks);
+  if (st != SMMC_OK) return st;
+  for (int t = 0; t < n_targets; t++)
+    if (ranks[t] >= (uint64_t)cfg->n_simulations)
+      return fail(SMMC_ERR_INVALID_ARG, "quantiles: rank %llu >= n_simulations", (unsigned long long)ranks[t]);
+  Context *ctx = nullptr;
+  st = get_context(comm->device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::vector<Shard> shards(1);
+  int64_t first = 0, count = 0;
+  rank_range(cfg->n_simulations, comm->n_ranks, comm->rank, &first, &count);
+  shards[0].ctx = ctx;
+  shards[0].cfg = *cfg;
+  shards[0].cfg.device = comm->device;
+  shards[0].cfg.stream_offset = cfg->stream_offset + (uint64_t)first;
+  shards[0].cfg.n_simulations = count;
+  const std::vector<smmc::NcclComm> comms(1, comm->nccl);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  float ms_total = 0.0f;
+  st = select_loop(shards, &comms, &sel, &ms_total);
+  if (st != SMMC_OK) return st;
   if (device_ms) *device_ms = ms_total;
   return smmc_select_values(&sel, values);
 }
@@ -1171,6 +1925,7 @@ smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_tar
 // ---- trajectory mode -----------------------------------------------------------------------------------------------
 
 smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *values, float *returns_pct) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
   smmc_config c2;
@@ -1266,6 +2021,7 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
 }
 
 smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *outbuf) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   smmc_result dummy;
   memset(&dummy, 0, sizeof dummy);
   smmc_config c2;
@@ -1306,6 +2062,7 @@ smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t 
 
 smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, int32_t rounds, int32_t n, int32_t device,
                                      uint32_t *outbuf) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (!ctr || !key || !outbuf || n < 0) return fail(SMMC_ERR_INVALID_ARG, "debug_philox: bad arguments");
   if (rounds != 7 && rounds != 10) return fail(SMMC_ERR_INVALID_ARG, "debug_philox: rounds must be 7 or 10");
   Context *ctx = nullptr;
@@ -1337,11 +2094,14 @@ smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
   else if (!strcmp(key, "sobol_tbl")) g_variant.sobol_tbl = (value == 0 || value == 1) ? value : def.sobol_tbl;
   else if (!strcmp(key, "sobol_unroll")) g_variant.sobol_unroll = value > 0 ? value : def.sobol_unroll;
   else if (!strcmp(key, "finals_chunks")) g_variant.finals_chunks = value > 0 ? value : def.finals_chunks;
+  else if (!strcmp(key, "select_candidates")) g_variant.select_candidates = (value == 0 || value == 1) ? value : def.select_candidates;
+  else if (!strcmp(key, "finals_threads")) g_variant.finals_threads = (value > 0 && value <= 64) ? value : def.finals_threads;
   else return fail(SMMC_ERR_INVALID_ARG, "debug_set_variant: unknown key '%s'", key);
   return SMMC_OK;
 }
 
 smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int32_t *n_out) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
   if (!ms_out || !n_out || max_n < 0) return fail(SMMC_ERR_INVALID_ARG, "kernel_times: bad arguments");
   Context *ctx = nullptr;
   smmc_status st = get_context(device, &ctx);
@@ -1364,6 +2124,7 @@ const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 2)"; }
 int32_t smmc_device_count(void) { return probe_devices(); }
 
 void smmc_shutdown(void) {
+  DeviceGuard device_guard;
   std::lock_guard<std::mutex> lk(g_ctx_mu);
   for (int d = 0; d < kMaxDevices; d++) {
     Context &c = g_ctx[d];
@@ -1381,6 +2142,25 @@ void smmc_shutdown(void) {
     if (c.last_use) cudaEventDestroy(c.last_use);
     c.last_use = nullptr;
     c.has_last_use = false;
+    for (int i = 0; i < Context::kStageSlots; i++) {
+      if (c.stage[i]) cudaFreeHost(c.stage[i]);
+      c.stage[i] = nullptr;
+    }
+    c.stage_cap = 0;
+    c.chunk_stats.release();
+    c.cand_keys.release();
+    c.cand_cursor.release();
+    c.cand_valid = false;
+    if (c.chunk_stats_host) cudaFreeHost(c.chunk_stats_host);
+    c.chunk_stats_host = nullptr;
+    c.chunk_stats_host_cap = 0;
+    for (int i = 0; i < Context::kChunkDepth; i++) {
+      cudaEventDestroy(c.kdone[i]);
+      cudaEventDestroy(c.cdone[i]);
+      cudaEventDestroy(c.sdone[i]);
+    }
+    if (c.copy_stream) cudaStreamDestroy(c.copy_stream);
+    c.copy_stream = nullptr;
     c.tbl.release();
     c.work.release();
     c.stats.release();

@@ -48,24 +48,27 @@ smmc_config base_config(long N, int n_periods, float initial_capital, std::vecto
   return c;
 }
 
-// Touches every page of a freshly reserved (not yet constructed) float buffer from several threads: the value-initialising
-// resize() that follows then runs over mapped pages instead of taking ~100 000 page faults serially (10^8 finals).
-void first_touch(void *ptr, size_t bytes) {
-  constexpr size_t kPage = 4096, kMin = 32u << 20;
-  if (!ptr || bytes < kMin) return;
-  const unsigned hw = std::thread::hardware_concurrency();
-  const unsigned nt = hw >= 16 ? 8u : (hw >= 4 ? hw / 2 : 1u);
-  char *base = static_cast<char *>(ptr);
-  const size_t pages = (bytes + kPage - 1) / kPage;
-  std::vector<std::thread> th;
-  for (unsigned t = 0; t < nt; t++)
-    th.emplace_back([=] {
-      for (size_t pg = pages * t / nt; pg < pages * (t + 1) / nt; pg++) {
-        const size_t off = pg * kPage;
-        if (off < bytes) *reinterpret_cast<volatile char *>(base + off) = 0;
-      }
-    });
-  for (auto &x : th) x.join();
+// A std::vector<float> of n elements whose storage is NOT value-initialised: the reference's contract is "totals is
+// replaced by a fresh N-element vector" (src/simulations.cu:643-644), and every element is about to be overwritten by
+// the download, so the 400 MB zero-fill of resize() (10^8 paths: ~40 ms, single-threaded, page faults included) is pure
+// overhead.  libstdc++'s vector is three pointers {begin, end, end_of_storage} -- the layout this drop-in is already
+// bound to by the reference's mangled signatures -- so after reserve(n) the size is set by moving `end`.
+// float is trivially constructible: no constructor is skipped.  Falls back to resize() if the layout check fails.
+void resize_uninitialized(std::vector<float> &v, size_t n) {
+  struct Rep {
+    float *begin, *end, *cap;
+  };
+  static_assert(sizeof(std::vector<float>) == sizeof(Rep), "libstdc++ std::vector layout expected");
+  v.clear();
+  v.reserve(n);
+  Rep rep;
+  std::memcpy(&rep, static_cast<void *>(&v), sizeof rep);
+  if (rep.begin == v.data() && rep.end == rep.begin && rep.cap >= rep.begin + n) {
+    rep.end = rep.begin + n;
+    std::memcpy(static_cast<void *>(&v), &rep, sizeof rep);
+  } else {
+    v.resize(n);
+  }
 }
 
 void export_stats(const smmc_result &r, smmc::Statistics *s) {
@@ -88,9 +91,7 @@ void mc_simulations_gpu(std::atomic<long> &n_simulations, long N, int n_periods,
   std::vector<float> fresh;
   if (totals) {
     const size_t n = (size_t)(N > 0 ? N : 0);
-    fresh.reserve(n);
-    first_touch(fresh.data(), n * sizeof(float));  // the page faults of a fresh 400 MB vector, on 8 threads instead of one
-    fresh.resize(n);
+    resize_uninitialized(fresh, n);  // pages are first touched by the library's download threads, in parallel
     r.finals = fresh.data();
   }
   if (stats && opt.hist_bins > 0) {

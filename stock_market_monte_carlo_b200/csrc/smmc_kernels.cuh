@@ -114,6 +114,8 @@ struct Variant {
   int sobol_tbl = -1;    // SOBOL_GAUSSIAN: 0 = MUFU sin/cos, 1 = table, -1 = default (table)
   int sobol_unroll = 0;  // SOBOL_BOOTSTRAP month unroll (experiment builds), 0 = default
   int finals_chunks = 0; // host-pointer finals pipeline: number of chunks (0 = automatic, 1 = one monolithic launch)
+  int finals_threads = 0; // ... and its host copy-out threads (0 = automatic)
+  int select_candidates = -1;  // 0 = the third select pass always replays (no candidate buffer), -1 / 1 = default
 };
 
 constexpr int kSobolHiRows = 98;   // rows of KParams::sobol_hi

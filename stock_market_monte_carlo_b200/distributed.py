@@ -94,3 +94,19 @@ def quantiles_sharded(mode, n_simulations, n_periods, ranks=None, *, device, str
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
             sel.advance(hist.cpu().numpy().astype("uint64"))
     return sel.values()
+
+
+def init_comm(device, group=None):
+    """A `simulations.Comm` for this rank of the torch.distributed job: rank 0 asks NCCL (inside libsmmc.so) for a unique id,
+    torch.distributed carries the 128 bytes to the other ranks, every rank calls ncclCommInitRank through the C ABI.
+    From then on the collective of the path is `smmc_run_rank` -- torch is only the launcher."""
+    import torch.distributed as dist
+
+    from .simulations import Comm
+
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    box = [Comm.unique_id() if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(box, src=0, group=group)
+    return Comm(box[0], world, rank, device)

@@ -455,3 +455,91 @@ def debug_philox(ctr, key, device=0, rounds=10):
 def set_variant(key=None, value=-1):
     """Test hook (`smmc_debug_set_variant`): pick a compiled kernel variant; set_variant() resets everything."""
     N.check(N.load().smmc_debug_set_variant(key.encode() if key is not None else None, int(value)))
+
+
+# ---- one rank per GPU: the NCCL collective behind the C ABI (include/smmc.h, smmc_comm_* / smmc_run_rank) -----------
+
+def rank_range(n_simulations, n_ranks, rank):
+    """(first path relative to the run's stream_offset, number of paths) of `rank` -- the partition of smmc_run_multi /
+    smmc_run_rank: contiguous ranges of whole 256-path blocks.  Host only."""
+    first, count = C.c_int64(), C.c_int64()
+    N.check(N.load().smmc_rank_range(int(n_simulations), int(n_ranks), int(rank), C.byref(first), C.byref(count)))
+    return int(first.value), int(count.value)
+
+
+class Comm:
+    """One rank's communicator (ncclCommInitRank inside libsmmc.so).  `Comm.unique_id()` on rank 0, the 128 bytes to every
+    rank by any means (distributed.init_comm uses torch.distributed), then `Comm(uid, n_ranks, rank, device)` on every rank."""
+
+    def __init__(self, uid, n_ranks, rank, device):
+        self.lib = N.load()
+        buf = C.create_string_buffer(bytes(uid), N.COMM_ID_BYTES)
+        h = C.c_void_p()
+        N.check(self.lib.smmc_comm_init_rank(buf, int(n_ranks), int(rank), int(device), C.byref(h)))
+        self.handle, self.n_ranks, self.rank, self.device = h, int(n_ranks), int(rank), int(device)
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(N.COMM_ID_BYTES)
+        N.check(N.load().smmc_comm_unique_id(buf))
+        return bytes(buf.raw)
+
+    def info(self):
+        a, b, c, d = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        N.check(self.lib.smmc_comm_info(self.handle, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return dict(n_ranks=a.value, rank=b.value, device=c.value, nccl_version=d.value)
+
+    def destroy(self):
+        if self.handle:
+            self.lib.smmc_comm_destroy(self.handle)
+            self.handle = None
+
+    def simulate(self, mode, n_simulations, n_periods, initial_capital=1000.0, returns=None, seed=0, stream_offset=0,
+                 gauss_mean=0.5, gauss_std=10.0 / 12.0, target=None, hist_bins=0, hist_range=None, want_finals=False,
+                 want_block_partials=False, **extra) -> Result:
+        """This rank's part of the GLOBAL run + the all-reduce (smmc_run_rank, host buffers, blocking).  count / mean / m2 /
+        below_count / hist describe the global run on every rank; finals / block partials cover this rank's range."""
+        cfg, keep = make_config(mode, n_simulations, n_periods, initial_capital, returns, seed, stream_offset, gauss_mean,
+                                gauss_std, target, hist_bins, hist_range, self.device, **extra)
+        _, n_local = rank_range(n_simulations, self.n_ranks, self.rank)
+        nb = (n_local + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
+        res, out = N.SmmcResult(), Result()
+        if want_finals:
+            out.finals = np.empty(n_local, dtype=np.float32)
+            res.finals = out.finals.ctypes.data
+        if want_block_partials:
+            out.block_means, out.block_vars = np.zeros(nb, dtype=np.float32), np.zeros(nb, dtype=np.float32)
+            res.block_means, res.block_vars = out.block_means.ctypes.data, out.block_vars.ctypes.data
+        if hist_bins:
+            out.hist = np.zeros(int(hist_bins) + 2, dtype=np.uint64)
+            res.hist = out.hist.ctypes.data
+        N.check(self.lib.smmc_run_rank(C.byref(cfg), C.byref(res), self.handle))
+        del keep
+        out.count, out.below_count = int(res.count), int(res.below_count)
+        out.mean, out.m2 = float(res.mean), float(res.m2)
+        out.device_ms, out.gpu_launches = float(res.device_ms), int(res.gpu_launches)
+        return out
+
+    def simulate_device(self, mode, n_simulations, n_periods, stats_ptr, stream=0, returns_ptr=None, n_returns=0,
+                        block_means_ptr=None, block_vars_ptr=None, finals_ptr=None, **kw):
+        """Asynchronous variant over device pointers on `stream`: kernel -> ncclAllReduce of the statistics vector at
+        `stats_ptr`, nothing synchronised.  Returns the number of kernels launched on this rank."""
+        cfg, _ = make_config(mode, n_simulations, n_periods, device=self.device, flags=N.FLAG_DEVICE_POINTERS | N.FLAG_NO_SYNC,
+                             stream=stream, returns_ptr=returns_ptr, n_returns=n_returns, **kw)
+        res = N.SmmcResult()
+        res.stats_dev = int(stats_ptr)
+        res.finals = int(finals_ptr) if finals_ptr else None
+        res.block_means = int(block_means_ptr) if block_means_ptr else None
+        res.block_vars = int(block_vars_ptr) if block_vars_ptr else None
+        N.check(self.lib.smmc_run_rank(C.byref(cfg), C.byref(res), self.handle))
+        return int(res.gpu_launches)
+
+    def quantiles(self, mode, n_simulations, n_periods, ranks=None, return_ms=False, **kw):
+        """sorted(finals of the GLOBAL run)[ranks] on every rank (smmc_quantiles_rank)."""
+        cfg, keep = make_config(mode, n_simulations, n_periods, device=self.device, **kw)
+        r = np.ascontiguousarray(np.asarray(quartile_ranks(n_simulations) if ranks is None else ranks, dtype=np.uint64))
+        out = np.zeros(r.size, dtype=np.float32)
+        ms = C.c_float()
+        N.check(self.lib.smmc_quantiles_rank(C.byref(cfg), self.handle, int(r.size), r.ctypes.data, out.ctypes.data, C.byref(ms)))
+        del keep
+        return (out, float(ms.value)) if return_ms else out

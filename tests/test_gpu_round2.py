@@ -1,0 +1,359 @@
+"""Round-2 rows, all through the C ABI on a B200: Philox4x32-7 stream contract, sin/cos table variants, the pipelined
+all-finals path, the NCCL collective behind the C ABI (single-rank communicator on any box, two ranks when two GPUs are
+visible), order statistics in two replays, cross-stream use of the cached workspace, input validation."""
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import ALL_MODES, EXACT_MODES, mode_kwargs
+
+pytestmark = pytest.mark.gpu
+
+# Random123 kat_vectors, "philox4x32 7" (written down before the oracle computed them; tests/test_oracle_pins.py pins the oracle)
+PHILOX7_KAT = [
+    ([0x00000000] * 4, [0x00000000] * 2, [0x5F6FB709, 0x0D893F64, 0x4F121F81, 0x4F730A48]),
+    ([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x5207DDC2, 0x45165E59, 0x4D8EE751, 0x8C52F662]),
+    ([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0],
+     [0x4DFCCABA, 0x190A87F0, 0xC47362BA, 0xB6B5242A]),
+]
+GAUSS_RTOL = 2e-5  # MUFU lg2/sqrt/sin/cos and the sin/cos table vs libm, compounded over <= 1000 months
+
+
+def _n_gpus(S):
+    return int(S.load().smmc_device_count())
+
+
+# ---- Philox4x32-7 ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ctr,key,want", PHILOX7_KAT)
+def test_device_philox7_known_answers(S, ctr, key, want):
+    assert [int(x) for x in S.debug_philox([ctr], key, rounds=7)[0]] == want
+
+
+def test_philox7_draws_and_finals_against_oracle(S, O, table):
+    for off in (0, 512, 1 << 33):
+        for mode in ("bootstrap", "gaussian"):
+            kw = dict(returns=table) if mode == "bootstrap" else {}
+            d = S.debug_draws(mode, 300, 37, seed=11, stream_offset=off, philox_rounds=7, **kw)
+            o = O.draws(mode, 300, 37, seed=11, stream_offset=off, philox_rounds=7, **kw)
+            assert np.array_equal(d, o), (mode, off)
+            assert not np.array_equal(d, S.debug_draws(mode, 300, 37, seed=11, stream_offset=off, **kw))  # a different stream
+    g = S.simulate("bootstrap", 5000, 121, returns=table, seed=3, philox_rounds=7, hist_bins=50, want_finals=True, want_block_partials=True)
+    o = O.simulate("bootstrap", 5000, 121, returns=table, seed=3, philox_rounds=7, hist_bins=50, want_finals=True, want_block_partials=True)
+    assert np.array_equal(g.finals, o.finals) and np.array_equal(g.hist, o.hist) and g.below_count == o.below_count
+    assert np.array_equal(g.block_means, o.block_means) and np.array_equal(g.block_vars, o.block_vars)
+    g = S.simulate("gaussian", 5000, 121, seed=3, philox_rounds=7, want_finals=True)
+    o = O.simulate("gaussian", 5000, 121, seed=3, philox_rounds=7, want_finals=True)
+    np.testing.assert_allclose(g.finals, o.finals, rtol=GAUSS_RTOL)
+    # trajectories and order statistics follow the same contract
+    t = S.trajectories("gaussian", 64, 121, seed=3, philox_rounds=7)
+    assert np.array_equal(t[:, -1], g.finals[:64])
+    q = S.quantiles("gaussian", 5000, 121, seed=3, philox_rounds=7)
+    assert np.array_equal(q, np.sort(g.finals)[S.quartile_ranks(5000)])
+
+
+def test_philox_rounds_are_validated(S):
+    for bad in (1, 5, 8, 20, -7):
+        with pytest.raises(S.SmmcError) as e:
+            S.simulate("gaussian", 1000, 12, philox_rounds=bad)
+        assert e.value.status == 1
+
+
+def test_philox7_closed_form_moments(S):
+    """RNG-independent known answer: E[V] = V0 (1+mu)^P, E[V^2] = V0^2 ((1+mu)^2 + sigma^2)^P at 4e7 paths"""
+    N, P, mu, sg = 40_000_000, 120, 0.005, 1.0 / 120.0
+    r = S.simulate("gaussian", N, P, seed=99, philox_rounds=7)
+    mean = 1000.0 * (1 + mu) ** P
+    var = 1000.0 ** 2 * (((1 + mu) ** 2 + sg ** 2) ** P) - mean ** 2
+    se = (var / N) ** 0.5
+    assert abs(r.mean - mean) < 5 * se
+    assert abs(r.std / var ** 0.5 - 1.0) < 1e-3
+
+
+# ---- sin/cos table -------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["gaussian", "sobol_gaussian"])
+def test_sincos_table_and_mufu_evaluate_the_same_contract(S, O, mode):
+    key = "gauss_tbl" if mode == "gaussian" else "sobol_tbl"
+    N, P = 20_000, 999 if mode == "sobol_gaussian" else 360
+    o = O.simulate(mode, N, P, seed=7, want_finals=True)
+    res = {}
+    try:
+        for v in (0, 5 if mode == "gaussian" else 1):
+            S.set_variant(key, v)
+            r = S.simulate(mode, N, P, seed=7, want_finals=True, hist_bins=20)
+            np.testing.assert_allclose(r.finals, o.finals, rtol=GAUSS_RTOL)
+            t = S.trajectories(mode, 50, P, seed=7)
+            assert np.array_equal(t[:, -1], r.finals[:50])  # the trajectory kernel follows the variant
+            q = S.quantiles(mode, N, P, seed=7)
+            assert np.array_equal(q, np.sort(r.finals)[S.quartile_ranks(N)])
+            res[v] = r
+    finally:
+        S.set_variant()
+    a, b = list(res.values())
+    assert float(np.max(np.abs(a.finals / b.finals - 1.0))) < 1e-5
+    assert not np.array_equal(a.finals, b.finals)  # the hook really switched kernels
+
+
+# ---- the pipelined all-finals path ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ALL_MODES)
+def test_finals_pipeline_is_bit_identical_to_one_launch(S, table, mode):
+    kw = mode_kwargs(mode, table)
+    N, P = 148 * 32 * 256 * 2 + 148 * 32 * 256 // 3 + 77, 6  # 2 1/3 launch waves + a ragged block
+    try:
+        S.set_variant("finals_chunks", 1)
+        a = S.simulate(mode, N, P, hist_bins=32, want_finals=True, want_block_partials=True, **kw)
+        S.set_variant("finals_chunks", 3)
+        b = S.simulate(mode, N, P, hist_bins=32, want_finals=True, want_block_partials=True, **kw)
+        S.set_variant("finals_chunks", 64)  # more chunks than waves: one wave per chunk
+        c = S.simulate(mode, N, P, hist_bins=32, want_finals=True, want_block_partials=True, **kw)
+    finally:
+        S.set_variant()
+    for r in (b, c):
+        assert r.gpu_launches > a.gpu_launches
+        assert np.array_equal(r.finals.view(np.uint32), a.finals.view(np.uint32))
+        assert np.array_equal(r.block_means.view(np.uint32), a.block_means.view(np.uint32))
+        assert np.array_equal(r.block_vars.view(np.uint32), a.block_vars.view(np.uint32))
+        assert np.array_equal(r.hist, a.hist) and r.below_count == a.below_count and r.count == a.count == N
+        assert abs(r.mean - a.mean) <= 1e-12 * abs(a.mean) and abs(r.m2 - a.m2) <= 1e-9 * abs(a.m2)
+
+
+def test_finals_pipeline_default_engages_above_16mb(S, table):
+    N = 5_000_000
+    r = S.simulate("bootstrap_compat", N, 3, returns=table, want_finals=True)
+    assert r.gpu_launches >= 4  # prep + several chunk launches
+    S.set_variant("finals_chunks", 1)
+    try:
+        a = S.simulate("bootstrap_compat", N, 3, returns=table, want_finals=True)
+    finally:
+        S.set_variant()
+    assert a.gpu_launches == 2 and np.array_equal(a.finals, r.finals)
+
+
+def test_mc_simulations_gpu_through_the_pipeline(S, table1127):
+    n, totals = S.AtomicLong(0), S.FloatVector()
+    S.mc_simulations_gpu(n, 6_000_000, 5, 1000.0, S.FloatVector(table1127), totals, 1)
+    ref = S.simulate("bootstrap_compat", 6_000_000, 5, returns=table1127, want_finals=True)
+    assert n.load() == 6_000_000 and np.array_equal(totals.array, ref.finals)
+
+
+# ---- NCCL behind the C ABI ------------------------------------------------------------------------------------------------
+def test_run_rank_on_a_single_rank_communicator(S, table):
+    """ncclCommInitRank + ncclAllReduce inside libsmmc.so, world size 1: must equal smmc_run bit for bit"""
+    comm = S.Comm(S.Comm.unique_id(), 1, 0, 0)
+    try:
+        info = comm.info()
+        assert info["n_ranks"] == 1 and info["rank"] == 0 and info["nccl_version"] >= 20400
+        for mode in ALL_MODES:
+            kw = mode_kwargs(mode, table)
+            a = S.simulate(mode, 70_001, 24, hist_bins=40, want_finals=True, want_block_partials=True, **kw)
+            b = comm.simulate(mode, 70_001, 24, hist_bins=40, want_finals=True, want_block_partials=True, **kw)
+            assert (a.count, a.below_count, a.mean, a.m2) == (b.count, b.below_count, b.mean, b.m2)
+            assert np.array_equal(a.hist, b.hist) and np.array_equal(a.finals, b.finals)
+            assert np.array_equal(a.block_means, b.block_means)
+            assert np.array_equal(comm.quantiles(mode, 70_001, 24, **kw), S.quantiles(mode, 70_001, 24, **kw))
+    finally:
+        comm.destroy()
+
+
+def test_run_rank_device_pointers_async(S):
+    import torch
+    comm = S.Comm(S.Comm.unique_id(), 1, 0, 0)
+    try:
+        stats = torch.zeros(S.stats_len(16), dtype=torch.float64, device="cuda")
+        st = torch.cuda.current_stream()
+        n = comm.simulate_device("gaussian", 300_000, 36, stats.data_ptr(), stream=st.cuda_stream, seed=5, hist_bins=16)
+        assert n >= 1
+        got = S.finalize_stats(stats.cpu().numpy(), 16, 1000.0)
+        ref = S.simulate("gaussian", 300_000, 36, seed=5, hist_bins=16)
+        assert (got.count, got.below_count, got.mean, got.m2) == (ref.count, ref.below_count, ref.mean, ref.m2)
+        assert np.array_equal(got.hist, ref.hist)
+    finally:
+        comm.destroy()
+
+
+def _two_rank_job(S, fn):
+    """two ranks as two host threads of this process, one GPU each (ncclCommInitRank blocks until both arrive)"""
+    uid = S.Comm.unique_id()
+    out, err = [None, None], []
+
+    def work(rank):
+        try:
+            comm = S.Comm(uid, 2, rank, rank)
+            try:
+                out[rank] = fn(comm)
+            finally:
+                comm.destroy()
+        except Exception as e:  # noqa: BLE001
+            err.append(e)
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(timeout=300)
+    assert not err, err
+    return out
+
+
+def test_run_rank_two_gpus_equals_one(S, table):
+    if _n_gpus(S) < 2:
+        pytest.skip("needs 2 GPUs")
+    for mode in ("gaussian", "bootstrap", "sobol_bootstrap"):
+        kw = mode_kwargs(mode, table)
+        N, P = 1_000_003, 24
+        one = S.simulate(mode, N, P, hist_bins=64, want_finals=True, **kw)
+        res = _two_rank_job(S, lambda c: (c.simulate(mode, N, P, hist_bins=64, want_finals=True, **kw), c.quantiles(mode, N, P, **kw)))
+        for r, q in res:
+            assert r.count == N and r.below_count == one.below_count and np.array_equal(r.hist, one.hist)
+            assert abs(r.mean - one.mean) <= 1e-12 * abs(one.mean) and abs(r.m2 - one.m2) <= 1e-9 * abs(one.m2)
+            assert np.array_equal(q, np.sort(one.finals)[S.quartile_ranks(N)])
+        assert np.array_equal(np.concatenate([res[0][0].finals, res[1][0].finals]), one.finals)  # ranks own disjoint ranges
+
+
+def test_run_multi_merges_on_the_devices(S, table):
+    if _n_gpus(S) < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch
+    before = torch.cuda.current_device()
+    for mode in ALL_MODES:
+        kw = mode_kwargs(mode, table)
+        one = S.simulate(mode, 600_001, 24, hist_bins=64, want_block_partials=True, **kw)
+        two = S.simulate(mode, 600_001, 24, hist_bins=64, want_block_partials=True, n_gpus=2, **kw)
+        assert two.count == one.count and two.below_count == one.below_count and np.array_equal(two.hist, one.hist)
+        assert np.array_equal(two.block_means, one.block_means)
+        assert abs(two.mean - one.mean) <= 1e-12 * abs(one.mean)
+        assert np.array_equal(S.quantiles(mode, 600_001, 24, n_gpus=2, **kw), S.quantiles(mode, 600_001, 24, **kw))
+    assert torch.cuda.current_device() == before  # the device guard restores the caller's device
+
+
+# ---- order statistics in two replays ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ALL_MODES)
+def test_third_select_pass_reads_candidates_not_a_replay(S, table, mode):
+    kw = mode_kwargs(mode, table)
+    N, P = 2_000_000, 120
+    fin = np.sort(S.simulate(mode, N, P, want_finals=True, **kw).finals)
+    ranks = [0, 1, N // 4, N // 2, N // 2 + 1, 3 * (N // 4), N - 2, N - 1]
+    q, ms = S.quantiles(mode, N, P, ranks=ranks, return_ms=True, **kw)
+    assert np.array_equal(q, fin[ranks])
+    t = S.kernel_times(0, 3)  # the three passes of that call
+    assert t[2] < 0.25 * t[1], t  # pass 3 is an HBM pass over the candidates, not a third simulation
+    try:
+        S.set_variant("select_candidates", 0)
+        q0, ms0 = S.quantiles(mode, N, P, ranks=ranks, return_ms=True, **kw)
+        t0 = S.kernel_times(0, 3)
+    finally:
+        S.set_variant()
+    assert np.array_equal(q0, q) and t0[2] > 0.5 * t0[1] and ms < 0.8 * ms0
+
+
+def test_candidate_buffer_is_never_reused_for_another_run(S, table):
+    """pass-by-pass protocol with an unrelated run in between: the fingerprint check must force a replay"""
+    cfg_a, keep_a = S.make_config("gaussian", 300_000, 60, seed=1)
+    cfg_b, keep_b = S.make_config("gaussian", 300_000, 60, seed=2)
+    fin_a = np.sort(S.simulate("gaussian", 300_000, 60, seed=1, want_finals=True).finals)
+    fin_b = np.sort(S.simulate("gaussian", 300_000, 60, seed=2, want_finals=True).finals)
+    ranks = S.quartile_ranks(300_000)
+    sa, sb = S.SelectState(ranks), S.SelectState(ranks)
+    for _ in range(2):  # passes 1 and 2 of both runs, interleaved: B's second pass overwrites A's candidates
+        sa.advance(sa.run_pass(cfg_a))
+        sb.advance(sb.run_pass(cfg_b))
+    sa.advance(sa.run_pass(cfg_a))  # A's third pass: candidates belong to B -> replay
+    sb.advance(sb.run_pass(cfg_b))  # B's third pass: A's replay invalidated the buffer -> replay
+    assert np.array_equal(sa.values(), fin_a[ranks]) and np.array_equal(sb.values(), fin_b[ranks])
+
+
+# ---- two streams, one cached workspace ------------------------------------------------------------------
+def test_two_streams_share_the_cached_workspace(S, table):
+    import torch
+    dev = torch.device("cuda", 0)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    tbl = torch.from_numpy(table).to(dev)
+    bins = 32
+    runs = []
+    for i in range(12):
+        mode = ("gaussian", "bootstrap", "sobol_gaussian", "bootstrap_compat")[i % 4]
+        stats = torch.zeros(S.stats_len(bins), dtype=torch.float64, device=dev)
+        st = (s1, s2)[i % 2]
+        kw = dict(returns_ptr=tbl.data_ptr(), n_returns=table.size) if "bootstrap" in mode else {}
+        seed = 0 if mode == "bootstrap_compat" else 100 + i
+        S.simulate_device(mode, 400_000 + 1000 * i, 30 + i, stats.data_ptr(), seed=seed, hist_bins=bins, stream=st.cuda_stream, **kw)
+        runs.append((mode, 400_000 + 1000 * i, 30 + i, seed, stats))
+    torch.cuda.synchronize()
+    for mode, n, p, seed, stats in runs:
+        got = S.finalize_stats(stats.cpu().numpy(), bins, 1000.0)
+        ref = S.simulate(mode, n, p, seed=seed, hist_bins=bins, returns=table if "bootstrap" in mode else None)
+        assert (got.count, got.below_count, got.mean, got.m2) == (ref.count, ref.below_count, ref.mean, ref.m2), mode
+        assert np.array_equal(got.hist, ref.hist)
+
+
+def test_withdrawal_schedules_change_between_async_launches(S):
+    """the schedule upload is versioned (no stream sync): back-to-back NO_SYNC launches with different schedules"""
+    import torch
+    st = torch.cuda.current_stream()
+    outs = []
+    for k in range(7):
+        sched = np.full(24, 0.1 * k, dtype=np.float32)
+        stats = torch.zeros(S.stats_len(0), dtype=torch.float64, device="cuda")
+        S.simulate_device("gaussian", 200_000, 24, stats.data_ptr(), seed=4, stream=st.cuda_stream, withdraw_pct_schedule=sched)
+        outs.append((sched, stats))
+    torch.cuda.synchronize()
+    for sched, stats in outs:
+        got = S.finalize_stats(stats.cpu().numpy(), 0, 1000.0)
+        ref = S.simulate("gaussian", 200_000, 24, seed=4, withdraw_pct_schedule=sched)
+        assert (got.mean, got.m2) == (ref.mean, ref.m2)
+
+
+# ---- validation ---------------------------------------------------------------------------------------------------------------
+def test_non_finite_inputs_are_rejected(S, table):
+    bad = table.copy()
+    bad[17] = np.nan
+    for mode in EXACT_MODES:
+        with pytest.raises(S.SmmcError) as e:
+            S.simulate(mode, 1000, 12, returns=bad)
+        assert e.value.status == 1 and "returns[17]" in str(e.value)
+    for kw in (dict(gauss_mean=float("nan")), dict(gauss_std=float("inf")), dict(initial_capital=float("nan"))):
+        with pytest.raises(S.SmmcError) as e:
+            S.simulate("gaussian", 1000, 12, **kw)
+        assert e.value.status == 1
+
+
+def test_sorted_table_kernel_places_every_entry_with_nans(S, table):
+    """device-pointer tables are not scanned on the host: the rank sort must still be a permutation (total order on keys)"""
+    import torch
+    t = table.copy()
+    t[5] = np.nan
+    d = torch.from_numpy(t).cuda()
+    stats = torch.zeros(S.stats_len(0), dtype=torch.float64, device="cuda")
+    S.simulate_device("sobol_bootstrap", 4096, 4, stats.data_ptr(), returns_ptr=d.data_ptr(), n_returns=t.size, seed=1,
+                      stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert S.finalize_stats(stats.cpu().numpy(), 0, 1000.0).count == 4096  # ran to completion; NaN paths are the caller's
+
+
+def test_debug_draws_validates_the_paths_asked_for(S, table):
+    with pytest.raises(S.SmmcError) as e:
+        S.debug_draws("bootstrap_compat", 1000, 4, returns=table, stream_offset=(1 << 31) - 512)
+    assert e.value.status == 1
+
+
+# ---- the remaining reference callers, relinked (VERDICT r1 "what's missing" 3) -------------------------------------------------
+def test_reduce_mean_and_vector_add_examples_relinked(S, tmp_path):
+    """examples/benchmark_reduce_mean.cpp (caller of reduce_mean_gpu, :38) and examples/example_gpu.cpp (caller of
+    vector_add_gpu, :29-32): the reference's sources untouched, linked against libsmmc.so (oracle/Makefile relink)"""
+    import os
+    import re
+    from test_gpu_parity import ROOT, _run_relinked
+    exe_rm = os.path.join(ROOT, "oracle", "_ref", "benchmark_reduce_mean")
+    exe_va = os.path.join(ROOT, "oracle", "_ref", "example_gpu")
+    if not (os.path.exists(exe_rm) and os.path.exists(exe_va)):
+        pytest.skip("relinked reference examples did not travel with the snapshot (make -C oracle relink)")
+    n = 3_000_001
+    out = _run_relinked(tmp_path, exe_rm, [n], np.zeros(1, dtype=np.float32))
+    m = re.search(r"mean_cpu: ([\d.,]+) \| mean_gpu: ([\d.,]+)", out)
+    assert m, out[-500:]
+    cpu, gpu = (float(x.replace(",", "")) for x in m.groups())
+    exact = np.arange(n, dtype=np.float32).astype(np.float64).mean()  # vec[i] = float(i), examples/benchmark_reduce_mean.cpp:22-23
+    assert abs(gpu - exact) <= 0.006 and abs(cpu - exact) <= 1.0  # printed with 2 decimals; the GPU mean is the fp64-exact one
+    out = _run_relinked(tmp_path, exe_va, [1000], np.zeros(1, dtype=np.float32))
+    vals = re.findall(r"[-\d.]+", out[out.index("["):])
+    assert len(vals) == 1000 and all(v == "3.000" for v in vals)  # 1.0f + 2.0f, print_vector's {:6.3f}
