@@ -52,15 +52,18 @@ UNIT = "path-months/s"
 # fields / 8 normals per call and need 12, so the fraction below stays an issue-slot utilisation (<= 1).  The
 # SURVEY-budget fraction is reported next to it as `frac_survey_budget`.
 I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstrap": 6, "sobol_gaussian": 9}
+# Philox4x32-7 (smmc_config.philox_rounds = 7): three rounds = 6 IMAD.WIDE + 6 LOP3 less per call of 6 / 8 months
+I_ALG_PHILOX7 = {"bootstrap": 12 - 12 / 6.0, "gaussian": 12 - 12 / 8.0}
 # Pipe floors (cycles per warp-month per SM sub-partition) from the measured reciprocal throughputs in
-# profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the binding
-# resource of these instruction mixes is a pipe, not the issue slot.
-#   gaussian, sobol_gaussian   2 MUFU per normal x 8.0 cycles (XU, 4 lanes/clk per sub-partition): both are
-#              Box-Muller pairs (sobol_gaussian: point 2 + pair {2 I2FP, FFMA, LG2, FMUL, SQRT, FMUL, FMUL.RZ, SIN, COS,
-#              2 FFMA, 2 FMUL}/2 = 7 -> I_alg 9)
+# profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the busiest single pipe
+# of the shipped instruction mix.  (The minimal-count recipes behind I_ALG are the all-MUFU ones; the shipped Gaussian
+# kernels trade MUFU for a few more FMA/ALU instructions, so I_ALG is NOT raised for them.)
+#   gaussian   pairs 0 and 2 of a call take sin/cos from the shared-memory table: (2 x 4 + 2 x 2) MUFU x 8.0 / 8 months = 12.0 on
+#              the XU pipe; Philox keeps fmaheavy at 9.0 and the ALU pipe at 8.5 -- no single pipe binds (ncu: XU 65 %, issue 72 %)
+#   sobol_gaussian  every pair from the table: XU 8.0; the ALU pipe carries 10 instructions per pair x 2.0 cycles = 10.0
 #   bootstrap  Philox: 8 per-lane rounds x 8.39 cycles (2 IMAD.WIDE + 2 LOP3, measured as a unit) per 6 months,
 #              + 16 further ALU-pipe instructions per call (fields, addresses) at their measured marginal 2.0 cycles
-PIPE_FLOOR = {"gaussian": ("xu", 16.0), "sobol_gaussian": ("xu", 16.0),
+PIPE_FLOOR = {"gaussian": ("xu", 12.0), "sobol_gaussian": ("alu", 10.0),
               "bootstrap": ("fmaheavy+alu (Philox)", (8 * 8.39 + 16 * 2.0) / 6.0)}
 I_ALG_SURVEY = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": None, "sobol_gaussian": None}
 
@@ -258,7 +261,7 @@ def run_reduce_mean(args):
         S.reduce_mean_gpu(h, h.size)
     e2e_s = (time.perf_counter() - t0) / 3
     peaks = measured_peaks()
-    peak = float(peaks.get("hbm_gbs") or 6400.0)
+    peak = float(peaks.get("hbm_gbs") or 6650.0)
     k_ms = sum(ms) / len(ms)
     gbs = 4.0 * n / (k_ms * 1e-3) / 1e9
     line = {
@@ -269,9 +272,9 @@ def run_reduce_mean(args):
                    "l2": "two 1 GiB buffers alternate between steps: every step reads from HBM"},
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                      "traffic": ncu_traffic("reduce_mean") if n == (1 << 28) else None, "algorithmic_bytes": 4 * n,
-                     "kernel": "smmc::reduce_sum_kernel", "kernel_ms": k_ms, "bytes_per_element": 4,
+                     "kernel": "smmc::reduce_sum_tma_kernel" if n >= 148 * 2 * 4 * 8192 else "smmc::reduce_sum_kernel", "kernel_ms": k_ms, "bytes_per_element": 4,
                      "peak_source": ("MEASURED_PEAKS.json hbm_gbs (copy: read + write bytes)" if peaks.get("hbm_gbs")
-                                     else "fallback 6400 GB/s (B200_PROFILING.md)")},
+                                     else "fallback 6650 GB/s (B200_PROFILING.md)")},
         "e2e": {"value": h.size / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(h.nbytes), "d2h_bytes_per_step": 8,
                 "api": "reduce_mean_gpu(host vector) -> smmc_reduce_mean: pageable H2D + kernel"},
         "gpu_launches": steps, "clocks": clocks, "result": {"exact": bool(ok)},
@@ -310,7 +313,7 @@ def run_vector_add(args):
         S.vector_add_gpu(ho, ha, hb, ha.size)
     e2e_s = (time.perf_counter() - t0) / 3
     peaks = measured_peaks()
-    peak = float(peaks.get("hbm_gbs") or 6400.0)
+    peak = float(peaks.get("hbm_gbs") or 6650.0)
     k_ms = sum(ms) / len(ms)
     gbs = 12.0 * n / (k_ms * 1e-3) / 1e9
     line = {
@@ -322,13 +325,168 @@ def run_vector_add(args):
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                      "traffic": ncu_traffic("vector_add") if n == (1 << 27) else None, "algorithmic_bytes": 12 * n, "kernel": "smmc::vector_add_kernel", "kernel_ms": k_ms, "bytes_per_element": 12,
                      "peak_source": ("MEASURED_PEAKS.json hbm_gbs (copy: read + write bytes)" if peaks.get("hbm_gbs")
-                                     else "fallback 6400 GB/s (B200_PROFILING.md)")},
+                                     else "fallback 6650 GB/s (B200_PROFILING.md)")},
         "e2e": {"value": ha.size / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(2 * ha.nbytes),
                 "d2h_bytes_per_step": int(ha.nbytes), "api": "vector_add_gpu(host arrays) -> smmc_vector_add: pageable H2D x2 + kernel + D2H"},
         "gpu_launches": steps, "clocks": clocks, "result": {"exact": ok},
     }
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ---- extras: every other claim of the build, device-timed in the same driver-run process (outside the headline's region) ---
+def issue_peak(torch, dev):
+    peaks = measured_peaks()
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    return n_sm * 128 * float(peaks.get("sm_max_mhz") or 1965.0) * 1e6, n_sm
+
+
+def short_leg(torch, S, name, dev, local, warm=3, steps=5, philox_rounds=0, with_e2e=False):
+    """3 warm-up + 5 timed steps of workload `name` on one GPU: value from CUDA events around every step on the launching
+    stream, kernel_ms from the library's own event pairs, issue-roofline fraction; fresh RNG offsets every step."""
+    wl = WORKLOADS[name]
+    mode, B, P = wl["mode"], wl["paths"], wl["periods"]
+    table = S.synthetic_sp500_table(1200) if "bootstrap" in mode else None
+    table_dev = torch.from_numpy(table).to(dev) if table is not None else None
+    seed = 0 if mode == "bootstrap_compat" else 1234
+    nb = (B + 255) // 256
+    stats = torch.zeros(S.stats_len(HIST_BINS), dtype=torch.float64, device=dev)
+    bm = torch.empty(nb, dtype=torch.float32, device=dev) if wl["block_partials"] else None
+    bv = torch.empty(nb, dtype=torch.float32, device=dev) if wl["block_partials"] else None
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    span = (1 << 31) - 256 - B if mode == "bootstrap_compat" else ((1 << 32) - 512 - B if mode.startswith("sobol") else 1 << 62)
+
+    def off(i):
+        return ((7_000 + i) * B % max(span, 1)) // 256 * 256
+
+    def step(i):
+        return S.simulate_device(mode, B, P, stats.data_ptr(), initial_capital=V0, seed=seed, stream_offset=off(i),
+                                 returns_ptr=table_dev.data_ptr() if table_dev is not None else None,
+                                 n_returns=table.size if table is not None else 0, hist_bins=HIST_BINS, hist_range=wl["hist_range"],
+                                 block_means_ptr=bm.data_ptr() if bm is not None else None,
+                                 block_vars_ptr=bv.data_ptr() if bv is not None else None, device=local, stream=stream.cuda_stream,
+                                 philox_rounds=philox_rounds, **GAUSS)
+
+    for i in range(warm):
+        step(i)
+        flush.zero_()
+    torch.cuda.synchronize(dev)
+    sampler = ClockSampler([local])
+    sampler.begin()
+    ev, launches = [], 0
+    for i in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        launches += step(warm + i)
+        b.record(stream)
+        flush.zero_()
+        ev.append((a, b))
+    torch.cuda.synchronize(dev)
+    sampler.end()
+    clocks = sampler.stop()
+    ms = [a.elapsed_time(b) for a, b in ev]
+    k_ms = float(np.mean(S.kernel_times(local, steps)))
+    peak, _ = issue_peak(torch, dev)
+    i_alg = I_ALG_PHILOX7[mode] if philox_rounds == 7 else I_ALG[mode]
+    fin = S.finalize_stats(stats.cpu().numpy(), HIST_BINS, V0)
+    leg = {"workload": wl["desc"] + (" [philox_rounds=7]" if philox_rounds == 7 else ""), "mode": mode, "paths": B, "periods": P,
+           "value": B * P * steps / (sum(ms) * 1e-3), "unit": UNIT, "ms_per_step": sum(ms) / steps, "kernel_ms": k_ms,
+           "steps": steps, "warmup": warm, "gpu_launches": launches,
+           "roofline": {"bound": "issue", "i_alg": i_alg, "frac": B * P * i_alg / (k_ms * 1e-3) / peak},
+           "sm_mhz": clocks.get("sm_mhz"), "clock_reasons": clocks.get("reasons"),
+           "result": {"mean": fin.mean, "std": fin.std, "p_below_target": fin.p_below_target}}
+    if mode in PIPE_FLOOR and philox_rounds != 7:
+        leg["roofline"]["pipe_floor_frac"] = B * P * PIPE_FLOOR[mode][1] / peak * 1e3 / k_ms
+    if with_e2e:  # through the host-buffer entry point: the table really is copied H2D every step
+        kw = dict(initial_capital=V0, returns=table, seed=seed, hist_bins=HIST_BINS, hist_range=wl["hist_range"],
+                  want_block_partials=wl["block_partials"], device=local, philox_rounds=philox_rounds, **GAUSS)
+        for i in range(2):
+            S.simulate(mode, B, P, stream_offset=off(100 + i), **kw)
+        t0 = time.perf_counter()
+        for i in range(steps):
+            S.simulate(mode, B, P, stream_offset=off(200 + i), **kw)
+        dt = time.perf_counter() - t0
+        leg["e2e"] = {"value": B * P * steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
+                      "d2h_bytes_per_step": int(S.stats_len(HIST_BINS) * 8 + (2 * nb * 4 if wl["block_partials"] else 0))}
+    del flush
+    return leg
+
+
+def hbm_leg(torch, S, which, dev, local, steps=200):
+    """reduce_mean_gpu / vector_add_gpu over device-resident vectors larger than L2: GB/s against MEASURED_PEAKS.json hbm_gbs"""
+    peaks = measured_peaks()
+    peak = float(peaks.get("hbm_gbs") or 6650.0)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    if which == "reduce_mean":
+        n, bpe = 1 << 28, 4
+        bufs = [torch.full((n,), 1.0 + 0.25 * i, dtype=torch.float32, device=dev) for i in range(2)]  # alternate: 2 GiB > L2
+        for i in range(3):
+            S.reduce_mean_device(bufs[i & 1].data_ptr(), n, device=local, stream=stream)
+        ms, ok = [], True
+        for i in range(steps):
+            m, k = S.reduce_mean_device(bufs[i & 1].data_ptr(), n, device=local, stream=stream)
+            ok = ok and (m == 1.0 + 0.25 * (i & 1))
+            ms.append(k)
+        kernel = "smmc::reduce_sum_tma_kernel"
+    else:
+        n, bpe = 1 << 27, 12
+        a = torch.full((n,), 1.25, dtype=torch.float32, device=dev)
+        b = torch.full((n,), 2.5, dtype=torch.float32, device=dev)
+        out = torch.empty_like(a)
+        for _ in range(3):
+            S.vector_add_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, device=local, stream=stream)
+        ms = [S.vector_add_device(out.data_ptr(), a.data_ptr(), b.data_ptr(), n, device=local, stream=stream) for _ in range(steps)]
+        ok = bool(torch.all(out == 3.75).item())
+        kernel = "smmc::vector_add_kernel"
+    k_ms = float(np.mean(ms))
+    gbs = bpe * n / (k_ms * 1e-3) / 1e9
+    return {"workload": f"{which}_gpu over {n} device-resident floats", "value": n / (k_ms * 1e-3), "unit": "elements/s", "kernel_ms": k_ms,
+            "steps": steps, "exact": bool(ok),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "bytes_per_element": bpe,
+                         "kernel": kernel, "traffic": ncu_traffic(which),
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks.get("hbm_gbs") else "fallback 6650 GB/s (B200_PROFILING.md)"}}
+
+
+def ref_gpu_same_box(S):
+    """The reference's own kernels (src/simulations.cu unmodified, compiled for sm_100a into oracle/_ref/libref_gpu.so) through its
+    own entry points at 10^8 x 360 on the 1127-entry table, next to this build's BOOTSTRAP_COMPAT on the same inputs (bit-identical
+    results, tests/test_gpu_parity.py).  A baseline leg like cpu_baseline: the only place bench.py runs the reference's GPU code."""
+    from oracle import binding as O
+    if not O.ref_available("libref_gpu.so"):
+        return {"unavailable": "oracle/_ref/libref_gpu.so did not travel with the snapshot"}
+    N, P = 100_000_000, 360
+    table = S.synthetic_sp500_table(1127, seed=7)
+
+    def best(fn, reps=3):
+        fn()
+        ts, extra = [], None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            extra = fn()
+            ts.append(time.perf_counter() - t0)
+        return min(ts), extra
+
+    out = {"paths": N, "periods": P, "n_returns": 1127, "unit": UNIT,
+           "how": "wall clock around the blocking entry point, best of 3 after one warm-up call; reference_own_kernel_clock = the "
+                  "reference library's 'GPU kernel itself took' line (host steady_clock, 1 ms resolution, src/simulations.cu:463)"}
+    t, _ = best(lambda: O.ref_mc_simulations_gpu_reduceBlock(N, P, V0, table))
+    k = O.ref_gpu_last_kernel_seconds()
+    out["reference_reduceBlock"] = {"wall_ms": 1e3 * t, "value": N * P / t, "reference_own_kernel_clock_ms": 1e3 * k if k > 0 else None,
+                                    "value_by_own_kernel_clock": N * P / k if k > 0 else None}
+    t, _ = best(lambda: O.ref_mc_simulations_gpu(N, P, V0, table), reps=2)
+    out["reference_all_finals"] = {"wall_ms": 1e3 * t, "value": N * P / t}
+    t, r = best(lambda: S.simulate("bootstrap_compat", N, P, returns=table, want_block_partials=True))
+    out["this_build_compat_block_partials"] = {"wall_ms": 1e3 * t, "value": N * P / t, "kernel_ms": r.device_ms, "value_kernel": N * P / (r.device_ms * 1e-3)}
+    t, r = best(lambda: S.simulate("bootstrap_compat", N, P, returns=table, want_finals=True))
+    out["this_build_compat_all_finals"] = {"wall_ms": 1e3 * t, "value": N * P / t, "device_span_ms": r.device_ms,
+                                           "how": "smmc_run, host buffers: chunked launches, D2H and host copy-out pipelined"}
+    return out
+
+
+def hist_sha256(hist):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(np.asarray(hist, dtype=np.uint64)).tobytes()).hexdigest()
 
 
 # ---- the GPU arm --------------------------------------------------------------------------------------------------
@@ -342,6 +500,8 @@ def main():
     ap.add_argument("--paths", type=int, default=0, help="override paths per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extras legs (other workloads, C5, same-box reference kernels)")
+    ap.add_argument("--no-c5", action="store_true")
     args = ap.parse_args()
     if args.workload == "reduce_mean":
         return run_reduce_mean(args)
@@ -360,7 +520,6 @@ def main():
     import torch
     import torch.distributed as dist
     import stock_market_monte_carlo_b200 as S
-    from stock_market_monte_carlo_b200.distributed import allreduce_stats
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -369,19 +528,24 @@ def main():
         raise SystemExit("bench.py needs a B200 per rank: the product has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    comm = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if not os.environ.get("SMMC_KEEP_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout: keep the JSON line alone there
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL's communicator lines are evidence (rank count, transport): keep them, but on stderr so that the JSON line
+        # stays alone on stdout.  libsmmc.so additionally prints one "rank r nranks N cudaDev d" line per rank to stderr.
+        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=dev)  # launcher plumbing: barrier + max-over-ranks of the timings
+        from stock_market_monte_carlo_b200.distributed import init_comm
+        comm = init_comm(local)  # the path's own communicator: ncclCommInitRank inside libsmmc.so (smmc_run_rank)
 
     mode, B, P = wl["mode"], wl["paths"], wl["periods"]
     strong = bool(wl.get("strong"))
     job_paths = B if strong else world * B  # paths of one step over all ranks
-    if strong:  # B = this rank's shard of the fixed global run (whole 256-path blocks, distributed.shard_range)
-        from stock_market_monte_carlo_b200.distributed import shard_range
-        total_paths = B
-        shard_off, B = shard_range(total_paths, rank, world)
+    # one step = ONE global run of job_paths paths, sharded over the ranks by RNG offset inside smmc_run_rank (whole 256-path
+    # blocks per rank); B = this rank's share of it
+    _, B = S.rank_range(job_paths, world, rank)
     nb = (B + 255) // 256
     table = S.synthetic_sp500_table(1200) if "bootstrap" in mode else None
     seed = 0 if mode == "bootstrap_compat" else 1234
@@ -397,22 +561,21 @@ def main():
     stream = torch.cuda.current_stream(dev)
 
     def offset_of(step):
-        if sobol or mode == "bootstrap_compat":  # 32-bit point / path ids: wrap the offsets, still disjoint per rank
-            span = (1 << 31) - 256 - B if mode == "bootstrap_compat" else (1 << 32) - 512 - B
-            return (((step * world + rank) * B) % max(span, 1)) // 256 * 256
-        if strong:
-            return step * total_paths + shard_off
-        return (step * world + rank) * B
+        """stream offset of the GLOBAL run of this step (fresh, disjoint streams every step)"""
+        if sobol or mode == "bootstrap_compat":  # 32-bit point / path ids: wrap the offsets
+            span = (1 << 31) - 256 - job_paths if mode == "bootstrap_compat" else (1 << 32) - 512 - job_paths
+            return ((step * job_paths) % max(span, 1)) // 256 * 256
+        return step * ((job_paths + 255) // 256 * 256)
+
+    dev_kw = dict(initial_capital=V0, seed=seed, returns_ptr=table_dev.data_ptr() if table_dev is not None else None,
+                  n_returns=table.size if table is not None else 0, hist_bins=HIST_BINS, hist_range=wl["hist_range"],
+                  block_means_ptr=bmeans.data_ptr() if bmeans is not None else None,
+                  block_vars_ptr=bvars.data_ptr() if bvars is not None else None, stream=stream.cuda_stream, **GAUSS)
 
     def device_step(step):
-        n = S.simulate_device(mode, B, P, stats.data_ptr(), initial_capital=V0, seed=seed, stream_offset=offset_of(step),
-                              returns_ptr=table_dev.data_ptr() if table_dev is not None else None,
-                              n_returns=table.size if table is not None else 0, hist_bins=HIST_BINS,
-                              hist_range=wl["hist_range"], block_means_ptr=bmeans.data_ptr() if bmeans is not None else None,
-                              block_vars_ptr=bvars.data_ptr() if bvars is not None else None, device=local,
-                              stream=stream.cuda_stream, **GAUSS)
-        allreduce_stats(stats)
-        return n
+        if comm is not None:  # kernel -> ncclAllReduce of the statistics vector, both enqueued by smmc_run_rank on this stream
+            return comm.simulate_device(mode, job_paths, P, stats.data_ptr(), stream_offset=offset_of(step), **dev_kw)
+        return S.simulate_device(mode, B, P, stats.data_ptr(), stream_offset=offset_of(step), device=local, **dev_kw)
 
     def barrier():
         if world > 1:
@@ -455,17 +618,13 @@ def main():
     if not args.no_e2e:
         k_e2e = min(args.steps, 50)
 
+        host_kw = dict(initial_capital=V0, returns=table, seed=seed, hist_bins=HIST_BINS, hist_range=wl["hist_range"],
+                       want_block_partials=wl["block_partials"], **GAUSS)
+
         def host_step(step):
-            r = S.simulate(mode, B, P, initial_capital=V0, returns=table, seed=seed, stream_offset=offset_of(step),
-                           hist_bins=HIST_BINS, hist_range=wl["hist_range"], want_block_partials=wl["block_partials"],
-                           device=local, **GAUSS)
-            if world > 1:  # merge the ranks' results: count / S1 / S2 / below / histogram through the same all-reduce
-                v = np.concatenate([[r.count, r.below_count, (r.mean - V0) * r.count,
-                                     r.m2 + r.count * (r.mean - V0) ** 2, 0.0, 0.0], r.hist.astype(np.float64)])
-                t = torch.from_numpy(v).to(dev)
-                allreduce_stats(t)
-                t.cpu()
-            return r
+            if comm is not None:  # smmc_run_rank with host buffers: table H2D, kernel, all-reduce, merged statistics + partials D2H
+                return comm.simulate(mode, job_paths, P, stream_offset=offset_of(step), **host_kw)
+            return S.simulate(mode, B, P, stream_offset=offset_of(step), device=local, **host_kw)
 
         for s in range(3):
             host_step(10_000 + s)
@@ -480,22 +639,82 @@ def main():
         e2e = {"value": job_paths * P * k_e2e / float(dt.item()), "unit": UNIT,
                "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
                "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
-               "steps": k_e2e, "api": "stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)",
+               "steps": k_e2e, "api": ("stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)" if comm is None else
+                                       "Comm.simulate -> smmc_run_rank (host buffers, blocking; ncclAllReduce inside the C ABI)"),
                "inputs": ("return table copied host->device every step" if table is not None else
                           "none to copy: the Gaussian modes take scalars only (mean, std, seed, offset)")}
 
-    # ---- SURVEY 8(f) rank 1, reported next to the headline (outside the timed region): the quartiles of the same
-    # workload by three replays (radix select in shared memory) instead of a finals download + host sort
-    extras = None
-    if world == 1 and not args.no_e2e and not sobol:
+    # ---- extras (outside the timed region).  SURVEY 8(f) rank 1: the quartiles of the same workload by replay radix select
+    # (two replays + one pass over the candidate keys) instead of a finals download + host sort
+    extras = {}
+    do_extras = not args.no_e2e and not args.no_extras
+    if world == 1 and do_extras and not sobol:
         q, q_ms = S.quantiles(mode, B, P, initial_capital=V0, returns=table, seed=seed, device=local, return_ms=True, **GAUSS)
         _, q_f, q_extra_ms = S.simulate_with_quantiles(mode, B, P, initial_capital=V0, returns=table, seed=seed, device=local,
                                                        hist_bins=HIST_BINS, hist_range=wl["hist_range"], target=V0,
                                                        want_block_partials=wl["block_partials"], **GAUSS)
-        extras = {"quartiles_min_q1_med_q3_max": [float(x) for x in q], "quartiles_device_ms": q_ms,
-                  "quartiles_how": "smmc_quantiles: 3 replays of the workload, 11+11+10-bit radix select on ordered keys; exact",
-                  "quartiles_riding_along_extra_ms": q_extra_ms, "quartiles_riding_along_equal": bool(np.array_equal(q, q_f)),
-                  "quartiles_riding_along_how": "smmc_run_select: the first select pass shares the statistics launch; 2 extra replays"}
+        extras.update({"quartiles_min_q1_med_q3_max": [float(x) for x in q], "quartiles_device_ms": q_ms,
+                       "quartiles_how": "smmc_quantiles: 2 replays of the workload (11 + 11 key bits; the second also collects the "
+                                        "candidate keys) + one HBM pass over the candidates (10 bits); exact",
+                       "quartiles_riding_along_extra_ms": q_extra_ms, "quartiles_riding_along_equal": bool(np.array_equal(q, q_f)),
+                       "quartiles_riding_along_how": "smmc_run_select: the first select pass shares the statistics launch; "
+                                                     "1 extra replay + the candidate pass"})
+
+    # ---- C5 (BASELINE config 5): ONE run of 10^10 paths x 360 months sharded over the ranks (strong scaling), two steps; the
+    # histogram hash of the step at stream offset 0 must be the same string for every number of GPUs
+    if do_extras and args.workload == "c2" and not args.no_c5:
+        c5 = WORKLOADS["c5"]
+        Nc5, Pc5 = c5["paths"], c5["periods"]
+        st5 = torch.zeros(slen, dtype=torch.float64, device=dev)
+        kw5 = dict(initial_capital=V0, seed=1234, hist_bins=HIST_BINS, hist_range=c5["hist_range"], stream=stream.cuda_stream, **GAUSS)
+
+        def c5_step(i):
+            if comm is not None:
+                comm.simulate_device("gaussian", Nc5, Pc5, st5.data_ptr(), stream_offset=i * Nc5, **kw5)
+            else:
+                S.simulate_device("gaussian", Nc5, Pc5, st5.data_ptr(), stream_offset=i * Nc5, device=local, **kw5)
+
+        barrier()
+        ev5, res5 = [], None
+        for i in (1, 0):  # the second (reported) step is the run at offset 0
+            a5, b5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a5.record(stream)
+            c5_step(i)
+            b5.record(stream)
+            ev5.append((a5, b5))
+        barrier()
+        ms5 = torch.tensor([sum(a5.elapsed_time(b5) for a5, b5 in ev5)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms5, op=dist.ReduceOp.MAX)
+        res5 = S.finalize_stats(st5.cpu().numpy(), HIST_BINS, V0)
+        mu, sg = GAUSS["gauss_mean"] * 0.01, GAUSS["gauss_std"] * 0.01
+        cf_mean = V0 * (1.0 + mu) ** Pc5  # E[V] = V0 (1+mu)^P, E[V^2] = V0^2 ((1+mu)^2 + sigma^2)^P (RNG-independent)
+        cf_std = (V0 ** 2 * ((1.0 + mu) ** 2 + sg ** 2) ** Pc5 - cf_mean ** 2) ** 0.5
+        extras["c5"] = {"workload": c5["desc"], "scaling": "strong", "n_gpus": world, "paths": Nc5, "periods": Pc5, "steps": 2,
+                        "ms_per_step": float(ms5.item()) / 2, "value": 2.0 * Nc5 * Pc5 / (float(ms5.item()) * 1e-3), "unit": UNIT,
+                        "count": res5.count, "mean": res5.mean, "std": res5.std, "below_count": res5.below_count,
+                        "hist_sha256": hist_sha256(res5.hist),
+                        "closed_form": {"mean": float(cf_mean), "std": float(cf_std), "mean_rel_err": float(res5.mean / cf_mean - 1.0),
+                                        "std_rel_err": float(res5.std / cf_std - 1.0)},
+                        "collective": "1 ncclAllReduce per step inside smmc_run_rank" if world > 1 else "none"}
+
+    # ---- sharded == single: a 1 M-path run through the rank path against the same run on one GPU (rank 0 runs both)
+    if do_extras and world > 1:
+        Ns, Ps = 1_000_003, 120
+        kws = dict(initial_capital=V0, seed=77, hist_bins=HIST_BINS, hist_range=(0.0, 20000.0), **GAUSS)
+        sharded = comm.simulate("gaussian", Ns, Ps, **kws)
+        q_sh = comm.quantiles("gaussian", Ns, Ps, initial_capital=V0, seed=77, **GAUSS)
+        if rank == 0:
+            single = S.simulate("gaussian", Ns, Ps, device=local, **kws)
+            q_1 = S.quantiles("gaussian", Ns, Ps, initial_capital=V0, seed=77, device=local, **GAUSS)
+            extras["sharded_equals_single"] = {
+                "paths": Ns, "periods": Ps, "n_ranks": world,
+                "hist_identical": bool(np.array_equal(sharded.hist, single.hist)), "count_identical": sharded.count == single.count,
+                "below_identical": sharded.below_count == single.below_count,
+                "mean_rel_diff": abs(sharded.mean - single.mean) / abs(single.mean), "m2_rel_diff": abs(sharded.m2 - single.m2) / abs(single.m2),
+                "quartiles_identical": bool(np.array_equal(q_sh, q_1)),
+                "how": "Comm.simulate / Comm.quantiles (smmc_run_rank / smmc_quantiles_rank, NCCL inside the C ABI) vs smmc_run / smmc_quantiles on rank 0"}
+        barrier()
 
     if rank != 0:
         if world > 1:
@@ -535,6 +754,29 @@ def main():
         cpu_baseline = {"value": n * P / dt, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
                         "sample": f"{n} paths x {P} months in {dt:.1f} s; {cpu.desc}"}
 
+    # ---- extras: the other workloads, the HBM-bound kernels and the same-box reference kernels, each a short device-timed leg
+    if world == 1 and do_extras and args.workload == "c2":
+        del flush, bmeans, bvars
+        torch.cuda.empty_cache()
+        legs = {}
+        for name in ("c3", "c3compat", "c4", "c4boot"):
+            legs[name] = short_leg(torch, S, name, dev, local, with_e2e=(name == "c3"))
+        legs["c2_philox7"] = short_leg(torch, S, "c2", dev, local, philox_rounds=7)
+        legs["c3_philox7"] = short_leg(torch, S, "c3", dev, local, philox_rounds=7)
+        legs["reduce_mean"] = hbm_leg(torch, S, "reduce_mean", dev, local)
+        legs["vector_add"] = hbm_leg(torch, S, "vector_add", dev, local)
+        extras["workloads"] = legs
+        try:
+            extras["ref_gpu_same_box"] = ref_gpu_same_box(S)
+            rb = extras["ref_gpu_same_box"].get("reference_reduceBlock")
+            if rb:
+                for k in ("c3", "c3_philox7", "c3compat"):
+                    legs[k]["vs_ref_gpu_same_box"] = {"e2e_wall": legs[k]["value"] / rb["value"],
+                                                      "reference_own_kernel_clock": (legs[k]["value"] / rb["value_by_own_kernel_clock"]
+                                                                                     if rb.get("value_by_own_kernel_clock") else None)}
+        except Exception as e:  # the baseline leg must never take the headline down with it
+            extras["ref_gpu_same_box"] = {"unavailable": f"{type(e).__name__}: {e}"}
+
     value = job_paths * P * args.steps / (total_ms * 1e-3)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -542,12 +784,13 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "mode": mode, "paths_per_gpu_per_step": B, "periods": P, "seed": seed,
                    "hist_bins": HIST_BINS, "block_partials": wl["block_partials"], "parallelism": f"paths sharded by RNG offset x{world}",
-                   "collective": "1 all_reduce(SUM) of %d float64 per step (NCCL)" % slen if world > 1 else "none",
+                   "collective": ("1 ncclAllReduce(ncclFloat64, ncclSum) of %d doubles per step, enqueued by smmc_run_rank (C ABI) "
+                                  "on the kernel's stream" % slen) if world > 1 else "none",
                    "l2": "flushed between timed steps (256 MiB memset outside the event pairs); the path has no HBM input larger than 4.8 KB"},
         "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,
         "result": {"count": final.count, "mean": final.mean, "std": final.std, "p_below_target": final.p_below_target},
-        "extras": extras,
+        "extras": extras or None,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

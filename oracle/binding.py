@@ -288,3 +288,10 @@ def ref_mc_simulations_gpu_reduceBlock(n, n_periods, initial_capital, returns):
     if rc != 0:
         raise RuntimeError(f"reference GPU reduceBlock run failed rc={rc}")
     return means, variances
+
+
+def ref_gpu_last_kernel_seconds():
+    """the reference library's own "GPU kernel itself took X s" clock of the last ref_mc_simulations_gpu* call (1 ms steps)"""
+    lib = ref_lib("libref_gpu.so")
+    lib.ref_last_kernel_seconds.restype = C.c_double
+    return float(lib.ref_last_kernel_seconds())

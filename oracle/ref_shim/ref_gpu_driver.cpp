@@ -5,6 +5,7 @@
 // n_returns must be <= 1127.
 #include <atomic>
 #include <cstdio>
+#include <cstring>
 #include <vector>
 #include <unistd.h>
 #include <fcntl.h>
@@ -16,24 +17,49 @@ void mc_simulations_gpu_reduceBlock(std::atomic<long> &n_simulations, long max_n
                                     std::vector<float> &variances, int n_gpus);
 
 namespace {
-struct QuietStdout {
+// The reference library prints its own timing lines to stdout (src/simulations.cu:401, :463: "GPU kernel itself took X s!",
+// host steady_clock in whole milliseconds).  They are captured into a scratch file instead of reaching the caller's
+// stdout, and the kernel line is kept for ref_last_kernel_seconds().
+double g_last_kernel_s = -1.0;
+struct CaptureStdout {
   int saved = -1;
-  QuietStdout() {
+  FILE *tmp = nullptr;
+  CaptureStdout() {
     fflush(stdout);
     saved = dup(1);
-    int devnull = open("/dev/null", O_WRONLY);
-    dup2(devnull, 1);
-    close(devnull);
+    tmp = tmpfile();
+    if (tmp) {
+      dup2(fileno(tmp), 1);
+    } else {
+      int devnull = open("/dev/null", O_WRONLY);
+      dup2(devnull, 1);
+      close(devnull);
+    }
   }
-  ~QuietStdout() {
+  ~CaptureStdout() {
     fflush(stdout);
     dup2(saved, 1);
     close(saved);
+    g_last_kernel_s = -1.0;
+    if (tmp) {
+      rewind(tmp);
+      char line[512];
+      while (fgets(line, sizeof line, tmp)) {
+        double v = 0.0;
+        const char *p = strstr(line, "GPU kernel itself took ");
+        if (p && sscanf(p, "GPU kernel itself took %lf s", &v) == 1) g_last_kernel_s = v;
+      }
+      fclose(tmp);
+    }
   }
 };
+typedef CaptureStdout QuietStdout;
 }  // namespace
 
 extern "C" {
+// seconds of the last "GPU kernel itself took" line the reference printed (1 ms resolution), -1 if none
+double ref_last_kernel_seconds(void) { return g_last_kernel_s; }
+
 int ref_mc_simulations_gpu(long N, int n_periods, float initial_capital, const float *returns, int n_returns,
                            float *totals, int n_gpus) {
   if (n_returns > 1127) return 1;

@@ -253,7 +253,7 @@ def test_c5_size_ten_billion_paths_closed_form_moments(S):
     assert r.count == N and int(r.hist.sum()) == N
     se_rel = np.sqrt(var / N) / mean                       # 1.6e-6
     assert abs(r.mean - mean) / mean < 5 * se_rel + 2e-6     # + the fp32 compounding bias budget
-    assert abs(r.std - np.sqrt(var)) / np.sqrt(var) < 1e-4
+    assert abs(r.std - np.sqrt(var)) / np.sqrt(var) < 1e-5   # north_star bound; this seed measures +2.8e-6 (the std's own standard error at 1e10 paths is 7.7e-6)
 
 
 def test_fused_benchmark_program_prints_the_reference_programs_statistics(S, O, table1127, tmp_path):
