@@ -528,14 +528,22 @@ def main():
         raise SystemExit("bench.py needs a B200 per rank: the product has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    comm = None
+    comm, nccl_log = None, None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL's communicator lines are evidence (rank count, transport): keep them, but on stderr so that the JSON line
-        # stays alone on stdout.  libsmmc.so additionally prints one "rank r nranks N cudaDev d" line per rank to stderr.
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
-        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL's communicator lines are evidence (rank count, transport).  Unless the caller already asked for INFO or TRACE,
+        # ask NCCL for its INIT log into a scratch file and replay the communicator lines on stderr at the end
+        # (NCCL_DEBUG_FILE=/dev/stderr would reopen -- and truncate -- a redirected stderr; NCCL's default is stdout, which
+        # must keep the JSON line).  libsmmc.so additionally prints one "rank r nranks N cudaDev d" line per rank to stderr.
+        asked = os.environ.get("NCCL_DEBUG", "").upper()
+        if asked not in ("INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "INFO"
+            os.environ["NCCL_DEBUG_SUBSYS"] = "INIT"
+        if "NCCL_DEBUG_FILE" not in os.environ:
+            nccl_log = f"/tmp/smmc_nccl_{os.getpid()}.log"
+            os.environ["NCCL_DEBUG_FILE"] = nccl_log
+        print(f"bench: rank {rank} NCCL_DEBUG={os.environ['NCCL_DEBUG']} (caller had {asked or 'none'}) "
+              f"NCCL_DEBUG_FILE={os.environ['NCCL_DEBUG_FILE']}", file=sys.stderr)
         dist.init_process_group("nccl", device_id=dev)  # launcher plumbing: barrier + max-over-ranks of the timings
         from stock_market_monte_carlo_b200.distributed import init_comm
         comm = init_comm(local)  # the path's own communicator: ncclCommInitRank inside libsmmc.so (smmc_run_rank)
@@ -716,8 +724,22 @@ def main():
                 "how": "Comm.simulate / Comm.quantiles (smmc_run_rank / smmc_quantiles_rank, NCCL inside the C ABI) vs smmc_run / smmc_quantiles on rank 0"}
         barrier()
 
+    def replay_nccl_log():
+        if world > 1 and nccl_log and os.path.exists(nccl_log):
+            p2p = 0
+            for ln in open(nccl_log, errors="replace"):
+                if "via P2P" in ln or "via SHM" in ln or "via NET" in ln:
+                    p2p += 1
+                    if p2p > 2:  # one line per channel and peer: the first two name the transport
+                        continue
+                elif not any(k in ln for k in ("nranks", "nRanks", "Init COMPLETE", "NVLS", "NCCL version", "Connected all")):
+                    continue
+                print(ln.rstrip(), file=sys.stderr)
+            sys.stderr.flush()
+
     if rank != 0:
         if world > 1:
+            replay_nccl_log()
             dist.barrier()
             dist.destroy_process_group()
         return 0
@@ -792,6 +814,7 @@ def main():
         "result": {"count": final.count, "mean": final.mean, "std": final.std, "p_below_target": final.p_below_target},
         "extras": extras or None,
     }
+    replay_nccl_log()
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
