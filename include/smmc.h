@@ -277,7 +277,9 @@ typedef struct smmc_plan {
   int32_t grid;            /* CTAs (one per SM) */
   int32_t threads;         /* threads per CTA: 32 x warps, warps chosen to fill the last wave of 256-path blocks */
   int32_t table_copies;    /* bank-private copies of the return table per entry (32 = conflict-free gather) */
-  int32_t reserved;
+  int32_t ticket;          /* 1: 256-path blocks are handed to the warps by an atomic ticket and their moments merged in block
+                            * order (launches of 1..48 waves); 0: static assignment.  Results do not depend on it beyond the
+                            * fp64 rounding of mean / M2 (integer outputs and every per-path / per-block output are identical) */
   uint64_t smem_bytes;     /* dynamic shared memory per CTA */
 } smmc_plan;
 /* The launch smmc_run would use for cfg on a device with n_sms SMs and smem_optin bytes of opt-in shared memory
@@ -301,8 +303,10 @@ smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, i
  * this to prove it).  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
  * (reduce_mean kernel: 1 = streaming loads, 2 = TMA ring), "gauss_tbl" (GAUSSIAN: 4-bit mask of the Box-Muller pairs of a
  * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0|1), "sobol_unroll",
- * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch), "finals_threads" (its host copy-out threads).  value < 0 (or 0 where 0 is not a choice)
- * restores the default; key NULL resets everything.  Process-wide; nothing in the library reads the environment. */
+ * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch), "finals_threads" (its host copy-out threads),
+ * "select_candidates" (0 = the third select pass always replays), "ticket" (256-path blocks handed to warps 0 = statically,
+ * 1 = by an atomic ticket with the block moments merged in block order; default: ticket for launches of 1..48 waves).
+ * value < 0 (or 0 where 0 is not a choice) restores the default; key NULL resets everything.  Process-wide; nothing in the library reads the environment. */
 smmc_status smmc_debug_set_variant(const char *key, int32_t value);
 
 /* ---- housekeeping ---------------------------------------------------------------------------------------- */

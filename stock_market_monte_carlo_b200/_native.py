@@ -96,7 +96,7 @@ class SmmcPlan(C.Structure):
         ("grid", C.c_int32),
         ("threads", C.c_int32),
         ("table_copies", C.c_int32),
-        ("reserved", C.c_int32),
+        ("ticket", C.c_int32),
         ("smem_bytes", C.c_uint64),
     ]
 

@@ -130,7 +130,7 @@ struct Context {
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
   cudaEvent_t red0 = nullptr, red1 = nullptr;  // around the reduce_mean kernel (smmc_reduce_mean_device)
-  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_full, sobol_shift, selhist, sincos;
+  DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_full, sobol_shift, selhist, sincos, block_moments;
   bool sincos_ready = false;
   bool sobol_full_ready = false;
   // Small host-built tables (withdrawal schedule, per-launch Sobol tables) are cached by content in a ring of device
@@ -266,6 +266,8 @@ smmc_status validate(const smmc_config *cfg, const smmc_result *out, bool read_t
   }
   if (cfg->hist_bins < 0 || cfg->hist_bins > SMMC_MAX_HIST_BINS) return fail(SMMC_ERR_INVALID_ARG, "hist_bins out of range");
   if (cfg->hist_bins > 0 && !(cfg->hist_hi > cfg->hist_lo)) return fail(SMMC_ERR_INVALID_ARG, "hist_hi must be > hist_lo");
+  if (cfg->hist_bins > 0 && (!std::isfinite(cfg->hist_lo) || !std::isfinite(cfg->hist_hi)))
+    return fail(SMMC_ERR_INVALID_ARG, "hist_lo / hist_hi must be finite");
   if (!std::isfinite(cfg->withdraw_fixed) || !std::isfinite(cfg->withdraw_pct))
     return fail(SMMC_ERR_INVALID_ARG, "withdraw_fixed / withdraw_pct must be finite");
   if (!std::isfinite(cfg->initial_capital)) return fail(SMMC_ERR_INVALID_ARG, "initial_capital must be finite");
@@ -328,6 +330,7 @@ void fill_stream_params(const smmc_config *cfg, smmc::KParams *p) {
   p->gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
   p->sigma_sqrt2 = (float)(1.41421356237309504880 * (double)sigma);
   p->one = 0x3F800000u;
+  p->cell_mask = smmc::kSinCosCellMask;
   p->v0 = cfg->initial_capital;
   p->idx_scale = (float)cfg->n_returns * 2.3283064365386963e-10f;  // exact: n < 2^24
   p->bc.c21 = (float)(4 * cfg->n_returns);                          // exact: n < 2^21 (validated)
@@ -583,9 +586,14 @@ smmc_status mark_last_use(Context *ctx, cudaStream_t st) {
 }
 
 // the (cos, sin) table of the Gaussian modes, built once per device
+const float *sincos_table_of(const Context *ctx, int mode) {
+  const char *base = (const char *)ctx->sincos.p;
+  return (const float *)(mode == SMMC_MODE_GAUSSIAN ? base + smmc::kSinCosBytes : base);
+}
+
 smmc_status prepare_sincos(Context *ctx, cudaStream_t st) {
   if (ctx->sincos_ready) return SMMC_OK;
-  CU(ctx->sincos.reserve(smmc::kSinCosBytes));
+  CU(ctx->sincos.reserve(2 * (size_t)smmc::kSinCosBytes));  // [swizzled copy (SOBOL_GAUSSIAN)][linear copy (GAUSSIAN)]
   smmc::launch_sincos_table((float *)ctx->sincos.p, st);
   CU(cudaGetLastError());
   ctx->sincos_ready = true;
@@ -621,7 +629,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
 
   smmc::LaunchInfo li;
   if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, has_withdrawals(cfg), sincos, N,
-                         ctx->n_sms, ctx->smem_optin, variant.warps, &li))
+                         ctx->n_sms, ctx->smem_optin, variant.warps, variant.ticket, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries (+ histograms / schedules) does not fit in %zu bytes of shared memory",
                 cfg->n_returns, ctx->smem_optin);
 
@@ -674,7 +682,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     smmc_status ss = prepare_sincos(ctx, st);
     if (ss != SMMC_OK) return ss;
     if (fresh) pd->launches++;
-    p.tbl_rep = (const float *)ctx->sincos.p;
+    p.tbl_rep = sincos_table_of(ctx, cfg->mode);
     p.tbl_bytes = smmc::kSinCosBytes;
   }
 
@@ -687,6 +695,11 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   p.hist_g = (unsigned long long *)(w + part_bytes);
   p.ticket = (unsigned int *)(w + part_bytes + hist_bytes);
   CU(cudaMemsetAsync(w + part_bytes, 0, hist_bytes + 16, st));
+  if (li.ticket && nb > 0) {  // blocks handed out by ticket, their moments merged in block order (smmc_kernels.cu, plan_ticket)
+    CU(ctx->block_moments.reserve((size_t)nb * sizeof(float2)));
+    p.block_moments = (float2 *)ctx->block_moments.p;
+    p.block_ticket = p.ticket + 1;  // inside the 16 bytes zeroed above
+  }
 
   // ---- outputs
   if (dout) {
@@ -860,16 +873,22 @@ struct Shard {
 };
 
 // Splits [0, N) of cfg over the given devices in whole 256-path blocks (the partition smmc_run_multi documents).
+// Whole 256-path blocks [b0, b1) of shard `rank` of `n`: floor(nb / n) blocks each, the remainder one apiece to the lowest
+// ranks -- balanced to one block (the ONE partition rule: smmc_run_multi, smmc_run_rank, smmc_rank_range, distributed.py).
+void shard_blocks(int64_t N, int n, int rank, int64_t *b0, int64_t *b1) {
+  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
+  const int64_t base = nb / n, extra = nb % n;
+  *b0 = base * rank + (rank < extra ? rank : extra);
+  *b1 = *b0 + base + (rank < extra ? 1 : 0);
+}
+
 void make_shards(const smmc_config *cfg, const smmc_result *out, const std::vector<Context *> &ctxs, std::vector<Shard> *shards) {
   const int n_gpus = (int)ctxs.size();
   const int64_t N = cfg->n_simulations;
-  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
-  const int64_t per = (nb + n_gpus - 1) / n_gpus;  // logical blocks per device
   shards->assign((size_t)n_gpus, Shard());
   for (int g = 0; g < n_gpus; g++) {
-    int64_t b0 = per * g, b1 = per * (g + 1);
-    if (b0 > nb) b0 = nb;
-    if (b1 > nb) b1 = nb;
+    int64_t b0 = 0, b1 = 0;
+    shard_blocks(N, n_gpus, g, &b0, &b1);
     int64_t p0 = b0 * SMMC_BLOCK, p1 = b1 * SMMC_BLOCK;
     if (p1 > N) p1 = N;
     if (p0 >= p1) p0 = p1 = 0;  // an empty shard keeps a block-aligned offset
@@ -1216,11 +1235,8 @@ smmc_status need_nccl(const smmc::NcclApi **api) {
 
 // first block-aligned path and path count of shard `rank` of `n` (the partition of make_shards)
 void rank_range(int64_t N, int n, int rank, int64_t *first, int64_t *count) {
-  const int64_t nb = (N + SMMC_BLOCK - 1) / SMMC_BLOCK;
-  const int64_t per = (nb + n - 1) / n;
-  int64_t b0 = per * rank, b1 = per * (rank + 1);
-  if (b0 > nb) b0 = nb;
-  if (b1 > nb) b1 = nb;
+  int64_t b0 = 0, b1 = 0;
+  shard_blocks(N, n, rank, &b0, &b1);
   int64_t p0 = b0 * SMMC_BLOCK, p1 = b1 * SMMC_BLOCK;
   if (p1 > N) p1 = N;
   if (p0 >= p1) p0 = p1 = 0;  // an empty shard keeps a block-aligned offset
@@ -1980,7 +1996,7 @@ smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *va
   if (p.gauss_tbl_mask) {  // the Gaussian modes' sin/cos table (read from global memory here)
     st = prepare_sincos(ctx, s);
     if (st != SMMC_OK) return st;
-    p.tbl_rep = (const float *)ctx->sincos.p;
+    p.tbl_rep = sincos_table_of(ctx, cfg->mode);
   }
   CU(smmc::launch_trajectories(cfg->mode, p, n_paths, tbl, raw, full_dev, shift_dev, vd, rd, s));
   st = versioned_mark_read(ctx->flow_v, flow_slot, s);
@@ -2009,13 +2025,13 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
   smmc::LaunchInfo li;
   const smmc::Variant variant = current_variant();
   if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, has_withdrawals(cfg),
-                         uses_sincos_table(cfg->mode, variant), cfg->n_simulations, n_sms, (size_t)smem_optin, variant.warps, &li))
+                         uses_sincos_table(cfg->mode, variant), cfg->n_simulations, n_sms, (size_t)smem_optin, variant.warps, variant.ticket, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %llu bytes of shared memory", cfg->n_returns,
                 (unsigned long long)smem_optin);
   plan->grid = li.grid;
   plan->threads = li.threads;
   plan->table_copies = li.rep;
-  plan->reserved = 0;
+  plan->ticket = li.ticket ? 1 : 0;
   plan->smem_bytes = li.smem_bytes;
   return SMMC_OK;
 }
@@ -2095,6 +2111,7 @@ smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
   else if (!strcmp(key, "sobol_unroll")) g_variant.sobol_unroll = value > 0 ? value : def.sobol_unroll;
   else if (!strcmp(key, "finals_chunks")) g_variant.finals_chunks = value > 0 ? value : def.finals_chunks;
   else if (!strcmp(key, "select_candidates")) g_variant.select_candidates = (value == 0 || value == 1) ? value : def.select_candidates;
+  else if (!strcmp(key, "ticket")) g_variant.ticket = (value == 0 || value == 1) ? value : def.ticket;
   else if (!strcmp(key, "finals_threads")) g_variant.finals_threads = (value > 0 && value <= 64) ? value : def.finals_threads;
   else return fail(SMMC_ERR_INVALID_ARG, "debug_set_variant: unknown key '%s'", key);
   return SMMC_OK;
@@ -2163,6 +2180,7 @@ void smmc_shutdown(void) {
     c.copy_stream = nullptr;
     c.tbl.release();
     c.work.release();
+    c.block_moments.release();
     c.stats.release();
     c.finals.release();
     c.bmeans.release();

@@ -200,7 +200,8 @@ __device__ __forceinline__ void gauss_pair(uint32_t w, uint32_t one, const Gauss
 // Cost: SHF + LOP3 (address) + LDS.64 + LOP3 + 3 FFMA instead of I2FP + FMUL + FMUL.RZ + 2 MUFU: the XU pipe (4 lanes per
 // clock per sub-partition, the binding pipe of the Gaussian modes) is relieved of half its work.  64 KB of shared memory.
 constexpr int kSinCosCells = 8192;
-constexpr uint32_t kSinCosBytes = kSinCosCells * 8u;
+constexpr uint32_t kSinCosBytes = kSinCosCells * 8u;   // one copy; the device buffer holds two: [swizzled][linear]
+constexpr uint32_t kSinCosCellMask = 0xFFF80000u;       // the 13 cell bits of the angle word
 constexpr float kSinCosKap = (float)(3.14159265358979323846 / 256.0);                       // 2 pi 2^23 / 2^32
 constexpr float kSinCosKap0 = (float)(-(1.0 + 1.0 / 32.0) * 3.14159265358979323846 / 256.0);  // -(1 + 2^-5) kap
 
@@ -211,19 +212,33 @@ constexpr float kSinCosKap0 = (float)(-(1.0 + 1.0 / 32.0) * 3.141592653589793238
 // GAUSSIAN's hashed words are random either way.  Byte offset = ((h >> 16) ^ (h >> 25)) & 0xFFF8: two SHF + one LOP3.
 __host__ __device__ __forceinline__ uint32_t sincos_slot(uint32_t cell) { return cell ^ (cell >> 9); }
 
-__device__ __forceinline__ void sincos_tbl(uint32_t h, uint32_t one, const char *sc_tbl, float &cv, float &sv) {
-  const float2 cs = *reinterpret_cast<const float2 *>(sc_tbl + (((h >> 16) ^ (h >> 25)) & 0xFFF8u));
-  const float beta = fmaf(__uint_as_float((h & 0x7FFFFu) | one), kSinCosKap, kSinCosKap0);
+// GAUSSIAN reads the LINEAR copy of the table (second half of the buffer, sincos_table_kernel): its hashed words are
+// random, a swizzle buys nothing there, and the linear offset is cheaper -- hc = h & cell_mask (LOP3, the mask passed as an
+// opaque value so that the shift is not commuted in front of it), address = base + (hc >> 16) (one LEA.HI), mantissa
+// (h & ~cell_mask) | one (one LOP3): 2 address instructions instead of 3 (SASS checked: LOP3, LEA.HI, LOP3, LDS.64 [R+UR]).
+template <bool SWZ>
+__device__ __forceinline__ void sincos_tbl(uint32_t h, uint32_t one, uint32_t cell_mask, const char *sc_tbl, float &cv, float &sv) {
+  float2 cs;
+  uint32_t mant;
+  if (SWZ) {
+    cs = *reinterpret_cast<const float2 *>(sc_tbl + (((h >> 16) ^ (h >> 25)) & 0xFFF8u));
+    mant = (h & 0x7FFFFu) | one;
+  } else {
+    const uint32_t hc = h & cell_mask;
+    cs = *reinterpret_cast<const float2 *>(sc_tbl + (hc >> 16));
+    mant = (h ^ hc) | one;
+  }
+  const float beta = fmaf(__uint_as_float(mant), kSinCosKap, kSinCosKap0);
   cv = fmaf(-cs.y, beta, cs.x);
   sv = fmaf(cs.x, beta, cs.y);
 }
 
-__device__ __forceinline__ void gauss_pair_tbl(uint32_t w, uint32_t one, const GaussConsts gc, const char *sc_tbl, float &g0,
-                                               float &g1) {
+__device__ __forceinline__ void gauss_pair_tbl(uint32_t w, uint32_t one, uint32_t cell_mask, const GaussConsts gc, const char *sc_tbl,
+                                               float &g0, float &g1) {
   const float mr = __uint_as_float((w & 0xFFFFFu) | one);
   const float u = fmaf(mr, 8.0f, -7.99999952316284179688f);
   float cv, sv;
-  sincos_tbl(w * kAngleHash, one, sc_tbl, cv, sv);
+  sincos_tbl<false>(w * kAngleHash, one, cell_mask, sc_tbl, cv, sv);
   const float rs = sqrt_approx(lg2_approx(u) * gc.k);
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);
@@ -252,7 +267,7 @@ __device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, u
                                                      const char *sc_tbl, float &g0, float &g1) {
   const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
   float cv, sv;
-  sincos_tbl(xa, one, sc_tbl, cv, sv);
+  sincos_tbl<true>(xa, one, 0u, sc_tbl, cv, sv);
   const float rs = sqrt_approx(lg2_approx(u) * gc.k);
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);

@@ -53,6 +53,9 @@ __global__ void sincos_table_kernel(float *__restrict__ dst) {
   const uint32_t slot = sincos_slot((uint32_t)i);  // bank swizzle, see sincos_tbl
   dst[2 * slot] = (float)cv;
   dst[2 * slot + 1] = (float)sv;
+  float *lin = dst + 2 * kSinCosCells;  // the linear copy GAUSSIAN reads
+  lin[2 * i] = (float)cv;
+  lin[2 * i + 1] = (float)sv;
 }
 
 // ---- trajectory mode ------------------------------------------------------------------------------------------------
@@ -105,7 +108,7 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
       const int j = m % kGaussMonthsPerCall;
       if (j == 0) stream_words_rt(p.philox_rounds, plo, phi, (uint32_t)(m / kGaussMonthsPerCall), kTagGaussian, p.keys, w);
       if ((j & 1) == 0) {  // the same evaluation of sin/cos as the statistics kernel's pair j/2 (table or MUFU)
-        if ((p.gauss_tbl_mask >> (j >> 1)) & 1) gauss_pair_tbl(w[j >> 1], p.one, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
+        if ((p.gauss_tbl_mask >> (j >> 1)) & 1) gauss_pair_tbl(w[j >> 1], p.one, p.cell_mask, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
         else gauss_pair(w[j >> 1], p.one, p.gc, g[0], g[1]);
       }
       const float gm = g[j & 1];
@@ -389,12 +392,14 @@ __global__ void __launch_bounds__(512) vector_add_kernel(float *__restrict__ out
 // last wave may be nearly empty (5 M paths = 19 531 blocks = 4.12 waves of 148 x 32 warps: 82 % efficient).  Fewer
 // warps per CTA can fill the last wave (27 warps: 4.89 of 5 waves); fewer resident warps cost some latency
 // hiding, hence the mild penalty.  Large launches (tens of waves) keep 32.
-int plan_warps(int64_t n_paths, int n_sms) {
+int plan_warps(int64_t n_paths, int n_sms, bool ticket) {
   const int64_t nb = (n_paths + kBlock - 1) / kBlock;
   if (nb <= 0) return kWarps;
   int best = kWarps;
   double best_score = 0.0;
-  for (int w = kWarps; w >= 20; w--) {
+  // ticket launches hand blocks out dynamically, so only the warp count per scheduler matters: multiples of 4 keep the four
+  // sub-partitions even (measured at 5 M x 1000 Sobol: 28 warps 1.385 ms, 27: 1.439, 30: 1.443, 32: 1.444, 24: 1.405)
+  for (int w = kWarps; w >= (ticket ? 24 : 20); w -= (ticket ? 4 : 1)) {
     const int64_t slots = (int64_t)n_sms * w;
     const int64_t waves = (nb + slots - 1) / slots;
     const double eff = (double)nb / (double)(slots * waves);
@@ -407,8 +412,18 @@ int plan_warps(int64_t n_paths, int n_sms) {
   return best;
 }
 
+// Blocks are handed out by ticket when the launch is more than one wave and fewer than kTicketMaxWaves waves of 32-warp
+// CTAs: there the tail (warps that run dry while others still hold a block) is a visible share of the kernel (5 M x 1000:
+// -5 %; 20 M x 360: -2 %; 100 M x 360, 82 waves: +-0.1 %, kept static).
+bool plan_ticket(int64_t n_paths, int n_sms, int ticket_override) {
+  if (ticket_override == 0 || ticket_override == 1) return ticket_override == 1;
+  const int64_t nb = (n_paths + kBlock - 1) / kBlock;
+  const int64_t per_wave = (int64_t)n_sms * kWarps;
+  return nb > per_wave && nb < (int64_t)kTicketMaxWaves * per_wave;
+}
+
 bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, bool sincos,
-                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li) {
+                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, int ticket_override, LaunchInfo *li) {
   const uint32_t sel_bytes = (uint32_t)sel_targets * kSelectBins * 4u;
   if (withdrawals && (size_t)n_periods * 4u > smem_optin) return false;  // (size_t: n_periods * 4 must not wrap)
   const uint32_t flow_bytes = withdrawals ? (uint32_t)n_periods * 4u : 0u;
@@ -417,7 +432,8 @@ bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_
   const bool has_table = (mode == SMMC_MODE_BOOTSTRAP_COMPAT || mode == SMMC_MODE_BOOTSTRAP ||
                           mode == SMMC_MODE_SOBOL_BOOTSTRAP);
   li->grid = n_sms;
-  li->threads = 32 * ((warps_override >= 1 && warps_override <= kWarps) ? warps_override : plan_warps(n_paths, n_sms));
+  li->ticket = plan_ticket(n_paths, n_sms, ticket_override);
+  li->threads = 32 * ((warps_override >= 1 && warps_override <= kWarps) ? warps_override : plan_warps(n_paths, n_sms, li->ticket));
   li->rep = 0;
   uint32_t tbl_bytes = 0;
   if (has_table) {

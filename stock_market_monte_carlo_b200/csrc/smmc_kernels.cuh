@@ -25,6 +25,7 @@ struct KParams {
   float idx_scale;     // compat: float(n) * 2^-32
   BootConsts bc;       // BOOTSTRAP: fma.rz index constants and the row shift
   uint32_t one;        // 0x3F800000, passed as a value the compiler cannot fold: keeps (w & mask) | one a single LOP3
+  uint32_t cell_mask;  // kSinCosCellMask, opaque for the same reason (sincos_tbl<false>)
   PhiloxKeys keys;
   int32_t philox_rounds;  // 10 (default) or 7 (smmc_config.philox_rounds); the simulation kernel takes it as a template parameter
   GaussConsts gc;
@@ -41,6 +42,11 @@ struct KParams {
   double *cta_partials;       // [grid][4] = n, mean, M2, below
   unsigned long long *hist_g;  // [bins+2], zeroed before launch
   unsigned int *ticket;        // zeroed before launch
+  // dynamic block assignment (launches of few waves): a warp's first block is static, every further one comes from
+  // *block_ticket (zeroed before launch).  Which warp ran a block then depends on timing, so the blocks' (mean, M2) go to
+  // block_moments[b] and the last CTA merges them in BLOCK order: every output bit stays a function of the launch plan.
+  unsigned int *block_ticket;  // null = static assignment (warp w of CTA c walks b = c W + w, += grid W)
+  float2 *block_moments;       // [nb]
   double *stats;               // [SMMC_STATS_HEADER + bins + 2]
   // Sobol (DESIGN.md "Sobol"): point index of path p is p + 256; month m is dimension m
   const uint32_t *sobol_lo;  // [P_pad][8]   direction numbers of index bits 0..7, month-major (staged to smem)
@@ -116,8 +122,10 @@ struct Variant {
   int finals_chunks = 0; // host-pointer finals pipeline: number of chunks (0 = automatic, 1 = one monolithic launch)
   int finals_threads = 0; // ... and its host copy-out threads (0 = automatic)
   int select_candidates = -1;  // 0 = the third select pass always replays (no candidate buffer), -1 / 1 = default
+  int ticket = -1;       // block assignment: 0 = static, 1 = ticket, -1 = by launch size (plan_ticket)
 };
 
+constexpr int kTicketMaxWaves = 48;  // launches of fewer waves of 256-path blocks take the ticket (the tail matters there)
 constexpr int kSobolHiRows = 98;   // rows of KParams::sobol_hi
 constexpr uint32_t kSobolSkip = 256;  // first Sobol point used; keeps 256-path blocks aligned to 256-point blocks
 
@@ -126,13 +134,14 @@ struct LaunchInfo {
   int threads;
   size_t smem_bytes;
   int rep;  // table replication factor chosen
+  bool ticket;  // 256-path blocks handed to warps by an atomic ticket (KParams::block_ticket) instead of statically
 };
 
 // Chooses replication / shared-memory layout for `mode`; returns false if the table cannot fit.
 // Also picks the warps per CTA for `n_paths` (warps_override in 1..32 forces it; 0 = automatic).
 // sincos: Gaussian modes stage the sin/cos table (kSinCosBytes) where the bootstrap modes stage the return table.
 bool plan_launch(int mode, int n_returns, int n_periods, int hist_bins, int sel_targets, bool withdrawals, bool sincos,
-                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, LaunchInfo *li);
+                 int64_t n_paths, int n_sms, size_t smem_optin, int warps_override, int ticket_override, LaunchInfo *li);
 
 // Builds the scaled, replicated table: dst[(i*rep + c)] = src[i] * 0.01f, row n = 0, tail padding = 0.
 void launch_prep_table(const float *returns_dev, int n, int rep, float *dst, uint32_t dst_floats, cudaStream_t s);

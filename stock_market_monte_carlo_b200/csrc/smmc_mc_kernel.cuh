@@ -33,6 +33,27 @@ __device__ __forceinline__ void merge(Moments &a, double nb, double meanb, doubl
   a.n = tot;
 }
 
+// all 32 lanes' moments -> every lane, by a butterfly that merges in a lane-symmetric order (the lower lane is always
+// "a"), so every lane ends with identical bits
+__device__ __forceinline__ void butterfly_merge(Moments &c, uint32_t lane) {
+#pragma unroll
+  for (int st = 1; st <= 16; st <<= 1) {
+    const double on = __shfl_xor_sync(0xffffffffu, c.n, st);
+    const double om = __shfl_xor_sync(0xffffffffu, c.mean, st);
+    const double o2 = __shfl_xor_sync(0xffffffffu, c.m2, st);
+    Moments a, bb;
+    if ((lane & st) == 0) {
+      a = c;
+      bb = {on, om, o2};
+    } else {
+      a = {on, om, o2};
+      bb = c;
+    }
+    merge(a, bb.n, bb.mean, bb.m2);
+    c = a;
+  }
+}
+
 // the reference's 256-slot reduction tree (src/simulations.cu:157-183) on values held 8 per lane (slot 32*j+lane):
 // strides 128, 64, 32 are lane-local adds, strides 16..1 are shuffles; lane 0's association order is the reference's.
 __device__ __forceinline__ float tree_sum_256(const float (&s)[8]) {
@@ -141,9 +162,9 @@ __device__ __forceinline__ void run_bootstrap(const KParams &p, const Flow<FLOW>
 // sin/cos from the shared-memory table (sincos_tbl, no MUFU) when bit j is set, from MUFU.SIN/COS otherwise -- the two
 // evaluate the same angle of the same contract (smmc_device.cuh); the mix balances the XU pipe against the FMA/ALU pipes.
 template <int TBL>
-__device__ __forceinline__ void gauss_pair_sel(int j, uint32_t w, uint32_t one, const GaussConsts gc, const char *sc_tbl,
-                                               float &g0, float &g1) {
-  if ((TBL >> j) & 1) gauss_pair_tbl(w, one, gc, sc_tbl, g0, g1);
+__device__ __forceinline__ void gauss_pair_sel(int j, uint32_t w, uint32_t one, uint32_t cell_mask, const GaussConsts gc,
+                                               const char *sc_tbl, float &g0, float &g1) {
+  if ((TBL >> j) & 1) gauss_pair_tbl(w, one, cell_mask, gc, sc_tbl, g0, g1);
   else gauss_pair(w, one, gc, g0, g1);
 }
 
@@ -151,7 +172,7 @@ template <int ILP, bool FLOW, int ROUNDS, int TBL>
 __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> &fl, const char *sc_tbl,
                                              const uint32_t (&plo)[ILP], uint32_t phi, float (&tot)[ILP]) {
   const GaussConsts gc = p.gc;
-  const uint32_t one = p.one;
+  const uint32_t one = p.one, cell_mask = p.cell_mask;
   const int nq = p.n_periods / kGaussMonthsPerCall;
 #pragma unroll 1
   for (int q = 0; q < nq; q++) {
@@ -162,7 +183,7 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float g0, g1;
-        gauss_pair_sel<TBL>(j, w[j], one, gc, sc_tbl, g0, g1);
+        gauss_pair_sel<TBL>(j, w[j], one, cell_mask, gc, sc_tbl, g0, g1);
         const int m = q * kGaussMonthsPerCall + 2 * j;
         tot[i] = fl(__fmul_rn(fl(__fmul_rn(tot[i], g0), m), g1), m + 1);
       }
@@ -177,7 +198,7 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float g0, g1;
-        gauss_pair_sel<TBL>(j, w[j], one, gc, sc_tbl, g0, g1);
+        gauss_pair_sel<TBL>(j, w[j], one, cell_mask, gc, sc_tbl, g0, g1);
         const int m = nq * kGaussMonthsPerCall + 2 * j;
         if (2 * j < rem) tot[i] = fl(__fmul_rn(tot[i], g0), m);
         if (2 * j + 1 < rem) tot[i] = fl(__fmul_rn(tot[i], g1), m + 1);
@@ -344,7 +365,8 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   unsigned int below_lane = 0;
   unsigned long long below_acc = 0ull;
 
-  for (int64_t b = (int64_t)blockIdx.x * n_warps + warp; b < nb; b += total_warps) {
+  const bool dyn = p.block_ticket != nullptr;
+  for (int64_t b = (int64_t)blockIdx.x * n_warps + warp; b < nb;) {
     const uint64_t base = p.path0 + (uint64_t)b * kBlock;  // 256-aligned: low 8 bits free for the in-block offset
     const uint32_t base_lo = (uint32_t)base, phi = (uint32_t)(base >> 32);
     const int64_t rem_paths = N - b * kBlock;
@@ -449,11 +471,20 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
       mean_live = (double)tmean;
       m2_live = (double)tree_sum_256(s);
     }
-    merge(acc, (double)live, mean_live, m2_live);
-
     if (below_lane > 0x7fffff00u) {  // keep the 32-bit per-lane counter far from wrapping
       below_acc += below_lane;
       below_lane = 0;
+    }
+    if (dyn) {  // both values are fp32 results widened above: the float2 loses nothing
+      unsigned int t = 0;
+      if (lane == 0) {
+        p.block_moments[b] = make_float2((float)mean_live, (float)m2_live);
+        t = atomicAdd(p.block_ticket, 1u);
+      }
+      b = total_warps + (int64_t)__shfl_sync(0xffffffffu, t, 0);
+    } else {
+      merge(acc, (double)live, mean_live, m2_live);
+      b += total_warps;
     }
   }
 
@@ -493,8 +524,27 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
   if (!is_last) return;
   __threadfence();
 
-  // last CTA: merge the per-CTA partials in CTA order (warp 0: lane-strided sequential merge, then a fixed
-  // butterfly), emit the allreduce-ready statistics vector (include/smmc.h, SMMC_STATS_HEADER)
+  // last CTA.  Ticket launches: the blocks' moments are merged in block order -- thread t takes blocks t, t + T, ...
+  // sequentially, lanes by the fixed butterfly, warps in warp order -- so the result does not depend on which warp ran
+  // which block.
+  if (dyn) {
+    Moments c = {0.0, 0.0, 0.0};
+    for (int64_t i = tid; i < nb; i += (int64_t)blockDim.x) {
+      const float2 m = __ldcg(p.block_moments + i);
+      const int64_t rem = N - i * kBlock;
+      merge(c, (double)(rem < kBlock ? rem : (int64_t)kBlock), (double)m.x, (double)m.y);
+    }
+    butterfly_merge(c, lane);
+    __syncthreads();  // wp[] of the CTA-level merge above is free again
+    if (lane == 0) {
+      wp[warp * 4 + 0] = c.n;
+      wp[warp * 4 + 1] = c.mean;
+      wp[warp * 4 + 2] = c.m2;
+    }
+    __syncthreads();
+  }
+  // Merge the per-CTA partials in CTA order (warp 0: lane-strided sequential merge, then a fixed butterfly), emit the
+  // allreduce-ready statistics vector (include/smmc.h, SMMC_STATS_HEADER)
   if (warp == 0) {
     Moments c = {0.0, 0.0, 0.0};
     double below = 0.0;
@@ -503,24 +553,12 @@ __global__ void __launch_bounds__(kThreads, 1) mc_kernel(const __grid_constant__
       merge(c, __ldcg(cp + 0), __ldcg(cp + 1), __ldcg(cp + 2));
       below += __ldcg(cp + 3);
     }
+    butterfly_merge(c, lane);
 #pragma unroll
-    for (int st = 1; st <= 16; st <<= 1) {
-      const double on = __shfl_xor_sync(0xffffffffu, c.n, st);
-      const double om = __shfl_xor_sync(0xffffffffu, c.mean, st);
-      const double o2 = __shfl_xor_sync(0xffffffffu, c.m2, st);
-      const double ob = __shfl_xor_sync(0xffffffffu, below, st);
-      // merge in a lane-symmetric order so every lane ends with identical bits: lower lane is always "a"
-      Moments a, bb;
-      if ((lane & st) == 0) {
-        a = c;
-        bb = {on, om, o2};
-      } else {
-        a = {on, om, o2};
-        bb = c;
-      }
-      merge(a, bb.n, bb.mean, bb.m2);
-      c = a;
-      below += ob;
+    for (int st = 1; st <= 16; st <<= 1) below += __shfl_xor_sync(0xffffffffu, below, st);  // integers < 2^53: exact
+    if (dyn) {  // every lane computes the same warp-order merge of the block-order partials
+      c = {0.0, 0.0, 0.0};
+      for (int w = 0; w < n_warps; w++) merge(c, wp[w * 4 + 0], wp[w * 4 + 1], wp[w * 4 + 2]);
     }
     if (lane == 0) {
       const double dm = c.mean - (double)p.v0;

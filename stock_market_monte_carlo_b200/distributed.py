@@ -15,18 +15,14 @@ from . import _native as N
 
 def shard_range(n_simulations, rank, world_size, stream_offset=0):
     """(first_path_id, n_paths) of `rank`: contiguous ranges in units of whole 256-path logical blocks, the
-    remainder blocks going to the lowest ranks.  Same partition rule family as smmc_run_multi
-    (csrc/smmc_api.cu), restated for the one-process-per-GPU launch."""
+    remainder blocks going to the lowest ranks -- smmc_rank_range of the C ABI (the partition of smmc_run_multi and
+    smmc_run_rank), plus the run's stream_offset."""
     n = int(n_simulations)
     if n < 0 or world_size < 1 or not (0 <= rank < world_size):
         raise ValueError("bad shard request")
-    nb = (n + N.SMMC_BLOCK - 1) // N.SMMC_BLOCK
-    base, extra = divmod(nb, world_size)
-    b0 = rank * base + min(rank, extra)
-    b1 = b0 + base + (1 if rank < extra else 0)
-    p0 = b0 * N.SMMC_BLOCK
-    p1 = min(b1 * N.SMMC_BLOCK, n)
-    return int(stream_offset) + p0, max(p1 - p0, 0)
+    from . import simulations as _S
+    first, count = _S.rank_range(n, world_size, rank)
+    return int(stream_offset) + first, count
 
 
 def allreduce_stats(stats, group=None):

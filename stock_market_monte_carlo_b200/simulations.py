@@ -422,13 +422,17 @@ def write_data_file(fname, returns, values):
 
 
 def plan_launch(mode, n_simulations, n_periods, n_returns=0, hist_bins=0, select_targets=0, n_sms=148,
-                smem_optin=232448):
-    """(grid, threads, table_copies, smem_bytes) smmc_run would use on a device with `n_sms` SMs (host only)"""
+                smem_optin=232448, full=False):
+    """(grid, threads, table_copies, smem_bytes) smmc_run would use on a device with `n_sms` SMs (host only);
+    full=True: a dict that also says whether the blocks are handed out by ticket"""
     lib = N.load()
     cfg, _ = make_config(mode, n_simulations, n_periods, hist_bins=hist_bins)
     cfg.n_returns = int(n_returns)
     plan = N.SmmcPlan()
     N.check(lib.smmc_plan_launch(C.byref(cfg), int(select_targets), int(n_sms), int(smem_optin), C.byref(plan)))
+    if full:
+        return dict(grid=int(plan.grid), threads=int(plan.threads), table_copies=int(plan.table_copies),
+                    smem_bytes=int(plan.smem_bytes), ticket=bool(plan.ticket))
     return int(plan.grid), int(plan.threads), int(plan.table_copies), int(plan.smem_bytes)
 
 

@@ -6,6 +6,7 @@ import os
 import re
 import subprocess
 
+import numpy as np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -140,6 +141,40 @@ def test_validation_precedes_device_probe(S, table):
         with pytest.raises(S.SmmcError) as e:
             S.simulate(**kw)
         assert e.value.status == 1, kw
+
+
+def test_round2_fields_are_validated_before_the_device_probe(S, table):
+    """ABI 3: philox_rounds in {0, 7, 10}; non-finite scalars and table entries are argument errors, not NaN results."""
+    bad = [
+        dict(mode="gaussian", n_simulations=10, n_periods=10, philox_rounds=8),
+        dict(mode="bootstrap", n_simulations=10, n_periods=10, returns=table, philox_rounds=-1),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, gauss_mean=float("nan")),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, gauss_std=float("inf")),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, initial_capital=float("nan")),
+        dict(mode="gaussian", n_simulations=10, n_periods=10, hist_bins=10, hist_range=(0.0, float("inf"))),
+        dict(mode="gaussian", n_simulations=2 ** 38 + 256, n_periods=1),
+    ]
+    nan_table = table.copy()
+    nan_table[17] = np.nan
+    bad.append(dict(mode="bootstrap", n_simulations=10, n_periods=10, returns=nan_table))
+    for kw in bad:
+        with pytest.raises(S.SmmcError) as e:
+            S.simulate(**kw)
+        assert e.value.status == 1, kw
+
+
+def test_comm_entry_points_validate_and_report(S):
+    """smmc_comm_*: null / out-of-range arguments are INVALID_ARG; destroying nothing is fine."""
+    lib = S.load()
+    n, r, d, v = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+    assert lib.smmc_comm_info(None, C.byref(n), C.byref(r), C.byref(d), C.byref(v)) == 1
+    assert lib.smmc_comm_unique_id(None) == 1
+    comm = C.c_void_p()
+    uid = C.create_string_buffer(128)  # SMMC_COMM_ID_BYTES
+    assert lib.smmc_comm_init_rank(uid, 0, 0, 0, C.byref(comm)) == 1   # n_ranks 0
+    assert lib.smmc_comm_init_rank(uid, 2, 2, 0, C.byref(comm)) == 1   # rank out of range
+    assert lib.smmc_comm_init_rank(None, 1, 0, 0, C.byref(comm)) == 1  # no id
+    assert lib.smmc_comm_destroy(None) == 0
 
 
 def test_new_entry_points_fail_loudly_without_a_device(S, table):

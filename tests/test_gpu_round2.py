@@ -357,3 +357,39 @@ def test_reduce_mean_and_vector_add_examples_relinked(S, tmp_path):
     out = _run_relinked(tmp_path, exe_va, [1000], np.zeros(1, dtype=np.float32))
     vals = re.findall(r"[-\d.]+", out[out.index("["):])
     assert len(vals) == 1000 and all(v == "3.000" for v in vals)  # 1.0f + 2.0f, print_vector's {:6.3f}
+
+
+# ---- block assignment by ticket -----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ALL_MODES)
+def test_ticket_assignment_changes_no_result(S, table, mode):
+    """launches of 1..48 waves hand 256-path blocks to the warps by an atomic ticket: which warp ran a block depends on
+    timing, yet every per-path / per-block / integer output is identical to the static assignment, mean and M2 agree to
+    fp64 rounding, and repeated ticket launches give identical bits (block-order merge in the last CTA)."""
+    kw = mode_kwargs(mode, table)
+    N, P = 148 * 32 * 256 * 2 + 777, 24  # just over two waves
+    assert S.plan_launch(mode, N, P, n_returns=len(table) if "bootstrap" in mode else 0, full=True)["ticket"] is True
+    runs = []
+    try:
+        for t, w in ((0, 0), (1, 0), (1, 0), (1, 20), (1, 32)):
+            S.set_variant()
+            S.set_variant("ticket", t)
+            S.set_variant("warps", w)
+            runs.append(S.simulate(mode, N, P, hist_bins=64, target=1100.0, want_finals=True, want_block_partials=True, **kw))
+    finally:
+        S.set_variant()
+    static, a, b = runs[0], runs[1], runs[2]
+    assert a.mean == b.mean and a.m2 == b.m2  # deterministic for a launch plan
+    for r in runs[1:]:
+        assert np.array_equal(r.finals.view(np.uint32), static.finals.view(np.uint32))
+        assert np.array_equal(r.block_means.view(np.uint32), static.block_means.view(np.uint32))
+        assert np.array_equal(r.block_vars.view(np.uint32), static.block_vars.view(np.uint32))
+        assert np.array_equal(r.hist, static.hist) and r.below_count == static.below_count and r.count == static.count
+        assert abs(r.mean - static.mean) <= 1e-12 * abs(static.mean) and abs(r.m2 - static.m2) <= 1e-9 * abs(static.m2)
+
+
+def test_ticket_launch_quantiles_and_partial_last_block(S, table):
+    N, P = 148 * 32 * 256 + 3, 12  # one wave + a 3-path block: ticket by size
+    r = S.simulate("bootstrap", N, P, returns=table, seed=3, want_finals=True)
+    q = S.quantiles("bootstrap", N, P, returns=table, seed=3)
+    assert np.array_equal(q, np.sort(r.finals)[S.quartile_ranks(N)])
+    assert r.count == N and abs(r.mean - float(np.mean(r.finals.astype(np.float64)))) <= 1e-9 * r.mean

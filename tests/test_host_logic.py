@@ -61,6 +61,34 @@ def test_shard_ranges_partition_the_path_ids(S, n, world):
     assert max(sizes) - min(sizes) <= 256 + 255  # balanced to one logical block
 
 
+@pytest.mark.parametrize("n", [0, 1, 255, 256, 257, 1000, 1_000_003, 100_000_000, 10 ** 10])
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+def test_rank_range_of_the_c_abi_partitions_the_run(S, n, world):
+    """smmc_rank_range (the partition smmc_run_rank / smmc_run_multi use): whole 256-path blocks, contiguous, complete,
+    balanced to one block, empty trailing ranks are zero-sized -- and it is the partition the Python plumbing uses."""
+    from stock_market_monte_carlo_b200.distributed import shard_range
+    nxt, sizes = 0, []
+    for r in range(world):
+        first, cnt = S.rank_range(n, world, r)
+        assert cnt >= 0 and first % 256 == 0
+        if cnt:
+            assert first == nxt
+            nxt = first + cnt
+            if r + 1 < world and S.rank_range(n, world, r + 1)[1]:
+                assert cnt % 256 == 0
+        sizes.append(cnt)
+        off, c2 = shard_range(n, r, world, stream_offset=0)
+        assert c2 == cnt and (cnt == 0 or off == first)
+    assert sum(sizes) == n and nxt == n
+    assert max(sizes) - min(sizes) <= 256 + 255
+
+
+def test_rank_range_rejects_bad_requests(S):
+    for args in ((10, 2, 2), (10, 2, -1), (-5, 1, 0), (10, 0, 0)):
+        with pytest.raises(S.SmmcError):
+            S.rank_range(*args)
+
+
 def test_shard_range_rejects_bad_requests(S):
     from stock_market_monte_carlo_b200.distributed import shard_range
     for args in ((10, 2, 2), (10, -1, 2), (-5, 0, 1), (10, 0, 0)):

@@ -76,7 +76,17 @@ def test_launch_plan_fills_the_last_wave(S):
     """one warp per 256-path block: 5 M paths are 19 531 blocks; 148 x 32 warps would run 4.12 waves (82 %),
     148 x 27 warps run 4.89 of 5 (98 %); large launches keep 32 warps; results never depend on the choice"""
     grid, threads, copies, smem = S.plan_launch("sobol_gaussian", 5_000_000, 1000, hist_bins=100)
-    assert grid == 148 and threads == 27 * 32 and copies == 0
+    # 1..48 waves: blocks are handed out by ticket, warps per CTA a multiple of 4 (28: 4.71 of 5 waves)
+    assert grid == 148 and threads == 28 * 32 and copies == 0
+    assert S.plan_launch("sobol_gaussian", 5_000_000, 1000, hist_bins=100, full=True)["ticket"] is True
+    assert S.plan_launch("gaussian", 100_000_000, 360, full=True)["ticket"] is False   # 82 waves: static
+    assert S.plan_launch("gaussian", 1000, 360, full=True)["ticket"] is False          # less than one wave: static
+    try:
+        S.set_variant("ticket", 0)
+        assert S.plan_launch("sobol_gaussian", 5_000_000, 1000, hist_bins=100)[1] == 27 * 32  # static: 4.89 of 5 waves
+        assert S.plan_launch("sobol_gaussian", 5_000_000, 1000, full=True)["ticket"] is False
+    finally:
+        S.set_variant()
     for mode in ("gaussian", "bootstrap_compat"):
         g, t, c, sm = S.plan_launch(mode, 100_000_000, 360, n_returns=1200 if "boot" in mode else 0, hist_bins=100)
         assert (g, t) == (148, 1024) and sm <= 232448

@@ -27,6 +27,39 @@ def test_philox_known_answers(O, ctr, key, want):
     assert [int(x) for x in O.philox([ctr], key)[0]] == want
 
 
+# Random123 kat_vectors, "philox4x32 7": the opt-in round count of ABI 3 (smmc_config.philox_rounds = 7)
+PHILOX7_KAT = [
+    ([0x00000000] * 4, [0x00000000] * 2, [0x5F6FB709, 0x0D893F64, 0x4F121F81, 0x4F730A48]),
+    ([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x5207DDC2, 0x45165E59, 0x4D8EE751, 0x8C52F662]),
+    ([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0],
+     [0x4DFCCABA, 0x190A87F0, 0xC47362BA, 0xB6B5242A]),
+]
+
+
+@pytest.mark.parametrize("ctr,key,want", PHILOX7_KAT)
+def test_philox7_known_answers(O, ctr, key, want):
+    assert [int(x) for x in O.philox([ctr], key, rounds=7)[0]] == want
+
+
+def test_philox_rounds_select_the_stream_in_the_oracle(O, table):
+    """7 and 10 rounds are different streams of the same contract: draws differ, 0 means 10, and both reproduce the
+    closed-form mean of the bootstrap (RNG-independent) within a few standard errors."""
+    kw = dict(seed=11, want_finals=True, returns=table)
+    a = O.simulate("bootstrap", 40_000, 120, philox_rounds=10, **kw)
+    b = O.simulate("bootstrap", 40_000, 120, philox_rounds=7, **kw)
+    c = O.simulate("bootstrap", 40_000, 120, philox_rounds=0, **kw)
+    assert np.array_equal(a.finals, c.finals)
+    assert not np.array_equal(a.finals, b.finals)
+    m1 = 1.0 + float(np.mean(table.astype(np.float64) * 0.01))
+    want = 1000.0 * m1 ** 120
+    for r in (a, b):
+        se = r.std / np.sqrt(40_000)
+        assert abs(r.mean - want) < 5 * se
+    d10 = O.draws("gaussian", 300, 16, seed=3, philox_rounds=10)
+    d7 = O.draws("gaussian", 300, 16, seed=3, philox_rounds=7)
+    assert d10.shape == d7.shape and not np.array_equal(d10, d7)
+
+
 def test_philox_matches_numpy_generator(O):
     """numpy's Philox is Philox4x64, not 4x32, so it cannot serve; instead check the round structure against an
     independent pure-Python restatement of the published algorithm on random counters."""

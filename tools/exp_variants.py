@@ -106,3 +106,18 @@ if "sobol" in groups:
             ms, mn, r = timed("sobol_bootstrap", N, P, reps=10, partials=False, hist_range=(0.0, 1.0e8))
             line(f"sobol_bootstrap unroll={u} warps={w}", "sobol_bootstrap", N, P, ms, mn, r)
     S.set_variant()
+
+if "ticket" in groups:
+    # block assignment: static vs ticket (block-order merge), warps per CTA sweep
+    for mode, N, P, rng, ws in (("gaussian", 100_000_000, 360, (0.0, 50000.0), (0,)), ("bootstrap", 100_000_000, 360, (0.0, 200000.0), (0,)),
+                                ("bootstrap", 20_000_000, 360, (0.0, 200000.0), (0, 32)), ("gaussian", 5_000_000, 360, (0.0, 50000.0), (0, 28, 32)),
+                                ("sobol_gaussian", 5_000_000, 1000, (0.0, 500000.0), (0, 24, 27, 28, 32)),
+                                ("sobol_bootstrap", 5_000_000, 1000, (0.0, 1.0e8), (0, 24, 27, 28, 32))):
+        for t in (0, 1, -1):
+            for w in ws:
+                S.set_variant()
+                S.set_variant("ticket", t)
+                S.set_variant("warps", w)
+                ms, mn, r = timed(mode, N, P, reps=5 if N > 10_000_000 else 10, partials=not mode.startswith("sobol"), hist_range=rng)
+                line(f"ticket={t} warps={w}", mode, N, P, ms, mn, r)
+    S.set_variant()
