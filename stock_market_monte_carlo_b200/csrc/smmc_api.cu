@@ -2137,7 +2137,7 @@ smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int3
 }
 
 const char *smmc_last_error(void) { return g_err; }
-const char *smmc_version(void) { return "smmc 0.1 (sm_100a, abi 2)"; }
+const char *smmc_version(void) { return "smmc 0.2 (sm_100a, abi 3)"; }
 int32_t smmc_device_count(void) { return probe_devices(); }
 
 void smmc_shutdown(void) {
