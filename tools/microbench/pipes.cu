@@ -13,7 +13,9 @@
 #include <cuda_runtime.h>
 
 #define ILP 8
-#define ITERS 2048
+#ifndef ITERS
+#define ITERS 32768  // long enough (ms per kernel) for the SM clock to settle at its maximum
+#endif
 
 enum Op {
   FFMA, FMUL, FADD_RZ, LOP3, SHF, IADD, IMAD, IMAD_HI, IMAD_WIDE, PHILOX_ROUND, I2FP, F2I,
