@@ -1,4 +1,4 @@
-"""Summarise gpurun_out/ of `bash tools/gpu_first_run.sh` into one text file for profiles/.
+"""Summarise gpurun_out/ of `bash tools/gpu_r02_run.sh` (+ the captures of tools/gpu_r02_capture.sh) into one text file for profiles/.
 usage: python tools/summarize_run.py "<header line>" > profiles/<name>.txt"""
 import collections
 import csv
@@ -9,23 +9,35 @@ import sys
 
 G = "gpurun_out"
 print("#", sys.argv[1] if len(sys.argv) > 1 else "GPU run")
-print("# command: gpurun -- 'bash tools/gpu_first_run.sh'\n")
+print("# commands: gpurun -- 'bash tools/gpu_r02_run.sh', then one gpurun -- 'bash tools/gpu_r02_capture.sh <mode>' per ncu --set full capture\n")
 print("## pytest -m gpu")
 print("".join(open(f"{G}/pytest_gpu.log").readlines()[-2:]))
 print("## smoke")
 print(open(f"{G}/smoke.log").read())
-print("## bench.py (device-timed value | e2e through smmc_run with host buffers | kernel ms | frac by restated I_alg | pipe floor | clocks)")
-for w in ["c2", "c3", "c3compat", "c4", "c4boot"]:
-    d = json.loads(open(f"{G}/bench_{w}.json").read().strip().splitlines()[-1])
-    r, c = d["roofline"], d["clocks"]
-    pf = r.get("pipe_floor")
-    print(f"{w:9s} value {d['value']:.4e} pm/s  e2e {d['e2e']['value']:.4e}  ms/step {d['ms_per_step']:.3f}  kernel_ms {r['kernel_ms']:.3f}  "
-          f"i_alg {r['i_alg']}  frac {r['frac']:.3f}  frac_survey_budget {r['frac_survey_budget'] and round(r['frac_survey_budget'], 3)}  "
-          f"pipe_floor {pf and (pf['pipe'], round(pf['frac'], 3))}  sm_mhz {c['sm_mhz']} reasons {c['reasons']} power_w_max {c['power_w_max']}")
-    if d.get("cpu_baseline"):
-        print("   cpu_baseline:", d["cpu_baseline"])
-    if d.get("extras"):
-        print("   extras:", d["extras"])
+print("## bench.py, the driver's default command (device-timed value | e2e through smmc_run with host buffers | kernel ms | frac by restated I_alg | pipe floor | clocks)")
+d = json.loads(open(f"{G}/bench_c2.json").read().strip().splitlines()[-1])
+r, c = d["roofline"], d["clocks"]
+pf = r.get("pipe_floor")
+print(f"c2        value {d['value']:.4e} pm/s  e2e {d['e2e']['value']:.4e}  ms/step {d['ms_per_step']:.3f}  kernel_ms {r['kernel_ms']:.3f}  "
+      f"i_alg {r['i_alg']}  frac {r['frac']:.3f}  frac_survey_budget {r['frac_survey_budget'] and round(r['frac_survey_budget'], 3)}  "
+      f"pipe_floor {pf and (pf['pipe'], round(pf['frac'], 3))}  traffic {r.get('traffic')}  sm_mhz {c['sm_mhz']} reasons {c['reasons']} power_w_max {c['power_w_max']}")
+print("   cpu_baseline:", d.get("cpu_baseline"))
+print("   gpu_launches:", d.get("gpu_launches"), " result:", d.get("result"))
+ex = d.get("extras") or {}
+print("\n## extras.workloads (5 timed steps each, same process, after the headline)")
+for k, w in (ex.get("workloads") or {}).items():
+    rf = w.get("roofline", {})
+    print(f"{k:12s} value {w['value']:.4e} {w['unit']}  kernel_ms {w.get('kernel_ms'):.4f}  frac {rf.get('frac'):.3f} ({rf.get('bound')}"
+          + (f", {rf.get('achieved'):.0f} of {rf.get('peak')} GB/s, traffic {rf.get('traffic')}" if rf.get("bound") == "hbm" else f", i_alg {rf.get('i_alg')}")
+          + f")  pipe_floor_frac {rf.get('pipe_floor_frac')}  e2e {w.get('e2e', {}).get('value')}  vs_ref_gpu_same_box {w.get('vs_ref_gpu_same_box')}  sm_mhz {w.get('sm_mhz')} {w.get('clock_reasons')}")
+print("\n## extras.ref_gpu_same_box (the reference's src/simulations.cu compiled for sm_100a, same process, same box)")
+for k, v in (ex.get("ref_gpu_same_box") or {}).items():
+    print(f"   {k}: {v}")
+print("\n## extras.c5 (10^10 paths x 360 months of ONE run)")
+print("  ", ex.get("c5"))
+print("\n## extras quartiles")
+for k in ("quartiles_min_q1_med_q3_max", "quartiles_device_ms", "quartiles_how", "quartiles_riding_along_extra_ms", "quartiles_riding_along_equal"):
+    print(f"   {k}: {ex.get(k)}")
 for aux in ("reduce_mean", "vector_add"):
     if not os.path.exists(f"{G}/bench_{aux}.json"):
         continue
@@ -36,7 +48,7 @@ for aux in ("reduce_mean", "vector_add"):
           f"sm_mhz {d['clocks']['sm_mhz']} {d['clocks']['reasons']}")
 d = json.loads(open(f"{G}/bench_ref.json").read().strip().splitlines()[-1])
 print("--impl reference:", d["value"], d["cpu_baseline"])
-print("\n## ncu launch list of: python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e  (gpu__time_duration.sum)")
+print("\n## ncu launch list of: python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e --no-extras  (gpu__time_duration.sum)")
 rows = list(csv.reader(l for l in open(f"{G}/launches_c2.csv") if l.startswith('"')))
 h = rows[0]
 ki, vi, ui = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Unit")
