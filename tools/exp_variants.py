@@ -14,7 +14,8 @@ import torch  # noqa: E402
 
 import stock_market_monte_carlo_b200 as S  # noqa: E402
 
-groups = sys.argv[1:] or ["gauss", "boot", "sobol"]
+groups = [a for a in sys.argv[1:] if "=" not in a] or ["gauss", "boot", "sobol"]
+MASKS = [int(x) for a in sys.argv[1:] if a.startswith("masks=") for x in a[6:].split(",")] or [0, 1, 5, 7, 15]
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
 tbl = S.synthetic_sp500_table(1200)
@@ -59,7 +60,7 @@ def check_gauss(mode, **kw):
 if "gauss" in groups:
     N, P = 100_000_000, 360
     for rounds in (10, 7):
-        for tblmask in (0, 1, 5, 7, 15):
+        for tblmask in MASKS:
             S.set_variant()
             S.set_variant("gauss_tbl", tblmask)
             ref = None
