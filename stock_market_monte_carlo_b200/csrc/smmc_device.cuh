@@ -233,6 +233,19 @@ __device__ __forceinline__ void sincos_tbl(uint32_t h, uint32_t one, uint32_t ce
   sv = fmaf(cs.x, beta, cs.y);
 }
 
+// The swizzled copy with the table given as a 32-bit shared-window address, the form the simulation kernel uses: slot << 3 =
+// ((h ^ (h >> 9)) & cell_mask) >> 16, so the address is SHF, LOP3 ((h ^ s) & mask, the mask opaque), LEA.HI (base + (t >> 16)):
+// the base add rides on the shift (the pointer form costs SHF, SHF, LOP3, IADD3; SOBOL_GAUSSIAN is issue-bound).
+__device__ __forceinline__ void sincos_tbl_swz_u32(uint32_t h, uint32_t one, uint32_t cell_mask, uint32_t sc_base, float &cv,
+                                                   float &sv) {
+  float c, s;
+  const uint32_t t = (h ^ (h >> 9)) & cell_mask;
+  asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c), "=f"(s) : "r"(sc_base + (t >> 16)));
+  const float beta = fmaf(__uint_as_float((h & 0x7FFFFu) | one), kSinCosKap, kSinCosKap0);
+  cv = fmaf(-s, beta, c);
+  sv = fmaf(c, beta, s);
+}
+
 __device__ __forceinline__ void gauss_pair_tbl(uint32_t w, uint32_t one, uint32_t cell_mask, const GaussConsts gc, const char *sc_tbl,
                                                float &g0, float &g1) {
   const float mr = __uint_as_float((w & 0xFFFFFu) | one);
@@ -263,11 +276,22 @@ __device__ __forceinline__ void sobol_gauss_pair(uint32_t xr, uint32_t xa, const
   g1 = fmaf(rs, sin_approx(v), gc.a);
 }
 
+// pointer form (trajectory kernel: the table is read from global memory there); same arithmetic, same bits
 __device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, uint32_t one, const GaussConsts gc,
                                                      const char *sc_tbl, float &g0, float &g1) {
   const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
   float cv, sv;
   sincos_tbl<true>(xa, one, 0u, sc_tbl, cv, sv);
+  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  g0 = fmaf(rs, cv, gc.a);
+  g1 = fmaf(rs, sv, gc.a);
+}
+
+__device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, uint32_t one, const GaussConsts gc,
+                                                     uint32_t cell_mask, uint32_t sc_base, float &g0, float &g1) {
+  const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
+  float cv, sv;
+  sincos_tbl_swz_u32(xa, one, cell_mask, sc_base, cv, sv);
   const float rs = sqrt_approx(lg2_approx(u) * gc.k);
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);

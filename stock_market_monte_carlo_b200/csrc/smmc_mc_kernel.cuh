@@ -213,6 +213,16 @@ __device__ __forceinline__ void run_gaussian(const KParams &p, const Flow<FLOW> 
 // h_0 contribution to gray bit 7 folded in) is warp-uniform, computed 32 months at a time with lane = month, and
 // broadcast by one SHFL per month.  gray bits 0..3 depend on the lane only (masks), bits 4..7 on (lane_4, j): the
 // eight per-j variants are one or two 3-input XORs away from a common base.  ~2 instructions per path-month.
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+// base ^= v when the (loop-invariant) lane flag is set: one predicated LOP3
+__device__ __forceinline__ void xor_if(uint32_t &base, uint32_t v, uint32_t flag) {
+  asm("{\n .reg .pred p;\n setp.ne.u32 p, %2, 0;\n @p xor.b32 %0, %0, %1;\n}" : "+r"(base) : "r"(v), "r"(flag));
+}
+
 template <int MODE, bool FLOW, int TBL, int UNROLL>
 __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl, const char *tbl, uint32_t lane_off,
                                           const uint4 *vlo, uint32_t h, uint32_t lane, float (&tot)[8]) {
@@ -227,6 +237,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   const uint32_t lane_base = smem_u32(tbl) + lane_off;  // shared-window address of this lane's table column
   const uint32_t one = p.one;
   const GaussConsts gc = p.gc;
+  const uint32_t sc_base = smem_u32(tbl), cell_mask = p.cell_mask;
   // warp-uniform part of month m0 + lane.  The host tabulates, per month, the XOR of the direction numbers of every 4-bit
   // group of gray(h) (six groups x 16 combinations) and the two variants of (digital shift ^ [h odd] V[7]): seven
   // independent, unconditional loads (L2-resident table) instead of 26 predicated ones behind 26 branches -- that was
@@ -242,19 +253,21 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   // the eight words of month m (one per path of the lane) from the broadcast block part Um
   auto month_words = [&](int m, uint32_t Um, uint32_t (&x)[8]) {
     const uint4 va = vlo[m * 2], vb = vlo[m * 2 + 1];
-    uint32_t base = Um ^ (va.x & mk0);
-    base ^= (va.y & mk1);
-    base ^= (va.z & mk2);
-    base ^= (va.w & mk3);
-    base ^= (vb.x & mk4);
-    x[0] = base;
-    x[1] = base ^ vb.x ^ vb.y;
-    x[2] = base ^ vb.y ^ vb.z;
-    x[3] = base ^ vb.x ^ vb.z;
-    x[4] = base ^ vb.z ^ vb.w;
-    x[5] = x[1] ^ vb.z ^ vb.w;
-    x[6] = base ^ vb.y ^ vb.w;
-    x[7] = base ^ vb.x ^ vb.w;
+    // five predicated XORs (the lane's gray bits are loop-invariant predicates): the mask form compiled to 4 SEL + 3 LOP3
+    uint32_t base = Um;
+    xor_if(base, va.x, mk0);
+    xor_if(base, va.y, mk1);
+    xor_if(base, va.z, mk2);
+    xor_if(base, va.w, mk3);
+    xor_if(base, vb.x, mk4);
+    x[0] = base;  // seven explicit 3-input XORs (left to itself the compiler shares 2-input partials: 9 LOP3)
+    x[1] = xor3(base, vb.x, vb.y);
+    x[2] = xor3(base, vb.y, vb.z);
+    x[3] = xor3(base, vb.x, vb.z);
+    x[4] = xor3(base, vb.z, vb.w);
+    x[5] = xor3(x[1], vb.z, vb.w);
+    x[6] = xor3(base, vb.y, vb.w);
+    x[7] = xor3(base, vb.x, vb.w);
   };
   uint32_t U_next = p.n_periods > 0 ? block_part(0) : 0u;
 #pragma unroll 1
@@ -280,7 +293,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
 #pragma unroll
         for (int j = 0; j < 8; j++) {
           float g0, g1;
-          if (TBL) sobol_gauss_pair_tbl(xr[j], xa[j], one, gc, tbl, g0, g1);  // sin/cos from the shared-memory table
+          if (TBL) sobol_gauss_pair_tbl(xr[j], xa[j], one, gc, cell_mask, sc_base, g0, g1);  // sin/cos from the shared-memory table
           else sobol_gauss_pair(xr[j], xa[j], gc, g0, g1);
           tot[j] = fl(__fmul_rn(fl(__fmul_rn(tot[j], g0), m0 + mi), g1), m0 + mi + 1);
         }
