@@ -309,8 +309,8 @@ bool uses_sincos_table(int mode, const smmc::Variant &v) {
   if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0;
   return false;
 }
-int gauss_table_mask(int mode, const smmc::Variant &v) {
-  if (mode == SMMC_MODE_GAUSSIAN) return v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::kGaussTblDefault;
+int gauss_table_mask(int mode, const smmc::Variant &v, int philox_rounds) {
+  if (mode == SMMC_MODE_GAUSSIAN) return v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::gauss_tbl_default(philox_rounds == 7 ? 7 : 10);
   if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0 ? 0xF : 0;
   return 0;
 }
@@ -324,7 +324,7 @@ void fill_stream_params(const smmc_config *cfg, smmc::KParams *p) {
   p->compat_seed = (uint32_t)cfg->seed;
   p->keys = make_keys(cfg->seed);
   p->philox_rounds = cfg->philox_rounds == 7 ? 7 : 10;
-  p->gauss_tbl_mask = gauss_table_mask(cfg->mode, current_variant());
+  p->gauss_tbl_mask = gauss_table_mask(cfg->mode, current_variant(), cfg->philox_rounds);
   const float mu = cfg->gauss_mean * 0.01f, sigma = cfg->gauss_std * 0.01f;
   p->gc.a = 1.0f + mu;
   p->gc.k = (float)(-2.0 * 0.69314718055994530942 * (double)sigma * (double)sigma);
@@ -1299,7 +1299,7 @@ CandFingerprint fingerprint_of(const smmc_config *cfg) {
                    : fnv1a(cfg->returns, (size_t)cfg->n_returns * 4);
   if (cfg->withdraw_pct_schedule) f.schedule = fnv1a(cfg->withdraw_pct_schedule, (size_t)cfg->n_periods * 4);
   const smmc::Variant v = current_variant();
-  f.tbl_mask = gauss_table_mask(cfg->mode, v);
+  f.tbl_mask = gauss_table_mask(cfg->mode, v, cfg->philox_rounds);
   return f;
 }
 

@@ -108,6 +108,9 @@ __host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, 
 
 // Build-time choices that do not touch the contract (every choice computes the same draws):
 constexpr int kGaussTblDefault = 5;      // GAUSSIAN: pairs 0 and 2 of a call take sin/cos from the shared-memory table
+// ... per Philox round count: with 7 rounds the multiplier pipe has more room and the best split moves to pairs 0 and 3
+// (100 M x 360: mask 5 14.98 ms, mask 9 14.70 ms; with 10 rounds mask 5 17.36, mask 9 17.51; profiles/r02_variants_*.txt)
+constexpr int gauss_tbl_default(int rounds) { return rounds == 7 ? 9 : kGaussTblDefault; }
 constexpr int kSobolUnrollDefault = 2;   // SOBOL_BOOTSTRAP month-loop unroll
 
 // Test / development hook (smmc_debug_set_variant): selects among the compiled kernel variants.  Zero / negative = default.

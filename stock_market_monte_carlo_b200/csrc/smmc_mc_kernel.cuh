@@ -253,21 +253,40 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
   // the eight words of month m (one per path of the lane) from the broadcast block part Um
   auto month_words = [&](int m, uint32_t Um, uint32_t (&x)[8]) {
     const uint4 va = vlo[m * 2], vb = vlo[m * 2 + 1];
-    // five predicated XORs (the lane's gray bits are loop-invariant predicates): the mask form compiled to 4 SEL + 3 LOP3
     uint32_t base = Um;
-    xor_if(base, va.x, mk0);
-    xor_if(base, va.y, mk1);
-    xor_if(base, va.z, mk2);
-    xor_if(base, va.w, mk3);
-    xor_if(base, vb.x, mk4);
-    x[0] = base;  // seven explicit 3-input XORs (left to itself the compiler shares 2-input partials: 9 LOP3)
-    x[1] = xor3(base, vb.x, vb.y);
-    x[2] = xor3(base, vb.y, vb.z);
-    x[3] = xor3(base, vb.x, vb.z);
-    x[4] = xor3(base, vb.z, vb.w);
-    x[5] = xor3(x[1], vb.z, vb.w);
-    x[6] = xor3(base, vb.y, vb.w);
-    x[7] = xor3(base, vb.x, vb.w);
+    if (MODE == SMMC_MODE_SOBOL_GAUSSIAN) {
+      // issue-bound kernel: five predicated XORs (the lane's gray bits are loop-invariant predicates) and seven explicit
+      // 3-input XORs = 12 instructions; the mask form below compiles to 4 SEL + 3 LOP3 + 8 LOP3 = 15 (C4: 2.016 -> 1.936 ms
+      // together with the LEA.HI table address)
+      xor_if(base, va.x, mk0);
+      xor_if(base, va.y, mk1);
+      xor_if(base, va.z, mk2);
+      xor_if(base, va.w, mk3);
+      xor_if(base, vb.x, mk4);
+      x[0] = base;
+      x[1] = xor3(base, vb.x, vb.y);
+      x[2] = xor3(base, vb.y, vb.z);
+      x[3] = xor3(base, vb.x, vb.z);
+      x[4] = xor3(base, vb.z, vb.w);
+      x[5] = xor3(x[1], vb.z, vb.w);
+      x[6] = xor3(base, vb.y, vb.w);
+      x[7] = xor3(base, vb.x, vb.w);
+      return;
+    }
+    // SOBOL_BOOTSTRAP is bound by the multiplier pipe, not by issue: the form the compiler schedules best (1.388 vs 1.395 ms)
+    base ^= (va.x & mk0);
+    base ^= (va.y & mk1);
+    base ^= (va.z & mk2);
+    base ^= (va.w & mk3);
+    base ^= (vb.x & mk4);
+    x[0] = base;
+    x[1] = base ^ vb.x ^ vb.y;
+    x[2] = base ^ vb.y ^ vb.z;
+    x[3] = base ^ vb.x ^ vb.z;
+    x[4] = base ^ vb.z ^ vb.w;
+    x[5] = x[1] ^ vb.z ^ vb.w;
+    x[6] = base ^ vb.y ^ vb.w;
+    x[7] = base ^ vb.x ^ vb.w;
   };
   uint32_t U_next = p.n_periods > 0 ? block_part(0) : 0u;
 #pragma unroll 1
