@@ -139,7 +139,12 @@ __global__ void __launch_bounds__(1024, 1) k(unsigned *out, long long *cyc, unsi
   __syncthreads();
   long long t0 = clock64();
   const unsigned c1 = seed | 0xD2511F53u, c2 = seed | 0xCD9E8D57u;
-#pragma unroll 1
+  // unrolled 8x: with "#pragma unroll 1" the three loop instructions (IADD3, ISETP, BRA) per 8 timed ones showed up as
+  // 1.42-1.45 "cycles" for the full-rate instructions (FFMA, FMUL, IADD3) in profiles/r01_pipe_microbench.txt
+  // (only for those rows: ptxas folds eight consecutive XORs / shifts of one register, so the ALU-pipe rows keep the loop form,
+  // where the 2-cycle instructions hide the loop overhead anyway)
+  constexpr int kUnroll = (OP == FFMA || OP == FMUL || OP == FADD_RZ || OP == IADD) ? 8 : 1;
+#pragma unroll kUnroll
   for (int it = 0; it < ITERS; it++) {
 #pragma unroll
     for (int j = 0; j < ILP; j++) step<OP>(x[j], y[j], f[j], c1, c2, fa, fb, smu, lane);
@@ -158,7 +163,7 @@ __global__ void __launch_bounds__(1024, 1) k(unsigned *out, long long *cyc, unsi
 template <int OP>
 void run(unsigned *out, long long *cyc_d, int nsm) {
   float fa = 1.0000001f, fb = 1e-9f;
-  if (OP == COMPAT_MONTH) fa = 1024.0f * 2.3283064e-10f;
+  if (OP == COMPAT_MONTH) fa = 1023.0f * 2.3283064e-10f;  // idx <= 1023 even when float(x) rounds up to 2^32 (the reference's idx == n quirk)
   if (OP == BOXMULLER_PAIR) { fa = -9.6e-5f; fb = 0.0f; }
   cudaFuncSetAttribute(k<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
