@@ -51,7 +51,11 @@ typedef enum smmc_mode {
    * dimension = month; optional Philox-keyed digital shift when seed != 0.
    * SOBOL_BOOTSTRAP: index = mulhi(word, n) into the SORTED table (empirical quantile function).
    * SOBOL_GAUSSIAN: Box-Muller on dimension pairs -- month 2k takes its radius from the word of dimension 2k, month
-   * 2k+1 its angle from dimension 2k+1; the unpaired last month of an odd horizon takes the inverse normal CDF. */
+   * 2k+1 its angle from dimension 2k+1; the unpaired last month of an odd horizon takes the inverse normal CDF.
+   * LIMITS (validated, SMMC_ERR_INVALID_ARG): n_periods <= 1111 (the dimensions of the vendored table) and 32-bit point
+   * indices, stream_offset + n_simulations + 256 <= 2^32.  The reference vendors i8_sobol (include/sobol/sobol.cpp:14191,
+   * 62-bit indices) but never calls it; its i4_sobol stops at 2^30 points (maxcol = 30), the 32 columns used here follow
+   * the same recurrence.  Runs beyond 2^32 points per seed are split over seeds (each a different digital shift). */
   SMMC_MODE_SOBOL_BOOTSTRAP = 3,
   SMMC_MODE_SOBOL_GAUSSIAN = 4
 } smmc_mode;
