@@ -306,7 +306,7 @@ smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, i
 /* Test hook: selects among the compiled variants of a kernel (all variants of a mode produce the same draws; the tests use
  * this to prove it).  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
  * (reduce_mean kernel: 1 = streaming loads, 2 = TMA ring), "gauss_tbl" (GAUSSIAN: 4-bit mask of the Box-Muller pairs of a
- * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0|1), "sobol_unroll",
+ * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0 = MUFU, 1 = table), "sobol_unroll",
  * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch), "finals_threads" (its host copy-out threads),
  * "select_candidates" (0 = the third select pass always replays), "ticket" (256-path blocks handed to warps 0 = statically,
  * 1 = by an atomic ticket with the block moments merged in block order; default: ticket for launches of 1..48 waves).

@@ -304,16 +304,32 @@ smmc::PhiloxKeys make_keys(uint64_t seed) {
 // does this configuration take sin/cos from the shared-memory table?  A function of (mode, variant hook) only -- never of
 // what else has to fit into shared memory -- so that every launch of a configuration (statistics, select replays, shards,
 // chunks) computes bit-identical paths.
-bool uses_sincos_table(int mode, const smmc::Variant &v) {
-  if (mode == SMMC_MODE_GAUSSIAN) return (v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::kGaussTblDefault) != 0;
-  if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0;
-  return false;
-}
+// Which Box-Muller pairs take sin/cos from the shared-memory table: GAUSSIAN a 4-bit mask over the pairs of a Philox call,
+// SOBOL_GAUSSIAN an 8-bit mask over a lane's path slots.  Only the masks a build has kernels for are handed out (anything
+// else falls back to the default), so the statistics kernel, the trajectory kernel and the candidate fingerprint agree.
 int gauss_table_mask(int mode, const smmc::Variant &v, int philox_rounds) {
-  if (mode == SMMC_MODE_GAUSSIAN) return v.gauss_tbl >= 0 ? v.gauss_tbl : smmc::gauss_tbl_default(philox_rounds == 7 ? 7 : 10);
-  if (mode == SMMC_MODE_SOBOL_GAUSSIAN) return v.sobol_tbl != 0 ? 0xF : 0;
+  if (mode == SMMC_MODE_GAUSSIAN) {
+    const int def = smmc::gauss_tbl_default(philox_rounds == 7 ? 7 : 10);
+    if (v.gauss_tbl < 0) return def;
+#ifdef SMMC_EXPERIMENT
+    return v.gauss_tbl;
+#else
+    return (v.gauss_tbl == 0 || v.gauss_tbl == def) ? v.gauss_tbl : def;
+#endif
+  }
+  if (mode == SMMC_MODE_SOBOL_GAUSSIAN) {
+    if (v.sobol_tbl < 0) return smmc::kSobolTblDefault;
+    if (v.sobol_tbl == 0) return 0;
+    if (v.sobol_tbl == 1 || v.sobol_tbl == 0xFF) return 0xFF;
+#ifdef SMMC_EXPERIMENT
+    return v.sobol_tbl;
+#else
+    return smmc::kSobolTblDefault;
+#endif
+  }
   return 0;
 }
+bool uses_sincos_table(int mode, const smmc::Variant &v, int philox_rounds) { return gauss_table_mask(mode, v, philox_rounds) != 0; }
 
 // the RNG-stream / arithmetic constants of a config (shared by the introspection and trajectory kernels; enqueue()
 // sets the same fields for the simulation kernel)
@@ -625,7 +641,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   const int bins = cfg->hist_bins;
   const int slen = smmc_stats_len(bins);
   const smmc::Variant variant = current_variant();
-  const bool sincos = uses_sincos_table(cfg->mode, variant);
+  const bool sincos = uses_sincos_table(cfg->mode, variant, cfg->philox_rounds);
 
   smmc::LaunchInfo li;
   if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, bins, sel ? sel->targets : 0, has_withdrawals(cfg), sincos, N,
@@ -2025,7 +2041,7 @@ smmc_status smmc_plan_launch(const smmc_config *cfg, int32_t select_targets, int
   smmc::LaunchInfo li;
   const smmc::Variant variant = current_variant();
   if (!smmc::plan_launch(cfg->mode, cfg->n_returns, cfg->n_periods, cfg->hist_bins, select_targets, has_withdrawals(cfg),
-                         uses_sincos_table(cfg->mode, variant), cfg->n_simulations, n_sms, (size_t)smem_optin, variant.warps, variant.ticket, &li))
+                         uses_sincos_table(cfg->mode, variant, cfg->philox_rounds), cfg->n_simulations, n_sms, (size_t)smem_optin, variant.warps, variant.ticket, &li))
     return fail(SMMC_ERR_UNSUPPORTED, "returns table of %d entries does not fit in %llu bytes of shared memory", cfg->n_returns,
                 (unsigned long long)smem_optin);
   plan->grid = li.grid;
@@ -2107,7 +2123,7 @@ smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
   else if (!strcmp(key, "warps")) g_variant.warps = (value >= 1 && value <= smmc::kWarps) ? value : def.warps;
   else if (!strcmp(key, "reduce")) g_variant.reduce = (value == 1 || value == 2) ? value : def.reduce;
   else if (!strcmp(key, "gauss_tbl")) g_variant.gauss_tbl = (value >= 0 && value <= 15) ? value : def.gauss_tbl;
-  else if (!strcmp(key, "sobol_tbl")) g_variant.sobol_tbl = (value == 0 || value == 1) ? value : def.sobol_tbl;
+  else if (!strcmp(key, "sobol_tbl")) g_variant.sobol_tbl = (value >= 0 && value <= 255) ? value : def.sobol_tbl;
   else if (!strcmp(key, "sobol_unroll")) g_variant.sobol_unroll = value > 0 ? value : def.sobol_unroll;
   else if (!strcmp(key, "finals_chunks")) g_variant.finals_chunks = value > 0 ? value : def.finals_chunks;
   else if (!strcmp(key, "select_candidates")) g_variant.select_candidates = (value == 0 || value == 1) ? value : def.select_candidates;

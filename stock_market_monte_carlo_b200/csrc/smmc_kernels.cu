@@ -140,7 +140,8 @@ __global__ void trajectory_kernel(int mode, const __grid_constant__ KParams p, i
       } else {  // Box-Muller on dimension pairs; an unpaired last month takes the inverse CDF (smmc_device.cuh)
         if ((m & 1) == 0) {
           if (m + 1 < P) {
-            if (p.gauss_tbl_mask) sobol_gauss_pair_tbl(x, word(m + 1), p.one, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
+            if ((p.gauss_tbl_mask >> ((uint32_t)(path >> 5) & 7u)) & 1)  // the statistics kernel's choice for this path slot
+              sobol_gauss_pair_tbl(x, word(m + 1), p.one, p.gc, reinterpret_cast<const char *>(p.tbl_rep), g[0], g[1]);
             else sobol_gauss_pair(x, word(m + 1), p.gc, g[0], g[1]);
           } else {
             g[0] = fmaf(erfinv_py(x), p.sigma_sqrt2, p.gc.a);

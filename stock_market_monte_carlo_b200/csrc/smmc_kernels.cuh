@@ -110,6 +110,10 @@ __host__ __device__ inline SmemLayout smem_layout(int bins, uint32_t sel_bytes, 
 constexpr int kGaussTblDefault = 5;      // GAUSSIAN: pairs 0 and 2 of a call take sin/cos from the shared-memory table
 // ... per Philox round count: with 7 rounds the multiplier pipe has more room and the best split moves to pairs 0 and 3
 // (100 M x 360: mask 5 14.98 ms, mask 9 14.70 ms; with 10 rounds mask 5 17.36, mask 9 17.51; profiles/r02_variants_*.txt)
+// SOBOL_GAUSSIAN: path slots (of a lane's eight) whose pairs take sin/cos from the table; slots 3 and 7 use MUFU.SIN/COS.
+// With every pair from the table the kernel is issue-bound (84 % issue, XU 56 %): a MUFU pair is 3 instructions shorter,
+// and a quarter of them balances the two (5 M x 1000: 0xFF 1.935 ms, 0x77 1.847, 0xBB 1.862, 0x6D 1.873, 0x55 1.887, 0x7F 1.950)
+constexpr int kSobolTblDefault = 0x77;
 constexpr int gauss_tbl_default(int rounds) { return rounds == 7 ? 9 : kGaussTblDefault; }
 constexpr int kSobolUnrollDefault = 2;   // SOBOL_BOOTSTRAP month-loop unroll
 
@@ -120,7 +124,7 @@ struct Variant {
   int warps = 0;         // warps per CTA (1..32), 0 = plan_warps
   int reduce = 0;        // reduce_mean kernel: 1 = plain streaming loads, 2 = TMA ring, 0 = by size
   int gauss_tbl = -1;    // GAUSSIAN: table mask (0 = all MUFU), -1 = default
-  int sobol_tbl = -1;    // SOBOL_GAUSSIAN: 0 = MUFU sin/cos, 1 = table, -1 = default (table)
+  int sobol_tbl = -1;    // SOBOL_GAUSSIAN: 0 = MUFU sin/cos, 1 = table for every path slot, 2..255 = slot mask, -1 = default
   int sobol_unroll = 0;  // SOBOL_BOOTSTRAP month unroll (experiment builds), 0 = default
   int finals_chunks = 0; // host-pointer finals pipeline: number of chunks (0 = automatic, 1 = one monolithic launch)
   int finals_threads = 0; // ... and its host copy-out threads (0 = automatic)

@@ -7,7 +7,7 @@ namespace smmc {
 namespace {
 template <int ROUNDS>
 cudaError_t launch_rounds(const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s) {
-  const int tbl = p.tbl_bytes ? (v.gauss_tbl >= 0 ? v.gauss_tbl : gauss_tbl_default(ROUNDS)) : 0;
+  const int tbl = p.tbl_bytes ? p.gauss_tbl_mask : 0;  // chosen by the host (gauss_table_mask): only masks this build has
   switch (tbl) {
     case 0: return v.ilp == 4 ? launch_one<SMMC_MODE_GAUSSIAN, 4, -1, ROUNDS, 0>(p, li, s)
                               : launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 0>(p, li, s);

@@ -312,7 +312,7 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
 #pragma unroll
         for (int j = 0; j < 8; j++) {
           float g0, g1;
-          if (TBL) sobol_gauss_pair_tbl(xr[j], xa[j], one, gc, cell_mask, sc_base, g0, g1);  // sin/cos from the shared-memory table
+          if ((TBL >> j) & 1) sobol_gauss_pair_tbl(xr[j], xa[j], one, gc, cell_mask, sc_base, g0, g1);  // path slot j: table
           else sobol_gauss_pair(xr[j], xa[j], gc, g0, g1);
           tot[j] = fl(__fmul_rn(fl(__fmul_rn(tot[j], g0), m0 + mi), g1), m0 + mi + 1);
         }

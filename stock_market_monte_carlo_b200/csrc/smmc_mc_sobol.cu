@@ -10,7 +10,25 @@ cudaError_t launch_mc_sobol(int mode, const KParams &p, const LaunchInfo &li, co
 #endif
     return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0, kSobolUnrollDefault>(p, li, s);
   }
-  return p.tbl_bytes ? launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 1>(p, li, s)
-                     : launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0>(p, li, s);
+  // TBL: which of a lane's eight path slots take sin/cos from the shared-memory table (the others use MUFU.SIN/COS)
+  if (!p.tbl_bytes) return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0>(p, li, s);
+  switch (p.gauss_tbl_mask) {
+#ifdef SMMC_EXPERIMENT
+    case 0x7F: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0x7F>(p, li, s);
+    case 0x77: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0x77>(p, li, s);
+    case 0x6D: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0x6D>(p, li, s);
+    case 0x55: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0x55>(p, li, s);
+    case 0xBB: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xBB>(p, li, s);
+    case 0xEE: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xEE>(p, li, s);
+    case 0xDD: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xDD>(p, li, s);
+    case 0x3F: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0x3F>(p, li, s);
+    case 0xCF: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xCF>(p, li, s);
+    case 0xB7: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xB7>(p, li, s);
+    case 0xFF: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xFF>(p, li, s);
+#else
+    case 0xFF: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, 0xFF>(p, li, s);
+#endif
+    default: return launch_one<SMMC_MODE_SOBOL_GAUSSIAN, 8, -1, 10, kSobolTblDefault>(p, li, s);
+  }
 }
 }  // namespace smmc

@@ -78,7 +78,7 @@ def test_sincos_table_and_mufu_evaluate_the_same_contract(S, O, mode):
     o = O.simulate(mode, N, P, seed=7, want_finals=True)
     res = {}
     try:
-        for v in (0, 5 if mode == "gaussian" else 1):
+        for v in ((0, 5) if mode == "gaussian" else (0, 1, 0x77)):  # MUFU | the table for every pair / path slot | default mix
             S.set_variant(key, v)
             r = S.simulate(mode, N, P, seed=7, want_finals=True, hist_bins=20)
             np.testing.assert_allclose(r.finals, o.finals, rtol=GAUSS_RTOL)
@@ -89,7 +89,7 @@ def test_sincos_table_and_mufu_evaluate_the_same_contract(S, O, mode):
             res[v] = r
     finally:
         S.set_variant()
-    a, b = list(res.values())
+    a, b = list(res.values())[:2]
     assert float(np.max(np.abs(a.finals / b.finals - 1.0))) < 1e-5
     assert not np.array_equal(a.finals, b.finals)  # the hook really switched kernels
 
