@@ -55,15 +55,16 @@ I_ALG = {"bootstrap_compat": 12, "bootstrap": 12, "gaussian": 12, "sobol_bootstr
 # Philox4x32-7 (smmc_config.philox_rounds = 7): three rounds = 6 IMAD.WIDE + 6 LOP3 less per call of 6 / 8 months
 I_ALG_PHILOX7 = {"bootstrap": 12 - 12 / 6.0, "gaussian": 12 - 12 / 8.0}
 # Pipe floors (cycles per warp-month per SM sub-partition) from the measured reciprocal throughputs in
-# profiles/r01_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the busiest single pipe
+# profiles/r02_pipe_microbench.txt and profiles/r01_pipe_mix_microbench.txt: the busiest single pipe
 # of the shipped instruction mix.  (The minimal-count recipes behind I_ALG are the all-MUFU ones; the shipped Gaussian
 # kernels trade MUFU for a few more FMA/ALU instructions, so I_ALG is NOT raised for them.)
 #   gaussian   pairs 0 and 2 of a call take sin/cos from the shared-memory table: (2 x 4 + 2 x 2) MUFU x 8.0 / 8 months = 12.0 on
 #              the XU pipe; Philox keeps fmaheavy at 9.0 and the ALU pipe at 8.5 -- no single pipe binds (ncu: XU 65 %, issue 72 %)
-#   sobol_gaussian  every pair from the table: XU 8.0; the ALU pipe carries 10 instructions per pair x 2.0 cycles = 10.0
+#   sobol_gaussian  six of a lane's eight path slots from the table, two by MUFU.SIN/COS: XU (2 + 0.25 x 2) x 8.0 / 2 = 10.0; the
+#              kernel is issue-bound (ncu: 11.5 executed instructions per path-month, issue 84.7 %, XU 73.7 %)
 #   bootstrap  Philox: 8 per-lane rounds x 8.39 cycles (2 IMAD.WIDE + 2 LOP3, measured as a unit) per 6 months,
 #              + 16 further ALU-pipe instructions per call (fields, addresses) at their measured marginal 2.0 cycles
-PIPE_FLOOR = {"gaussian": ("xu", 12.0), "sobol_gaussian": ("alu", 10.0),
+PIPE_FLOOR = {"gaussian": ("xu", 12.0), "sobol_gaussian": ("xu", 10.0),
               "bootstrap": ("fmaheavy+alu (Philox)", (8 * 8.39 + 16 * 2.0) / 6.0)}
 I_ALG_SURVEY = {"bootstrap_compat": 12, "bootstrap": 19, "gaussian": 22, "sobol_bootstrap": None, "sobol_gaussian": None}
 
