@@ -170,7 +170,9 @@ smmc_status smmc_comm_info(const smmc_comm *comm, int32_t *n_ranks, int32_t *ran
  * so count / mean / m2 / below_count / hist in `out` describe the GLOBAL run on every rank.  finals / block_means /
  * block_vars, when requested, cover this rank's own range only (they never travel).  Flags as for smmc_run: host
  * pointers (blocking) by default; DEVICE_POINTERS [+ NO_SYNC] runs on cfg->stream, fully asynchronously with NO_SYNC
- * (read the merged vector from out->stats_dev).  Collective: every rank must call it. */
+ * (read the merged vector from out->stats_dev).  Collective: every rank must call it.  Host-pointer runs that return block
+ * partials of >= 16 Mi paths per rank are launched in two parts (the first part's download hides behind the second
+ * kernel) and issue two such all-reduces, on every rank alike. */
 smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *comm);
 /* first path (relative to cfg->stream_offset) and number of paths of rank `rank` of `n_ranks` for a run of n paths */
 smmc_status smmc_rank_range(int64_t n_simulations, int32_t n_ranks, int32_t rank, int64_t *first, int64_t *count);

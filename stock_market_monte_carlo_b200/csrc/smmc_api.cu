@@ -14,6 +14,7 @@
 #include <sys/mman.h>
 #endif
 #include <atomic>
+#include <chrono>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -1166,6 +1167,114 @@ smmc_status run_finals_pipelined(std::vector<Shard> &shards, const smmc_config *
   return SMMC_OK;
 }
 
+// ---- block partials into host memory: the download of the first part hides behind the second part's kernel -------------
+// reduceBlock-style runs (block_means / block_vars, no finals) return 8 bytes per 256 paths: 3.1 MB at 10^8 paths, into the
+// caller's pageable -- usually freshly allocated -- arrays: 0.55 ms behind a 17.4 ms kernel when it is one copy after one
+// launch (measured, tools/exp_e2e.py).  Each shard is therefore launched in two parts (7/8 of its launch waves, then the
+// rest; the path id is the RNG offset, so the values are those of one launch); the first part's partials are downloaded on
+// the copy stream while the second part computes -- a pageable cudaMemcpyAsync blocks the host, which has nothing else to
+// do -- and only the last eighth is exposed.  Statistics: the two allreduce-ready vectors are added on the host.
+constexpr int64_t kSplitMinPaths = (int64_t)16 << 20;
+
+// api / nccl (smmc_run_rank): every part's vector is all-reduced over the ranks on the kernel's stream before it is downloaded
+// (two collectives per call, on every rank alike).
+smmc_status run_partials_split(std::vector<Shard> &shards, const smmc_config *cfg, std::vector<double> *total, float *device_ms,
+                               int *launches, const smmc::NcclApi *api = nullptr, smmc::NcclComm nccl = nullptr) {
+  const int slen = smmc_stats_len(cfg->hist_bins);
+  const size_t S = shards.size();
+  std::vector<int64_t> n_first(S, 0);
+  *launches = 0;
+  // ---- enqueue both parts of every shard
+  for (size_t s = 0; s < S; s++) {
+    Shard &sh = shards[s];
+    Context *ctx = sh.ctx;
+    const int64_t n = sh.cfg.n_simulations;
+    if (n <= 0 && !api) continue;  // (with a communicator an empty rank still takes part in the two collectives)
+    CU(cudaSetDevice(ctx->device));
+    const int64_t wave = (int64_t)ctx->n_sms * smmc::kWarps * SMMC_BLOCK;
+    const int64_t waves = n / wave;
+    n_first[s] = waves >= 8 ? (waves - (waves + 7) / 8) * wave : 0;  // whole waves; 0 = too small to split
+    const int64_t nb = (n + SMMC_BLOCK - 1) / SMMC_BLOCK;
+    if (sh.bmeans) CU(ctx->bmeans.reserve((size_t)nb * 4));
+    if (sh.bvars) CU(ctx->bvars.reserve((size_t)nb * 4));
+    CU(ctx->chunk_stats.reserve((size_t)2 * slen * sizeof(double)));
+    if (ctx->chunk_stats_host_cap < (size_t)2 * slen) {
+      if (ctx->chunk_stats_host) cudaFreeHost(ctx->chunk_stats_host);
+      ctx->chunk_stats_host = nullptr;
+      ctx->chunk_stats_host_cap = 0;
+      CU(cudaMallocHost(&ctx->chunk_stats_host, (size_t)2 * slen * sizeof(double)));
+      ctx->chunk_stats_host_cap = (size_t)2 * slen;
+    }
+    CU(cudaEventRecord(ctx->red0, ctx->stream));
+    for (int part = 0; part < 2; part++) {
+      const int64_t p0 = part == 0 ? 0 : n_first[s], cnt = part == 0 ? n_first[s] : n - n_first[s];
+      double *stats_dev = (double *)ctx->chunk_stats.p + (size_t)part * slen;
+      if (cnt <= 0) {  // unsplit shard: part 0 is empty (an empty rank: both)
+        CU(cudaMemsetAsync(stats_dev, 0, (size_t)slen * sizeof(double), ctx->stream));
+      } else {
+        smmc_config cc = sh.cfg;
+        cc.stream_offset = sh.cfg.stream_offset + (uint64_t)p0;
+        cc.n_simulations = cnt;
+        DeviceOutputs d;
+        d.bmeans = sh.bmeans ? (float *)ctx->bmeans.p + p0 / SMMC_BLOCK : nullptr;
+        d.bvars = sh.bvars ? (float *)ctx->bvars.p + p0 / SMMC_BLOCK : nullptr;
+        d.stats = stats_dev;
+        EnqueueOpts o;
+        o.dout = &d;
+        o.reuse_table = part == 1 && n_first[s] > 0;
+        smmc_result dummy;
+        memset(&dummy, 0, sizeof dummy);
+        Pending pd;
+        smmc_status st = enqueue(&cc, &dummy, ctx, &pd, nullptr, o);
+        if (st != SMMC_OK) return st;
+        *launches += pd.launches;
+      }
+      if (part == 0) CU(cudaEventRecord(ctx->kdone[0], ctx->stream));
+      if (api) {
+        const int r = api->AllReduce(stats_dev, stats_dev, (size_t)slen, smmc::kNcclFloat64, smmc::kNcclSum, nccl, ctx->stream);
+        if (r != 0) return fail(SMMC_ERR_CUDA, "ncclAllReduce failed: %s", api->GetErrorString(r));
+      }
+      CU(cudaMemcpyAsync(ctx->chunk_stats_host + (size_t)part * slen, stats_dev, (size_t)slen * sizeof(double), cudaMemcpyDeviceToHost,
+                         ctx->stream));
+    }
+    CU(cudaEventRecord(ctx->red1, ctx->stream));
+  }
+  // ---- first parts: downloaded while the second parts compute
+  for (size_t s = 0; s < S; s++) {
+    Shard &sh = shards[s];
+    Context *ctx = sh.ctx;
+    const size_t nbA = (size_t)(n_first[s] / SMMC_BLOCK);
+    if (nbA == 0) continue;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->kdone[0], 0));
+    if (sh.bmeans) CU(cudaMemcpyAsync(sh.bmeans, ctx->bmeans.p, nbA * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (sh.bvars) CU(cudaMemcpyAsync(sh.bvars, ctx->bvars.p, nbA * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+  }
+  // ---- second parts, statistics, timing
+  total->assign((size_t)slen, 0.0);
+  *device_ms = 0.0f;
+  for (size_t s = 0; s < S; s++) {
+    Shard &sh = shards[s];
+    Context *ctx = sh.ctx;
+    const int64_t n = sh.cfg.n_simulations;
+    if (n <= 0 && !api) continue;
+    CU(cudaSetDevice(ctx->device));
+    const size_t nb = (size_t)((n + SMMC_BLOCK - 1) / SMMC_BLOCK), nbA = (size_t)(n_first[s] / SMMC_BLOCK);
+    if (sh.bmeans && nb > nbA)
+      CU(cudaMemcpyAsync(sh.bmeans + nbA, (float *)ctx->bmeans.p + nbA, (nb - nbA) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sh.bvars && nb > nbA)
+      CU(cudaMemcpyAsync(sh.bvars + nbA, (float *)ctx->bvars.p + nbA, (nb - nbA) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_stream));
+    for (int part = 0; part < 2; part++)
+      for (int k = 0; k < slen; k++) (*total)[(size_t)k] += ctx->chunk_stats_host[(size_t)part * slen + k];
+    float ms = 0.0f;
+    CU(cudaEventElapsedTime(&ms, ctx->red0, ctx->red1));
+    if (ms > *device_ms) *device_ms = ms;
+  }
+  return SMMC_OK;
+}
+
 smmc_status multi_comms(int n_gpus, const std::vector<smmc::NcclComm> **out);
 smmc_status need_nccl(const smmc::NcclApi **api);
 
@@ -1182,6 +1291,9 @@ smmc_status run_host(const smmc_config *cfg, const std::vector<Context *> &ctxs,
   for (const Shard &sh : shards) biggest = std::max(biggest, (int64_t)sh.cfg.n_simulations);
   if (out->finals && variant.finals_chunks != 1 && (biggest >= kPipelineMinPaths || variant.finals_chunks > 1)) {
     smmc_status st = run_finals_pipelined(shards, cfg, &total, &ms_max, &launches);
+    if (st != SMMC_OK) return st;
+  } else if (!out->finals && (out->block_means || out->block_vars) && variant.finals_chunks != 1 && biggest >= kSplitMinPaths) {
+    smmc_status st = run_partials_split(shards, cfg, &total, &ms_max, &launches);
     if (st != SMMC_OK) return st;
   } else {
     // every device's launch is enqueued before anything waits, and every download is issued before any is awaited
@@ -1600,6 +1712,26 @@ smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *c
   c2.n_simulations = count;
   st = validate(&c2, out, false);  // 32-bit id limits of COMPAT / Sobol apply to the shard as well
   if (st != SMMC_OK) return st;
+  const bool host_ptrs = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) == 0;
+  if (host_ptrs && !out->finals && (out->block_means || out->block_vars) && current_variant().finals_chunks != 1 &&
+      cfg->n_simulations / comm->n_ranks >= kSplitMinPaths) {
+    // block partials into host memory: two launches (and two collectives) so that most of the download hides behind the
+    // second kernel; the criterion is a function of the job, not of the shard, so every rank takes the same branch
+    std::vector<Shard> one(1);
+    one[0].ctx = ctx;
+    one[0].cfg = c2;
+    one[0].bmeans = out->block_means;
+    one[0].bvars = out->block_vars;
+    std::vector<double> total;
+    float ms = 0.0f;
+    int launches = 0;
+    st = run_partials_split(one, cfg, &total, &ms, &launches, api, comm->nccl);
+    if (st != SMMC_OK) return st;
+    out->device_ms = ms;
+    out->gpu_launches = launches;
+    return smmc_stats_finalize(total.data(), cfg->hist_bins, cfg->initial_capital, &out->count, &out->below_count, &out->mean,
+                               &out->m2, out->hist);
+  }
   Pending pd;
   st = enqueue(&c2, out, ctx, &pd);
   if (st != SMMC_OK) return st;

@@ -393,3 +393,40 @@ def test_ticket_launch_quantiles_and_partial_last_block(S, table):
     q = S.quantiles("bootstrap", N, P, returns=table, seed=3)
     assert np.array_equal(q, np.sort(r.finals)[S.quartile_ranks(N)])
     assert r.count == N and abs(r.mean - float(np.mean(r.finals.astype(np.float64)))) <= 1e-9 * r.mean
+
+
+# ---- block partials into host memory: two launches, the first download hidden behind the second kernel ---------------------
+@pytest.mark.parametrize("mode", ["bootstrap_compat", "gaussian"])
+def test_split_launch_for_block_partials_changes_nothing(S, table, mode):
+    """host-pointer runs of >= 16 Mi paths that ask for block partials (no finals) are launched in two parts so that 7/8 of the
+    download overlaps the second kernel: block partials, histogram and counters are those of one launch, mean / M2 agree to
+    fp64 rounding (two allreduce-ready vectors added on the host)."""
+    kw = mode_kwargs(mode, table)
+    N, P = (16 << 20) + 148 * 32 * 256 * 3 + 77, 6
+    split = S.simulate(mode, N, P, hist_bins=32, target=1001.0, want_block_partials=True, **kw)
+    try:
+        S.set_variant("finals_chunks", 1)  # one monolithic launch
+        mono = S.simulate(mode, N, P, hist_bins=32, target=1001.0, want_block_partials=True, **kw)
+    finally:
+        S.set_variant()
+    assert split.gpu_launches > mono.gpu_launches
+    assert np.array_equal(split.block_means.view(np.uint32), mono.block_means.view(np.uint32))
+    assert np.array_equal(split.block_vars.view(np.uint32), mono.block_vars.view(np.uint32))
+    assert np.array_equal(split.hist, mono.hist) and split.below_count == mono.below_count and split.count == mono.count == N
+    assert abs(split.mean - mono.mean) <= 1e-12 * abs(mono.mean) and abs(split.m2 - mono.m2) <= 1e-9 * abs(mono.m2)
+
+
+def test_run_rank_split_launch_two_gpus(S, table):
+    """the same through smmc_run_rank on two ranks (two launches and two collectives per rank): block partials of the ranks
+    concatenate to those of one GPU, merged statistics equal the single-GPU run's"""
+    if _n_gpus(S) < 2:
+        pytest.skip("needs 2 GPUs")
+    N, P = 2 * ((16 << 20) + 148 * 32 * 256 * 2) + 1000, 4
+    one = S.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True)
+    res = _two_rank_job(S, lambda c: c.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True))
+    for r in res:
+        assert r.gpu_launches >= 2
+        assert r.count == N and r.below_count == one.below_count and np.array_equal(r.hist, one.hist)
+        assert abs(r.mean - one.mean) <= 1e-12 * abs(one.mean) and abs(r.m2 - one.m2) <= 1e-9 * abs(one.m2)
+    assert np.array_equal(np.concatenate([res[0].block_means, res[1].block_means]), one.block_means)
+    assert np.array_equal(np.concatenate([res[0].block_vars, res[1].block_vars]), one.block_vars)
