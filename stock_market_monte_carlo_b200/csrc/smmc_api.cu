@@ -133,6 +133,7 @@ struct Context {
   cudaEvent_t red0 = nullptr, red1 = nullptr;  // around the reduce_mean kernel (smmc_reduce_mean_device)
   DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_full, sobol_shift, selhist, sincos, block_moments;
   bool sincos_ready = false;
+  uint32_t sincos_kbits = 0;  // bits of the GaussConsts::k the table was scaled for
   bool sobol_full_ready = false;
   // Small host-built tables (withdrawal schedule, per-launch Sobol tables) are cached by content in a ring of device
   // versions: an unchanged table costs no upload at all; a changed one goes into the next slot, ordered behind the last
@@ -608,12 +609,19 @@ const float *sincos_table_of(const Context *ctx, int mode) {
   return (const float *)(mode == SMMC_MODE_GAUSSIAN ? base + smmc::kSinCosBytes : base);
 }
 
-smmc_status prepare_sincos(Context *ctx, cudaStream_t st) {
-  if (ctx->sincos_ready) return SMMC_OK;
+// The table holds sqrt(-k) * (cos, sin): it belongs to a value of gauss_std and is rebuilt (one 3 us kernel on `st`, ordered behind
+// the last use of the workspace like every other write to it) when that changes.  *rebuilt: a kernel was launched.
+smmc_status prepare_sincos(Context *ctx, float k, cudaStream_t st, bool *rebuilt = nullptr) {
+  if (rebuilt) *rebuilt = false;
+  uint32_t kbits;
+  memcpy(&kbits, &k, sizeof kbits);
+  if (ctx->sincos_ready && ctx->sincos_kbits == kbits) return SMMC_OK;
   CU(ctx->sincos.reserve(2 * (size_t)smmc::kSinCosBytes));  // [swizzled copy (SOBOL_GAUSSIAN)][linear copy (GAUSSIAN)]
-  smmc::launch_sincos_table((float *)ctx->sincos.p, st);
+  smmc::launch_sincos_table((float *)ctx->sincos.p, std::sqrt(-(double)k), st);
   CU(cudaGetLastError());
   ctx->sincos_ready = true;
+  ctx->sincos_kbits = kbits;
+  if (rebuilt) *rebuilt = true;
   return SMMC_OK;
 }
 
@@ -695,8 +703,8 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
     p.bc.row_shift = 2;
     while ((1u << p.bc.row_shift) < (uint32_t)li.rep * 4u) p.bc.row_shift++;
   } else if (sincos) {
-    const bool fresh = !ctx->sincos_ready;
-    smmc_status ss = prepare_sincos(ctx, st);
+    bool fresh = false;
+    smmc_status ss = prepare_sincos(ctx, p.gc.k, st, &fresh);
     if (ss != SMMC_OK) return ss;
     if (fresh) pd->launches++;
     p.tbl_rep = sincos_table_of(ctx, cfg->mode);
@@ -2109,6 +2117,8 @@ smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *va
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(cudaSetDevice(cfg->device));
   cudaStream_t s = ctx->stream;
+  st = order_after_last_use(ctx, s);  // the cached buffers written below may still be read by an asynchronous launch
+  if (st != SMMC_OK) return st;
   const int P = cfg->n_periods, n = cfg->n_returns;
   smmc::KParams p;
   memset(&p, 0, sizeof p);
@@ -2142,7 +2152,7 @@ smmc_status smmc_trajectories(const smmc_config *cfg, int32_t n_paths, float *va
   st = prepare_flow(ctx, cfg, s, &p, &flow_slot);
   if (st != SMMC_OK) return st;
   if (p.gauss_tbl_mask) {  // the Gaussian modes' sin/cos table (read from global memory here)
-    st = prepare_sincos(ctx, s);
+    st = prepare_sincos(ctx, p.gc.k, s);
     if (st != SMMC_OK) return st;
     p.tbl_rep = sincos_table_of(ctx, cfg->mode);
   }

@@ -251,8 +251,8 @@ __device__ __forceinline__ void gauss_pair_tbl(uint32_t w, uint32_t one, uint32_
   const float mr = __uint_as_float((w & 0xFFFFFu) | one);
   const float u = fmaf(mr, 8.0f, -7.99999952316284179688f);
   float cv, sv;
-  sincos_tbl<false>(w * kAngleHash, one, cell_mask, sc_tbl, cv, sv);
-  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  sincos_tbl<false>(w * kAngleHash, one, cell_mask, sc_tbl, cv, sv);  // the table is pre-scaled by sqrt(-k)
+  const float rs = sqrt_approx(-lg2_approx(u));
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);
 }
@@ -282,7 +282,7 @@ __device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, u
   const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
   float cv, sv;
   sincos_tbl<true>(xa, one, 0u, sc_tbl, cv, sv);
-  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  const float rs = sqrt_approx(-lg2_approx(u));
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);
 }
@@ -292,7 +292,7 @@ __device__ __forceinline__ void sobol_gauss_pair_tbl(uint32_t xr, uint32_t xa, u
   const float u = fmaf(__uint2float_rn(xr), 2.3283064365386963e-10f, 1.1641532182693481e-10f);  // 2^-32, 2^-33
   float cv, sv;
   sincos_tbl_swz_u32(xa, one, cell_mask, sc_base, cv, sv);
-  const float rs = sqrt_approx(lg2_approx(u) * gc.k);
+  const float rs = sqrt_approx(-lg2_approx(u));
   g0 = fmaf(rs, cv, gc.a);
   g1 = fmaf(rs, sv, gc.a);
 }

@@ -50,18 +50,21 @@ __global__ void sort_table_kernel(const float *__restrict__ src, int n, float *_
   }
 }
 
-// (cos, sin) of the cell centres 2 pi (i + 1/2) / kSinCosCells, evaluated in double and rounded once (sincos_tbl)
-__global__ void sincos_table_kernel(float *__restrict__ dst) {
+// scale * (cos, sin) of the cell centres 2 pi (i + 1/2) / kSinCosCells, evaluated in double and rounded once (sincos_tbl).
+// scale = sqrt(-k) = std/100 * sqrt(2 ln 2): the Box-Muller radius of a table pair is then sqrt(-lg2 u) with the negation
+// folded into the MUFU operand -- the FMUL by k of the MUFU pairs is not needed (gauss_pair_tbl).
+__global__ void sincos_table_kernel(float *__restrict__ dst, double scale) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= kSinCosCells) return;
   double sv, cv;
   sincospi(2.0 * ((double)i + 0.5) / (double)kSinCosCells, &sv, &cv);
+  const float c = (float)(scale * cv), sn = (float)(scale * sv);
   const uint32_t slot = sincos_slot((uint32_t)i);  // bank swizzle, see sincos_tbl
-  dst[2 * slot] = (float)cv;
-  dst[2 * slot + 1] = (float)sv;
+  dst[2 * slot] = c;
+  dst[2 * slot + 1] = sn;
   float *lin = dst + 2 * kSinCosCells;  // the linear copy GAUSSIAN reads
-  lin[2 * i] = (float)cv;
-  lin[2 * i + 1] = (float)sv;
+  lin[2 * i] = c;
+  lin[2 * i + 1] = sn;
 }
 
 // ---- trajectory mode ------------------------------------------------------------------------------------------------
@@ -480,7 +483,7 @@ cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, const Va
   }
 }
 
-void launch_sincos_table(float *dst, cudaStream_t s) { sincos_table_kernel<<<kSinCosCells / 256, 256, 0, s>>>(dst); }
+void launch_sincos_table(float *dst, double scale, cudaStream_t s) { sincos_table_kernel<<<kSinCosCells / 256, 256, 0, s>>>(dst, scale); }
 
 cudaError_t launch_select_candidates(const uint32_t *keys_dev, const unsigned long long *count_dev, unsigned long long capacity,
                                      int targets, int digit_shift, uint32_t digit_mask, int prefix_shift,

@@ -157,7 +157,7 @@ void launch_sort_table(const float *src, int n, float *dst, cudaStream_t s);
 
 cudaError_t launch_mc(int mode, const KParams &p, const LaunchInfo &li, const Variant &v, cudaStream_t s);
 // fills dst[kSinCosCells][2] with (cos, sin) of the cell centres, correctly rounded from double (once per device)
-void launch_sincos_table(float *dst, cudaStream_t s);
+void launch_sincos_table(float *dst, double scale, cudaStream_t s);  // scale = sqrt(-GaussConsts::k)
 
 // introspection kernels (parity tests)
 // sobol_full: [n_dims][32] direction numbers (device), only read in the Sobol modes
