@@ -430,3 +430,15 @@ def test_run_rank_split_launch_two_gpus(S, table):
         assert abs(r.mean - one.mean) <= 1e-12 * abs(one.mean) and abs(r.m2 - one.m2) <= 1e-9 * abs(one.m2)
     assert np.array_equal(np.concatenate([res[0].block_means, res[1].block_means]), one.block_means)
     assert np.array_equal(np.concatenate([res[0].block_vars, res[1].block_vars]), one.block_vars)
+
+
+@pytest.mark.parametrize("mode", ["gaussian", "sobol_gaussian"])
+def test_sincos_table_follows_gauss_std(S, O, mode):
+    """the table is scaled by std/100 sqrt(2 ln 2): alternating standard deviations (and std = 0) must each get their own"""
+    N, P = 5000, 36
+    for std in (0.8333, 2.5, 0.0, 0.8333, 0.1):
+        o = O.simulate(mode, N, P, seed=3, gauss_mean=0.4, gauss_std=std, want_finals=True)
+        r = S.simulate(mode, N, P, seed=3, gauss_mean=0.4, gauss_std=std, want_finals=True)
+        np.testing.assert_allclose(r.finals, o.finals, rtol=GAUSS_RTOL)
+        t = S.trajectories(mode, 40, P, seed=3, gauss_mean=0.4, gauss_std=std)
+        assert np.array_equal(t[:, -1], r.finals[:40])
