@@ -1,5 +1,5 @@
 #!/bin/bash
-# experiment build: parity tests of the touched modes, then variant timings.  usage: bash tools/gpu_exp4.sh "<pytest -k expr>" <groups...>
+# experiment build: parity tests of the touched modes, then variant timings.  usage: bash tools/gpu_exp.sh "<pytest -k expr>" <groups...>
 mkdir -p gpurun_out
 k=$1; shift
 export SMMC_LIB=stock_market_monte_carlo_b200/lib_exp/libsmmc.so

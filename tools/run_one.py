@@ -16,6 +16,7 @@ for a in sys.argv[4:]:
             bins = int(v)
         else:
             S.set_variant(k, int(v))
+S.set_variant("finals_chunks", 1)  # one monolithic launch: the capture is of the whole workload (no split partials download)
 if "bootstrap" in mode:
     kw["returns"] = S.synthetic_sp500_table(1200)
 if mode == "bootstrap_compat":
