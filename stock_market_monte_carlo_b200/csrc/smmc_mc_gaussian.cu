@@ -15,11 +15,11 @@ cudaError_t launch_rounds(const KParams &p, const LaunchInfo &li, const Variant 
     case 1: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 1>(p, li, s);
     case 3: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 3>(p, li, s);
     case 6: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 6>(p, li, s);
-    case 7: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 7>(p, li, s);
     case 10: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 10>(p, li, s);
     case 12: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 12>(p, li, s);
     case 15: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 15>(p, li, s);
-    case (ROUNDS == 7 ? 5 : 9): return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, (ROUNDS == 7 ? 5 : 9)>(p, li, s);
+    case (ROUNDS == 7 ? 5 : 7): return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, (ROUNDS == 7 ? 5 : 7)>(p, li, s);
+    case 9: return launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, 9>(p, li, s);
 #endif
     default: return v.ilp == 4 ? launch_one<SMMC_MODE_GAUSSIAN, 4, -1, ROUNDS, gauss_tbl_default(ROUNDS)>(p, li, s)
                                : launch_one<SMMC_MODE_GAUSSIAN, 8, -1, ROUNDS, gauss_tbl_default(ROUNDS)>(p, li, s);
