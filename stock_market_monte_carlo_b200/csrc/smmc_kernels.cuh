@@ -111,6 +111,10 @@ constexpr int kGaussTblDefault = 5;      // GAUSSIAN: pairs 0 and 2 of a call ta
 // ... per Philox round count: with 7 rounds the multiplier pipe has more room and three table pairs per call are best
 // (100 M x 360 with the pre-scaled table: mask 5 14.78 ms, 9 14.64, 15 14.63, 7 14.56; with 10 rounds mask 5 17.11, 9 17.32,
 // 7 17.46, 15 17.39; profiles/r02_variants_*.txt)
+// SOBOL_GAUSSIAN: path slots (of a lane's eight) whose pairs take sin/cos from the table; slots 3 and 7 use MUFU.SIN/COS.
+// With every pair from the table the kernel is issue-bound (84 % issue, XU 56 %): a MUFU pair is 3 instructions shorter,
+// and a quarter of them balances the two (5 M x 1000: 0xFF 1.935 ms, 0x77 1.847, 0xBB 1.862, 0x6D 1.873, 0x55 1.887, 0x7F 1.950)
+constexpr int kSobolTblDefault = 0x77;
 constexpr int gauss_tbl_default(int rounds) { return rounds == 7 ? 7 : kGaussTblDefault; }
 constexpr int kSobolUnrollDefault = 2;   // SOBOL_BOOTSTRAP month-loop unroll
 
