@@ -7,7 +7,17 @@ cudaError_t launch_mc_sobol(int mode, const KParams &p, const LaunchInfo &li, co
 #ifdef SMMC_EXPERIMENT
     if (v.sobol_unroll == 4) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0, 4>(p, li, s);
     if (v.sobol_unroll == 8) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0, 8>(p, li, s);
+    if (p.rep4 == 128u) {
+      if (v.sobol_unroll == 100) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0xFF, kSobolUnrollDefault>(p, li, s);
+      if (v.sobol_unroll == 101) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0, kSobolUnrollDefault>(p, li, s);
+      if (v.sobol_unroll == 102) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0x11, kSobolUnrollDefault>(p, li, s);
+      if (v.sobol_unroll == 103) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0x77, kSobolUnrollDefault>(p, li, s);
+    }
 #endif
+    // 32 table copies (rows of 128 bytes, every table up to ~1800 entries): half of a lane's path slots form the row address by a
+    // shift-add on the ALU pipe, the other half by an IMAD on the multiplier pipe the IMAD.HI index already fills (5 M x 1000,
+    // same box: all IMAD 1.433 ms, slots 0x55 by LEA 1.397, 0x77 1.402, all LEA 1.406, 0x11 1.435)
+    if (p.rep4 == 128u) return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, kSobolBootLeaSlots, kSobolUnrollDefault>(p, li, s);
     return launch_one<SMMC_MODE_SOBOL_BOOTSTRAP, 8, -1, 10, 0, kSobolUnrollDefault>(p, li, s);
   }
   // TBL: which of a lane's eight path slots take sin/cos from the shared-memory table (the others use MUFU.SIN/COS)
