@@ -115,7 +115,7 @@ constexpr int kGaussTblDefault = 5;      // GAUSSIAN: pairs 0 and 2 of a call ta
 // With every pair from the table the kernel is issue-bound (84 % issue, XU 56 %): a MUFU pair is 3 instructions shorter,
 // and a quarter of them balances the two (5 M x 1000: 0xFF 1.935 ms, 0x77 1.847, 0xBB 1.862, 0x6D 1.873, 0x55 1.887, 0x7F 1.950)
 constexpr int kSobolTblDefault = 0x77;
-constexpr int kSobolBootLeaSlots = 0x55;  // SOBOL_BOOTSTRAP with 128-byte rows: path slots whose row address is an ALU shift-add
+constexpr int kSobolBootImmSlots = 0x55;  // SOBOL_BOOTSTRAP with 128-byte rows: path slots whose row stride is an immediate
 constexpr int gauss_tbl_default(int rounds) { return rounds == 7 ? 7 : kGaussTblDefault; }
 constexpr int kSobolUnrollDefault = 2;   // SOBOL_BOOTSTRAP month-loop unroll
 

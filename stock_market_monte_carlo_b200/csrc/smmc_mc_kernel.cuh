@@ -301,8 +301,8 @@ __device__ __forceinline__ void run_sobol(const KParams &p, const Flow<FLOW> &fl
         month_words(m0 + mi, __shfl_sync(0xffffffffu, U, mi), x);
 #pragma unroll
         for (int j = 0; j < 8; j++) {
-          // TBL (SOBOL_BOOTSTRAP): path slots whose row address is a shift-add on the ALU pipe (LEA; rows of 128 bytes, i.e.
-          // 32 table copies) instead of an IMAD on the multiplier pipe that the IMAD.HI index already fills
+          // TBL (SOBOL_BOOTSTRAP): path slots whose row stride is the constant 128 (32 table copies): IMAD with an immediate
+          // multiplier instead of a register one (smmc_mc_sobol.cu)
           if ((TBL >> j) & 1) tot[j] = fl(fmaf(tot[j], lds_f32((__umulhi(x[j], n) << 7) + lane_base), tot[j]), m0 + mi);
           else tot[j] = fl(boot_step(tot[j], x[j], n, rep4, lane_base), m0 + mi);
         }
