@@ -138,8 +138,8 @@ smmc_status smmc_run(const smmc_config *cfg, smmc_result *out);
 
 /* Multi-GPU, single process, one host thread (the reference's driver model, src/simulations.cu:576-655): shards
  * [0,N) into n_gpus contiguous 256-aligned path ranges by RNG offset, runs them concurrently on devices
- * 0..n_gpus-1 and merges the partial statistics on the host.  Results are identical to a 1-GPU run of the same
- * config (histogram / counts bit-identical; mean/M2 to fp64 rounding). Host pointers only. */
+ * 0..n_gpus-1 and merges the partial statistics (see below: on the devices).  Results are identical to a 1-GPU run of the
+ * same config (histogram / counts bit-identical; mean/M2 to fp64 rounding). Host pointers only. */
 smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out);
 /* (statistics-only runs of smmc_run_multi merge on the DEVICES: one communicator per device from ncclCommInitAll, one
  * grouped ncclAllReduce, one 864-byte download from device 0; runs that return all finals stream them through the host

@@ -442,3 +442,28 @@ def test_sincos_table_follows_gauss_std(S, O, mode):
         np.testing.assert_allclose(r.finals, o.finals, rtol=GAUSS_RTOL)
         t = S.trajectories(mode, 40, P, seed=3, gauss_mean=0.4, gauss_std=std)
         assert np.array_equal(t[:, -1], r.finals[:40])
+
+
+def test_ranks_example_program_one_thread_per_gpu(S, tmp_path):
+    """examples/benchmark_mc_ranks.cpp: the one-rank-per-GPU C binding of INTEGRATION.md section 4 as a compiled program (plain
+    C ABI, one thread per rank, as many ranks as the box has GPUs, at most 2): smmc_comm_*, smmc_run_rank and smmc_quantiles_rank
+    give every rank the statistics and quartiles of the whole run, equal to the single-GPU entry points'."""
+    import os
+    import re
+    import subprocess
+    from conftest import ROOT
+    from stock_market_monte_carlo_b200 import _native
+    libdir = os.path.dirname(_native.LIB_PATH)
+    exe = tmp_path / "benchmark_mc_ranks"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", "-o", str(exe), os.path.join(ROOT, "examples", "benchmark_mc_ranks.cpp"),
+                    f"-I{ROOT}/include", f"-L{libdir}", "-lsmmc", f"-Wl,-rpath,{libdir}"], check=True)
+    n_ranks = min(_n_gpus(S), 2)
+    N, P = 1_000_003, 24
+    out = subprocess.run([str(exe), str(n_ranks), str(P), str(N), "7"], capture_output=True, text=True, check=True).stdout
+    one = S.simulate("gaussian", N, P, seed=7, hist_bins=100)
+    q = S.quantiles("gaussian", N, P, seed=7)
+    mean, std, below = re.search(r"mean: ([\d.]+) \| std: ([\d.]+) \| below target: (\d+)", out).groups()
+    assert abs(float(mean) - one.mean) < 1e-4 and abs(float(std) - one.std) < 1e-4 and int(below) == one.below_count
+    got = [float(v) for v in re.search(r"quartiles: ([\d.]+) ([\d.]+) ([\d.]+) ([\d.]+) ([\d.]+)", out).groups()]
+    np.testing.assert_allclose(got, q.astype(np.float64), rtol=0, atol=1e-4 + 1e-7 * float(q.max()))
+    assert f"ranks: {n_ranks} " in out and f"n_simulations: {N} " in out
