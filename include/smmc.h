@@ -202,6 +202,24 @@ smmc_status smmc_reduce_mean(const float *vec, int64_t n, int32_t device, float 
  * 4 bytes per element. */
 smmc_status smmc_reduce_mean_device(const float *vec_dev, int64_t n, int32_t device, void *stream, float *mean_out,
                                     float *kernel_ms);
+/* The mean of n device-resident floats for hosts in which this library must not allocate device memory.  NO COUNTERPART IN
+ * THE REFERENCE (its reduce_mean_gpu cudaMallocs on every call, src/simulations.cu:283-289).
+ * Callers it is for: a service whose own arena or caching allocator already owns the whole GPU, so that a cudaMalloc made by
+ * a plugin fails; a host with work in flight on other streams, which a cudaMalloc/cudaFree would stall device-wide; a
+ * deployment with a memory budget fixed at load time.  Every other compute entry point here builds a per-device context
+ * and grows cudaMalloc'ed buffers on demand; this one calls no cudaMalloc / cudaFree / allocating routine at all.
+ * Its scratch (one fp64 partial per 32768 floats + ticket + sum) is a fixed 262 400-byte __device__ array inside the
+ * library: every GPU that loads the library's module holds it until the process exits.
+ *   - n must be <= SMMC_NOALLOC_MAX_N; larger n returns SMMC_ERR_INVALID_ARG (use smmc_reduce_mean_device or reduce in pieces).
+ *   - vec_dev: any 4-byte-aligned pointer into `device` memory; mean_out: HOST float.  Launched on `stream` (NULL = legacy
+ *     default stream); blocks until the result is on the host.  Same arithmetic as smmc_reduce_mean_device (fp64
+ *     accumulation, mean = (float)(sum / n)); the order of the additions differs, so the two agree to fp64 rounding.
+ *   - All calls on a device share the one array and it keeps the previous call's contents; each call clears the words that
+ *     must start at zero.  Calls are serialised inside the process; GPU work of two calls that overlapped would race.
+ *   - The FIRST call on each device resolves the array's device address (cudaGetSymbolAddress, may load the module): make
+ *     that call before starting any stream capture. */
+#define SMMC_NOALLOC_MAX_N 1073741824LL /* 2^30 floats = 4 GiB */
+smmc_status smmc_reduce_mean_device_noalloc(const float *vec_dev, int64_t n, int32_t device, void *stream, float *mean_out);
 /* out = a + b on the device (reference vector_add_gpu, src/gpu.cu:17-47). Host pointers. */
 smmc_status smmc_vector_add(float *out, const float *a, const float *b, int64_t n, int32_t device);
 /* The same over DEVICE-resident vectors (any 4-byte alignment; 16-byte aligned pointers take the vector path), on `stream`

@@ -13,6 +13,7 @@ SMMC_ABI_VERSION = 3
 SMMC_BLOCK = 256
 SMMC_STATS_HEADER = 6
 SMMC_MAX_HIST_BINS = 4096
+SMMC_NOALLOC_MAX_N = 1 << 30
 
 MODE_BOOTSTRAP_COMPAT = 0
 MODE_BOOTSTRAP = 1
@@ -109,7 +110,7 @@ class SmmcError(RuntimeError):
 
 # every symbol include/smmc.h declares (tests check the library exports exactly these)
 C_ABI_SYMBOLS = [
-    "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_vector_add", "smmc_vector_add_device",
+    "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_reduce_mean_device_noalloc", "smmc_vector_add", "smmc_vector_add_device",
     "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
@@ -149,6 +150,8 @@ def load():
     lib.smmc_reduce_mean.restype = C.c_int
     lib.smmc_reduce_mean_device.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, P(C.c_float), P(C.c_float)]
     lib.smmc_reduce_mean_device.restype = C.c_int
+    lib.smmc_reduce_mean_device_noalloc.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, P(C.c_float)]
+    lib.smmc_reduce_mean_device_noalloc.restype = C.c_int
     lib.smmc_vector_add.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]
     lib.smmc_vector_add.restype = C.c_int
     lib.smmc_debug_draws.argtypes = [P(SmmcConfig), C.c_int32, C.c_void_p]

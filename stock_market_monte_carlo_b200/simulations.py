@@ -268,6 +268,17 @@ def reduce_mean_device(ptr, n, device=0, stream=0):
     return float(out.value), float(ms.value)
 
 
+def reduce_mean_device_noalloc(ptr, n, device=0, stream=0):
+    """Mean of n floats resident on `device`, through smmc_reduce_mean_device_noalloc: for processes in which the library
+    may not allocate device memory (the GPU is fully owned by the host's own allocator, other streams must not be stalled
+    by cudaMalloc, or the memory budget is fixed at load time).  Scratch is a fixed array inside the library, so
+    n <= SMMC_NOALLOC_MAX_N (2**30) and calls on one device must not overlap.  No counterpart in the reference."""
+    lib = N.load()
+    out = C.c_float()
+    N.check(lib.smmc_reduce_mean_device_noalloc(int(ptr), int(n), int(device), int(stream) or None, C.byref(out)))
+    return float(out.value)
+
+
 def vector_add_device(out_ptr, a_ptr, b_ptr, n, device=0, stream=0):
     """out = a + b over device-resident float vectors (data_ptr()s); returns the kernel's CUDA-event time in ms."""
     lib = N.load()
