@@ -547,6 +547,7 @@ def main():
               f"NCCL_DEBUG_FILE={os.environ['NCCL_DEBUG_FILE']}", file=sys.stderr)
         dist.init_process_group("nccl", device_id=dev)  # launcher plumbing: barrier + max-over-ranks of the timings
         from stock_market_monte_carlo_b200.distributed import init_comm
+        S.set_variant("verbose", 1)  # libsmmc's own "rank r nranks N cudaDev d" line (silent by default)
         comm = init_comm(local)  # the path's own communicator: ncclCommInitRank inside libsmmc.so (smmc_run_rank)
 
     mode, B, P = wl["mode"], wl["paths"], wl["periods"]

@@ -143,7 +143,8 @@ smmc_status smmc_run(const smmc_config *cfg, smmc_result *out);
 smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out);
 /* (statistics-only runs of smmc_run_multi merge on the DEVICES: one communicator per device from ncclCommInitAll, one
  * grouped ncclAllReduce, one 864-byte download from device 0; runs that return all finals stream them through the host
- * anyway and sum the per-chunk vectors there.) */
+ * anyway and sum the per-chunk vectors there.  When NCCL cannot be loaded or ncclCommInitAll fails, smmc_run_multi and
+ * smmc_quantiles(n_gpus > 1) download every device's vector and add them on the host: they never fail for want of NCCL.) */
 
 /* ---- one rank per GPU: the collective behind the C ABI ---------------------------------------------------------
  * The reference drives all GPUs from one host thread and re-runs the SAME paths on every device
@@ -151,8 +152,9 @@ smmc_status smmc_run_multi(const smmc_config *cfg, int n_gpus, smmc_result *out)
  * offset and merges the O(KB) statistics vector with a single ncclAllReduce(ncclFloat64, ncclSum) enqueued on the
  * same stream as the kernel: count / below / S1 / S2 / histogram are all sum-reducible and the integer fields are
  * exact in fp64, so the merged histogram and counts are bit-identical for every number of ranks.  No per-path data
- * ever crosses NVLink.  NCCL is bound at run time (dlopen of libnccl.so.2): when it is absent these entry points fail
- * with SMMC_ERR_UNSUPPORTED -- there is no host-side stand-in. */
+ * ever crosses NVLink.  NCCL is bound at run time (dlopen of libnccl.so.2): when it is absent the rank entry points
+ * (smmc_comm_*, smmc_run_rank, smmc_quantiles_rank) fail with SMMC_ERR_UNSUPPORTED -- ranks of different processes have
+ * no host-side stand-in. */
 typedef struct smmc_comm smmc_comm;     /* opaque: an ncclComm_t plus the rank's device */
 #define SMMC_COMM_ID_BYTES 128          /* = NCCL_UNIQUE_ID_BYTES */
 /* rank 0: ncclGetUniqueId into id[SMMC_COMM_ID_BYTES]; distribute the bytes to the other ranks by any means. */
@@ -323,13 +325,21 @@ smmc_status smmc_debug_philox(const uint32_t *ctr, const uint32_t *key, int32_t 
 /* The same with `rounds` in {7, 10} (smmc_config.philox_rounds): the device code behind both stream contracts. */
 smmc_status smmc_debug_philox_rounds(const uint32_t *ctr, const uint32_t *key, int32_t rounds, int32_t n, int32_t device,
                                      uint32_t *out);
-/* Test hook: selects among the compiled variants of a kernel (all variants of a mode produce the same draws; the tests use
- * this to prove it).  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
+/* Test hook: selects among the compiled variants of a kernel.  Every variant of a mode consumes the same INTEGER draws
+ * (Philox words, table indices, Sobol words) and the integer / table modes return identical results under every key; the
+ * tests use the hook to prove that.  The two Gaussian modes are bit-reproducible only for a fixed build AND a fixed table
+ * mask: "gauss_tbl" / "sobol_tbl" move sin/cos between the MUFU unit and the shared-memory table, which changes finals by
+ * about 1e-5 relative, and the default GAUSSIAN mask depends on philox_rounds (5 for 10 rounds, 7 for 7).  The Gaussian
+ * finals also changed between ABI 2 and ABI 3 (table pre-scaled by sqrt(-k)).  The hook is process-wide: changing a mask
+ * between smmc_run, smmc_trajectories and smmc_quantiles of one configuration breaks their bit-identity, so set it once,
+ * before the first call, or not at all.  Keys: "ilp" (paths per lane in flight: 2|4|8), "warps" (warps per CTA, 1..32), "reduce"
  * (reduce_mean kernel: 1 = streaming loads, 2 = TMA ring), "gauss_tbl" (GAUSSIAN: 4-bit mask of the Box-Muller pairs of a
  * call that take sin/cos from the shared-memory table; 0 = all MUFU), "sobol_tbl" (SOBOL_GAUSSIAN: 0 = MUFU, 1 = table), "sobol_unroll",
  * "finals_chunks" (host-pointer finals pipeline: 1 = one monolithic launch), "finals_threads" (its host copy-out threads),
  * "select_candidates" (0 = the third select pass always replays), "ticket" (256-path blocks handed to warps 0 = statically,
  * 1 = by an atomic ticket with the block moments merged in block order; default: ticket for launches of 1..48 waves).
+ * "host_merge" (1 = smmc_run_multi / smmc_quantiles add their shards on the host, as they do when NCCL cannot be loaded),
+ * "verbose" (1 = smmc_comm_init_rank prints one line per rank on stderr; the library prints nothing otherwise).
  * value < 0 (or 0 where 0 is not a choice) restores the default; key NULL resets everything.  Process-wide; nothing in the library reads the environment. */
 smmc_status smmc_debug_set_variant(const char *key, int32_t value);
 

@@ -465,9 +465,16 @@ smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream
   p->sobol_lo_bytes = (uint32_t)ppad * 32u;
   if (ppad == 0) return SMMC_OK;
   const uint64_t tag = (seed * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)n_periods << 1) ^ 1ull;
-  int slot = versioned_find(ctx->sobol_v, tag, nullptr, 0);
+  // The tag only narrows the search (it can collide for some (seed, n_periods) pairs): a cached version is reused only when
+  // the exact key stored behind its tables -- n_periods and both halves of the seed -- is the one asked for.
+  const uint32_t key[3] = {(uint32_t)n_periods, (uint32_t)seed, (uint32_t)(seed >> 32)};
+  int slot = -1;
+  for (int i = 0; i < Context::kVersions && slot < 0; i++) {
+    const std::vector<unsigned char> &c = ctx->sobol_v.content[i];
+    if (c.size() >= sizeof key && ctx->sobol_v.tag[i] == tag && memcmp(c.data() + c.size() - sizeof key, key, sizeof key) == 0) slot = i;
+  }
   if (slot < 0) {
-    std::vector<uint32_t> buf((size_t)ppad * 8 + (size_t)smmc::kSobolHiRows * ppad + 2, 0u);
+    std::vector<uint32_t> buf((size_t)ppad * 8 + (size_t)smmc::kSobolHiRows * ppad + 3, 0u);
     uint32_t *lo = buf.data(), *hi = buf.data() + (size_t)ppad * 8;
     for (int m = 0; m < n_periods; m++) {
       const uint32_t *Vm = V + (size_t)m * 32;
@@ -483,9 +490,8 @@ smmc_status prepare_sobol(Context *ctx, int n_periods, uint64_t seed, cudaStream
           hi[(size_t)(2 + 16 * g + c) * ppad + m] = x;
         }
     }
-    // the exact (n_periods, seed) rides behind the tables so that a tag collision cannot alias two configurations
-    buf[buf.size() - 2] = (uint32_t)n_periods;
-    buf[buf.size() - 1] = (uint32_t)(seed ^ (seed >> 32));
+    // the exact (n_periods, seed) rides behind the tables: compared above on lookup, and by versioned_upload (whole content)
+    memcpy(&buf[buf.size() - 3], key, sizeof key);
     smmc_status us = versioned_upload(ctx->sobol_v, tag, buf.data(), buf.size() * 4, st, &slot);
     if (us != SMMC_OK) return us;
   }
@@ -1285,6 +1291,7 @@ smmc_status run_partials_split(std::vector<Shard> &shards, const smmc_config *cf
 
 smmc_status multi_comms(int n_gpus, const std::vector<smmc::NcclComm> **out);
 smmc_status need_nccl(const smmc::NcclApi **api);
+const std::vector<smmc::NcclComm> *multi_comms_or_null(int n_gpus);
 
 // Host-pointer run of cfg over the devices of `ctxs` (1 = smmc_run, more = smmc_run_multi); caller holds every ctx->mu.
 smmc_status run_host(const smmc_config *cfg, const std::vector<Context *> &ctxs, smmc_result *out) {
@@ -1318,13 +1325,15 @@ smmc_status run_host(const smmc_config *cfg, const std::vector<Context *> &ctxs,
     }
     // several devices: ONE grouped ncclAllReduce of the statistics vectors, in place, each on its kernel's stream -- the
     // merge happens on the devices (NVLink), and only device 0's 864 bytes are read back
-    const bool merged_on_device = shards.size() > 1 && rc == SMMC_OK;
-    if (merged_on_device) {
-      const std::vector<smmc::NcclComm> *comms = nullptr;
-      const smmc::NcclApi *api = nullptr;
-      rc = need_nccl(&api);
-      if (rc == SMMC_OK) rc = multi_comms((int)shards.size(), &comms);
-      if (rc == SMMC_OK) {
+    // Without NCCL (libnccl.so.2 not loadable, or no communicator over these devices) the per-shard vectors are downloaded
+    // and added on the host instead, as the pipelined-finals and split-partials branches above do: a single-process
+    // multi-GPU call never fails for want of NCCL.  (smmc_run_rank / smmc_quantiles_rank have no such stand-in.)
+    bool merged_on_device = false;
+    if (shards.size() > 1 && rc == SMMC_OK) {
+      const std::vector<smmc::NcclComm> *comms = multi_comms_or_null((int)shards.size());
+      const smmc::NcclApi *api = comms ? smmc::nccl_api() : nullptr;
+      if (api) {
+        merged_on_device = true;
         int r = api->GroupStart();
         for (size_t g = 0; g < launched && r == 0; g++)
           r = api->AllReduce(pend[g].stats_dev, pend[g].stats_dev, (size_t)slen, smmc::kNcclFloat64, smmc::kNcclSum, (*comms)[g], pend[g].stream);
@@ -1399,6 +1408,30 @@ smmc_status multi_comms(int n_gpus, const std::vector<smmc::NcclComm> **out) {
   }
   *out = &v;
   return SMMC_OK;
+}
+
+// smmc_shutdown: the communicators die with the contexts whose streams they were used on
+void release_multi_comms() {
+  std::lock_guard<std::mutex> lk(g_multi_mu);
+  const smmc::NcclApi *api = smmc::nccl_api();
+  for (std::vector<smmc::NcclComm> &v : g_multi_comms) {
+    if (api)
+      for (smmc::NcclComm c : v)
+        if (c) api->CommDestroy(c);
+    v.clear();
+  }
+}
+
+// The communicators of smmc_run_multi / smmc_quantiles, or null when the shards have to be merged on the host: NCCL cannot be
+// loaded, ncclCommInitAll fails on these devices, or the test hook "host_merge" asks for that path.
+const std::vector<smmc::NcclComm> *multi_comms_or_null(int n_gpus) {
+  if (current_variant().host_merge == 1 || !smmc::nccl_api()) return nullptr;
+  const std::vector<smmc::NcclComm> *comms = nullptr;
+  if (multi_comms(n_gpus, &comms) != SMMC_OK) {
+    g_err[0] = 0;  // not an error of the call: the host merge takes over
+    return nullptr;
+  }
+  return comms;
 }
 
 // ---- select passes: replay, or -- for the last 10 key bits -- a pass over the candidate keys of the previous replay --------
@@ -1643,12 +1676,15 @@ smmc_status smmc_comm_init_rank(const void *id, int32_t n_ranks, int32_t rank, i
   *comm = out;
   int ver = 0;
   api->GetVersion(&ver);
-  // one line per rank on stderr (stdout stays free for the caller's own output, e.g. bench.py's JSON line)
-  fprintf(stderr, "smmc: NCCL %d communicator ready: rank %d nranks %d cudaDev %d\n", ver, rank, n_ranks, device);
+  // a library stays silent unless asked: smmc_debug_set_variant("verbose", 1) (bench.py does) gives one line per rank on
+  // stderr (stdout stays free for the caller's own output, e.g. bench.py's JSON line)
+  if (current_variant().verbose == 1)
+    fprintf(stderr, "smmc: NCCL %d communicator ready: rank %d nranks %d cudaDev %d\n", ver, rank, n_ranks, device);
   return SMMC_OK;
 }
 
 smmc_status smmc_comm_adopt(void *nccl_comm, int32_t device, smmc_comm **comm) {
+  DeviceGuard device_guard;  // get_context may switch the device; the caller's choice is restored on every return path
   if (!nccl_comm || !comm) return fail(SMMC_ERR_INVALID_ARG, "comm_adopt: null argument");
   const smmc::NcclApi *api = nullptr;
   smmc_status st = need_nccl(&api);
@@ -1762,6 +1798,10 @@ namespace {
 // sum of n device floats on `st`; blocks until done; kernel_ms (nullable) = CUDA-event time of the reduction kernel
 smmc_status reduce_sum_device(Context *ctx, const float *v_dev, int64_t n, cudaStream_t st, double *sum, float *kernel_ms) {
   const size_t part = (size_t)ctx->n_sms * 4 * sizeof(double);
+  // ctx->work also holds the CTA partials, histogram and ticket of a simulation launch: a SMMC_FLAG_NO_SYNC run that is still in
+  // flight on another stream must finish with them before this reduction overwrites them (and later users wait for this one)
+  smmc_status os = order_after_last_use(ctx, st);
+  if (os != SMMC_OK) return os;
   CU(ctx->work.reserve(part + 32));
   char *w = (char *)ctx->work.p;
   CU(cudaMemsetAsync(w + part, 0, 32, st));
@@ -1770,6 +1810,8 @@ smmc_status reduce_sum_device(Context *ctx, const float *v_dev, int64_t n, cudaS
   CU(smmc::launch_reduce_sum(v_dev, n, (double *)w, (unsigned int *)(w + part + 16), (double *)(w + part), ctx->n_sms,
                              current_variant().reduce, st));
   if (kernel_ms) CU(cudaEventRecord(e1, st));
+  os = mark_last_use(ctx, st);
+  if (os != SMMC_OK) return os;
   CU(cudaMemcpyAsync(sum, w + part, sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   if (kernel_ms) CU(cudaEventElapsedTime(kernel_ms, e0, e1));
@@ -2002,15 +2044,27 @@ smmc_status select_loop(std::vector<Shard> &shards, const std::vector<smmc::Nccl
     }
     std::fill(total.begin(), total.end(), 0ull);
     float ms_pass = 0.0f;
+    // merged on the devices: shard 0 holds the sum.  No communicator (one shard, or NCCL absent in smmc_quantiles): every
+    // shard's histogram is downloaded and the words are added on the host.
+    std::vector<uint64_t> parts(comms || S == 1 ? 0 : S * words_all, 0ull);
     for (size_t g = 0; g < S; g++) {
       Context *ctx = shards[g].ctx;
       CU(cudaSetDevice(ctx->device));
-      if (g == 0)
+      if (g == 0 && parts.empty())
         CU(cudaMemcpyAsync(total.data(), hd[g], (size_t)words[g] * sizeof(uint64_t), cudaMemcpyDeviceToHost, streams[g]));
+      else if (!parts.empty())
+        CU(cudaMemcpyAsync(parts.data() + g * words_all, hd[g], (size_t)words[g] * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                           streams[g]));
+    }
+    for (size_t g = 0; g < S; g++) {
+      Context *ctx = shards[g].ctx;
+      CU(cudaSetDevice(ctx->device));
       CU(cudaStreamSynchronize(streams[g]));
       float ms = 0.0f;
       CU(cudaEventElapsedTime(&ms, ctx->ev0[slots[g]], ctx->ev1[slots[g]]));
       if (ms > ms_pass) ms_pass = ms;
+      if (!parts.empty())
+        for (size_t i = 0; i < (size_t)words[g]; i++) total[i] += parts[g * words_all + i];
     }
     *ms_total += ms_pass;
     smmc_status st = smmc_select_advance(sel, total.data());
@@ -2043,11 +2097,8 @@ smmc_status smmc_quantiles(const smmc_config *cfg, int32_t n_gpus, int32_t n_tar
     st = get_context(n_gpus == 1 ? cfg->device : g, &ctxs[(size_t)g]);
     if (st != SMMC_OK) return st;
   }
-  const std::vector<smmc::NcclComm> *comms = nullptr;
-  if (n_gpus > 1) {
-    st = multi_comms(n_gpus, &comms);
-    if (st != SMMC_OK) return st;
-  }
+  // null = one device, or no NCCL: select_loop then adds the shards' digit histograms on the host
+  const std::vector<smmc::NcclComm> *comms = n_gpus > 1 ? multi_comms_or_null(n_gpus) : nullptr;
   std::vector<Shard> shards;
   make_shards(cfg, &dummy, ctxs, &shards);
   for (int g = 0; g < n_gpus; g++) ctxs[(size_t)g]->mu.lock();
@@ -2218,6 +2269,8 @@ smmc_status smmc_debug_draws(const smmc_config *cfg, int32_t n_paths, uint32_t *
   fill_stream_params(cfg, &p);
   const size_t bytes = (size_t)n_paths * (size_t)cfg->n_periods * 4;
   if (bytes == 0) return SMMC_OK;
+  st = order_after_last_use(ctx, ctx->stream);  // the Sobol tables rebuilt below may still be read by an asynchronous launch
+  if (st != SMMC_OK) return st;
   CU(ctx->scratch.reserve(bytes));
   const uint32_t *full_dev = nullptr, *shift_dev = nullptr;
   if (is_sobol(cfg->mode)) {
@@ -2270,6 +2323,8 @@ smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
   else if (!strcmp(key, "finals_chunks")) g_variant.finals_chunks = value > 0 ? value : def.finals_chunks;
   else if (!strcmp(key, "select_candidates")) g_variant.select_candidates = (value == 0 || value == 1) ? value : def.select_candidates;
   else if (!strcmp(key, "ticket")) g_variant.ticket = (value == 0 || value == 1) ? value : def.ticket;
+  else if (!strcmp(key, "verbose")) g_variant.verbose = value == 1 ? 1 : def.verbose;
+  else if (!strcmp(key, "host_merge")) g_variant.host_merge = value == 1 ? 1 : def.host_merge;
   else if (!strcmp(key, "finals_threads")) g_variant.finals_threads = (value > 0 && value <= 64) ? value : def.finals_threads;
   else return fail(SMMC_ERR_INVALID_ARG, "debug_set_variant: unknown key '%s'", key);
   return SMMC_OK;
@@ -2358,6 +2413,7 @@ void smmc_shutdown(void) {
     cudaStreamDestroy(c.stream);
     c.ready = false;
   }
+  release_multi_comms();
 }
 
 }  // extern "C"

@@ -132,6 +132,8 @@ struct Variant {
   int finals_threads = 0; // ... and its host copy-out threads (0 = automatic)
   int select_candidates = -1;  // 0 = the third select pass always replays (no candidate buffer), -1 / 1 = default
   int ticket = -1;       // block assignment: 0 = static, 1 = ticket, -1 = by launch size (plan_ticket)
+  int verbose = 0;       // 1 = smmc_comm_init_rank reports its communicator on stderr (one line per rank); silent otherwise
+  int host_merge = 0;    // 1 = smmc_run_multi / smmc_quantiles merge their shards on the host as if NCCL could not be loaded
 };
 
 constexpr int kTicketMaxWaves = 48;  // launches of fewer waves of 256-path blocks take the ticket (the tail matters there)
