@@ -477,11 +477,74 @@ def ref_gpu_same_box(S):
                                     "value_by_own_kernel_clock": N * P / k if k > 0 else None}
     t, _ = best(lambda: O.ref_mc_simulations_gpu(N, P, V0, table), reps=2)
     out["reference_all_finals"] = {"wall_ms": 1e3 * t, "value": N * P / t}
+    # the reference's kernels by a real clock: CUDA events around the unmodified kernels (oracle/ref_shim/ref_gpu_event_driver.cu)
+    if O.ref_available("libref_gpu_events.so"):
+        ev_rb = O.ref_kernel_event_ms("reduceBlock", N, P, V0, table, reps=5)
+        ev_fin = O.ref_kernel_event_ms("finals", N, P, V0, table, reps=3)
+        out["reference_kernel_event_ms"] = ev_rb
+        out["reference_finals_kernel_event_ms"] = ev_fin
+        out["reference_reduceBlock"]["value_by_event"] = N * P / (ev_rb * 1e-3)
+        out["event_how"] = ("mc_simulations_gpu_kernel_reduceBlock<256> / mc_simulations_gpu_kernel<256> (src/simulations.cu:185-247, "
+                            ":112-152), compiled unmodified for sm_100a, between cudaEvents; mean of 5 / 3 launches after a warm-up")
     t, r = best(lambda: S.simulate("bootstrap_compat", N, P, returns=table, want_block_partials=True))
     out["this_build_compat_block_partials"] = {"wall_ms": 1e3 * t, "value": N * P / t, "kernel_ms": r.device_ms, "value_kernel": N * P / (r.device_ms * 1e-3)}
     t, r = best(lambda: S.simulate("bootstrap_compat", N, P, returns=table, want_finals=True))
     out["this_build_compat_all_finals"] = {"wall_ms": 1e3 * t, "value": N * P / t, "device_span_ms": r.device_ms,
                                            "how": "smmc_run, host buffers: chunked launches, D2H and host copy-out pipelined"}
+    return out
+
+
+def cpu_v2_leg():
+    """BASELINE config 1 itself: the reference's CPU v2 (`mc_simulations`, src/simulations.cpp:204-266, the call of
+    examples/benchmark_mc_cpu_v2.cpp:32) at 360 months x 1 M paths on this box's host cores, from oracle/_ref/libref_cpu.so
+    (the unmodified reference source).  One warm-up run, then three timed runs."""
+    cpu = CpuReference("bootstrap", 360)
+    n = 1_000_000
+    cpu.run(n)
+    ts = [cpu.run(n)[0] for _ in range(3)]
+    return {"workload": "C1: 360 months x 1 M bootstrap paths, reference CPU v2", "kind": cpu.kind, "cores": cpu.cores,
+            "seconds_best": min(ts), "seconds_mean": sum(ts) / len(ts), "value": n * 360 / min(ts), "unit": UNIT, "how": cpu.desc}
+
+
+def r4(x):
+    """4 significant digits (the summary has to fit the 1500-character tail the driver keeps)"""
+    return None if x is None else float(f"{float(x):.4g}")
+
+
+def make_summary(extras):
+    """The numbers BASELINE.md section 5 quotes, compact, for the END of the JSON line."""
+    out = {}
+    legs = (extras or {}).get("workloads") or {}
+    for k in ("c3", "c3compat", "c4", "c4boot", "c2_philox7", "c3_philox7"):
+        if k in legs:
+            out[k] = [r4(legs[k]["value"] / 1e9), r4(legs[k]["kernel_ms"]), r4(legs[k]["roofline"]["frac"])]
+    for k in ("reduce_mean", "vector_add"):
+        if k in legs:
+            out[k] = [r4(legs[k]["value"] / 1e9), r4(legs[k]["kernel_ms"]), r4(legs[k]["roofline"]["frac"])]
+    if "c3" in legs and "e2e" in legs["c3"]:
+        out["c3_e2e"] = [r4(legs["c3"]["e2e"]["value"] / 1e9), legs["c3"]["e2e"]["h2d_bytes_per_step"]]
+    c5 = (extras or {}).get("c5")
+    if c5:
+        out["c5"] = [r4(c5["ms_per_step"]), c5["hist_sha256"][:12], r4(c5["closed_form"]["mean_rel_err"]),
+                     r4(c5["closed_form"]["std_rel_err"])]
+    v2 = (extras or {}).get("cpu_v2")
+    if v2 and "value" in v2:
+        out["cpu_v2"] = [r4(v2["value"] / 1e9), v2["cores"]]
+    rg = (extras or {}).get("ref_gpu_same_box") or {}
+    if "reference_reduceBlock" in rg:
+        out["ref_gpu"] = [r4(rg["reference_reduceBlock"]["wall_ms"]), r4(rg["reference_all_finals"]["wall_ms"]),
+                          r4(rg["this_build_compat_block_partials"]["wall_ms"]), r4(rg["this_build_compat_all_finals"]["wall_ms"])]
+        if rg.get("reference_kernel_event_ms"):
+            out["ref_kernel_event_ms"] = r4(rg["reference_kernel_event_ms"])
+    se = (extras or {}).get("sharded_equals_single")
+    if se:
+        out["all_modes_identical"] = se["all_modes_identical"]
+        out["modes"] = sorted(k for k, v in se["modes"].items() if v)
+    if "quartiles_device_ms" in (extras or {}):
+        out["quartiles_ms"] = [r4(extras["quartiles_device_ms"]), r4(extras.get("quartiles_riding_along_extra_ms"))]
+    out["keys"] = ("legs [G path-months/s (G elements/s: reduce_mean, vector_add), kernel_ms, roofline frac]; c3_e2e [G/s, h2d bytes]; "
+                   "c5 [ms_per_step, sha256[:12], mean_rel_err, std_rel_err]; cpu_v2 [G/s, threads]; "
+                   "ref_gpu wall ms [ref reduceBlock, ref finals, ours partials, ours finals]")
     return out
 
 
@@ -708,22 +771,42 @@ def main():
                                         "std_rel_err": float(res5.std / cf_std - 1.0)},
                         "collective": "1 ncclAllReduce per step inside smmc_run_rank" if world > 1 else "none"}
 
-    # ---- sharded == single: a 1 M-path run through the rank path against the same run on one GPU (rank 0 runs both)
+    # ---- sharded == single, every mode: a 1 M-path run through the rank path (finals + block partials + histogram +
+    # quartiles) against the same run on ONE GPU.  Every rank repeats the single-GPU run on its own device and compares its
+    # own path range bit for bit; the verdicts are AND-ed over the ranks.  1 000 003 paths do not divide into equal shards;
+    # the Sobol / COMPAT runs start at a non-zero 256-aligned stream offset.
     if do_extras and world > 1:
         Ns, Ps = 1_000_003, 120
-        kws = dict(initial_capital=V0, seed=77, hist_bins=HIST_BINS, hist_range=(0.0, 20000.0), **GAUSS)
-        sharded = comm.simulate("gaussian", Ns, Ps, **kws)
-        q_sh = comm.quantiles("gaussian", Ns, Ps, initial_capital=V0, seed=77, **GAUSS)
-        if rank == 0:
-            single = S.simulate("gaussian", Ns, Ps, device=local, **kws)
-            q_1 = S.quantiles("gaussian", Ns, Ps, initial_capital=V0, seed=77, device=local, **GAUSS)
-            extras["sharded_equals_single"] = {
-                "paths": Ns, "periods": Ps, "n_ranks": world,
-                "hist_identical": bool(np.array_equal(sharded.hist, single.hist)), "count_identical": sharded.count == single.count,
-                "below_identical": sharded.below_count == single.below_count,
-                "mean_rel_diff": abs(sharded.mean - single.mean) / abs(single.mean), "m2_rel_diff": abs(sharded.m2 - single.m2) / abs(single.m2),
-                "quartiles_identical": bool(np.array_equal(q_sh, q_1)),
-                "how": "Comm.simulate / Comm.quantiles (smmc_run_rank / smmc_quantiles_rank, NCCL inside the C ABI) vs smmc_run / smmc_quantiles on rank 0"}
+        tbl_s = S.synthetic_sp500_table(1200)
+        first_s, count_s = S.rank_range(Ns, world, rank)
+        per_mode, worst_mean, worst_m2 = {}, 0.0, 0.0
+        for m in ("bootstrap_compat", "bootstrap", "gaussian", "sobol_bootstrap", "sobol_gaussian"):
+            kws = dict(initial_capital=V0, seed=0 if m == "bootstrap_compat" else 77, hist_bins=HIST_BINS, hist_range=(0.0, 20000.0),
+                       stream_offset=0 if m in ("bootstrap", "gaussian") else 7 * 256, **GAUSS)
+            if "bootstrap" in m:
+                kws["returns"] = tbl_s
+            sharded = comm.simulate(m, Ns, Ps, want_finals=True, want_block_partials=True, **kws)
+            kwq = {k: v for k, v in kws.items() if k not in ("hist_bins", "hist_range")}
+            q_sh = comm.quantiles(m, Ns, Ps, **kwq)
+            single = S.simulate(m, Ns, Ps, device=local, want_finals=True, want_block_partials=True, **kws)
+            q_1 = S.quantiles(m, Ns, Ps, device=local, **kwq)
+            b0 = first_s // 256
+            ok = (np.array_equal(sharded.finals, single.finals[first_s:first_s + count_s])
+                  and np.array_equal(sharded.block_means, single.block_means[b0:b0 + sharded.block_means.size])
+                  and np.array_equal(sharded.block_vars, single.block_vars[b0:b0 + sharded.block_vars.size])
+                  and np.array_equal(sharded.hist, single.hist) and sharded.count == single.count
+                  and sharded.below_count == single.below_count and np.array_equal(q_sh, q_1))
+            worst_mean = max(worst_mean, abs(sharded.mean - single.mean) / abs(single.mean))
+            worst_m2 = max(worst_m2, abs(sharded.m2 - single.m2) / abs(single.m2))
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            per_mode[m] = bool(flag.item())
+        extras["sharded_equals_single"] = {
+            "paths": Ns, "periods": Ps, "n_ranks": world, "modes": per_mode, "all_modes_identical": all(per_mode.values()),
+            "compared": "finals and block mean/variance partials of each rank's range, histogram, count, below, quartiles: bitwise",
+            "mean_rel_diff_max": worst_mean, "m2_rel_diff_max": worst_m2,
+            "how": "Comm.simulate / Comm.quantiles (smmc_run_rank / smmc_quantiles_rank, NCCL inside the C ABI) vs smmc_run / "
+                   "smmc_quantiles of the whole run on each rank's own GPU; AND over ranks"}
         barrier()
 
     def replay_nccl_log():
@@ -791,11 +874,17 @@ def main():
         legs["vector_add"] = hbm_leg(torch, S, "vector_add", dev, local)
         extras["workloads"] = legs
         try:
+            extras["cpu_v2"] = cpu_v2_leg()
+        except Exception as e:
+            extras["cpu_v2"] = {"unavailable": f"{type(e).__name__}: {e}"}
+        try:
             extras["ref_gpu_same_box"] = ref_gpu_same_box(S)
             rb = extras["ref_gpu_same_box"].get("reference_reduceBlock")
             if rb:
                 for k in ("c3", "c3_philox7", "c3compat"):
                     legs[k]["vs_ref_gpu_same_box"] = {"e2e_wall": legs[k]["value"] / rb["value"],
+                                                      "kernel_event": (extras["ref_gpu_same_box"]["reference_kernel_event_ms"] / legs[k]["kernel_ms"]
+                                                                       if extras["ref_gpu_same_box"].get("reference_kernel_event_ms") else None),
                                                       "reference_own_kernel_clock": (legs[k]["value"] / rb["value_by_own_kernel_clock"]
                                                                                      if rb.get("value_by_own_kernel_clock") else None)}
         except Exception as e:  # the baseline leg must never take the headline down with it
@@ -816,6 +905,7 @@ def main():
         "result": {"count": final.count, "mean": final.mean, "std": final.std, "p_below_target": final.p_below_target},
         "extras": extras or None,
     }
+    line["summary"] = make_summary(extras)  # LAST key: survives in the tail of the line that the driver's record keeps
     replay_nccl_log()
     print(json.dumps(line), flush=True)
     if world > 1:

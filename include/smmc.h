@@ -187,6 +187,12 @@ smmc_status smmc_quantiles_rank(const smmc_config *cfg, smmc_comm *comm, int32_t
  * most 256 are kept), whichever entry point or flags enqueued them.  Blocks until those kernels have finished.
  * This is how an asynchronous caller (SMMC_FLAG_NO_SYNC) times the kernel on the stream it was launched on. */
 smmc_status smmc_kernel_times(int32_t device, float *ms_out, int32_t max_n, int32_t *n_out);
+/* WHICH kernel each of those entries was (same ring, same order): a full simulation / replay of the paths, or the pass
+ * over the candidate keys that replaces the third replay of a select.  Lets a caller (and the tests) see what a call
+ * launched without inferring it from durations.  No counterpart in the reference (it has one kernel per call). */
+#define SMMC_KERNEL_SIMULATION 1          /* smmc::mc_kernel<...> */
+#define SMMC_KERNEL_SELECT_CANDIDATES 2   /* smmc::select_candidates_kernel */
+smmc_status smmc_kernel_kinds(int32_t device, int32_t *kinds_out, int32_t max_n, int32_t *n_out);
 
 int32_t smmc_stats_len(int32_t hist_bins);
 /* stats: HOST vector of smmc_stats_len(bins) doubles (e.g. after an allreduce). hist may be NULL. */

@@ -295,3 +295,17 @@ def ref_gpu_last_kernel_seconds():
     lib = ref_lib("libref_gpu.so")
     lib.ref_last_kernel_seconds.restype = C.c_double
     return float(lib.ref_last_kernel_seconds())
+
+
+def ref_kernel_event_ms(which, n, n_periods, initial_capital, returns, reps=5):
+    """CUDA-event duration (ms, mean of `reps` launches after a warm-up) of the reference's own kernel, compiled unmodified for
+    sm_100a: which = "reduceBlock" (src/simulations.cu:185-247) or "finals" (:112-152), launched as its launcher does."""
+    lib = ref_lib("libref_gpu_events.so")
+    lib.ref_kernel_event_ms.argtypes = [C.c_int, C.c_long, C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_int]
+    lib.ref_kernel_event_ms.restype = C.c_float
+    r = np.ascontiguousarray(np.asarray(returns, dtype=np.float32))
+    ms = float(lib.ref_kernel_event_ms(0 if which == "reduceBlock" else 1, int(n), int(n_periods), float(initial_capital),
+                                       r.ctypes.data, int(r.size), int(reps)))
+    if ms <= 0.0:
+        raise RuntimeError(f"reference kernel event timing failed ({ms})")
+    return ms

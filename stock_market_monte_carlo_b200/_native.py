@@ -14,6 +14,8 @@ SMMC_BLOCK = 256
 SMMC_STATS_HEADER = 6
 SMMC_MAX_HIST_BINS = 4096
 SMMC_NOALLOC_MAX_N = 1 << 30
+KERNEL_SIMULATION = 1
+KERNEL_SELECT_CANDIDATES = 2
 
 MODE_BOOTSTRAP_COMPAT = 0
 MODE_BOOTSTRAP = 1
@@ -111,7 +113,7 @@ class SmmcError(RuntimeError):
 # every symbol include/smmc.h declares (tests check the library exports exactly these)
 C_ABI_SYMBOLS = [
     "smmc_run", "smmc_run_multi", "smmc_run_select", "smmc_stats_len", "smmc_stats_finalize", "smmc_reduce_mean", "smmc_reduce_mean_device", "smmc_reduce_mean_device_noalloc", "smmc_vector_add", "smmc_vector_add_device",
-    "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
+    "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_kernel_kinds", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
     "smmc_comm_unique_id", "smmc_comm_init_rank", "smmc_comm_adopt", "smmc_comm_destroy", "smmc_comm_info", "smmc_run_rank",
@@ -164,6 +166,8 @@ def load():
     lib.smmc_debug_set_variant.restype = C.c_int
     lib.smmc_kernel_times.argtypes = [C.c_int32, C.c_void_p, C.c_int32, P(C.c_int32)]
     lib.smmc_kernel_times.restype = C.c_int
+    lib.smmc_kernel_kinds.argtypes = [C.c_int32, C.c_void_p, C.c_int32, P(C.c_int32)]
+    lib.smmc_kernel_kinds.restype = C.c_int
     lib.smmc_select_begin.argtypes = [P(SmmcSelectState), C.c_int32, C.c_void_p]
     lib.smmc_select_begin.restype = C.c_int
     lib.smmc_select_pass.argtypes = [P(SmmcConfig), P(SmmcSelectState), C.c_void_p]

@@ -130,6 +130,7 @@ struct Context {
   // ring of event pairs around the simulation kernel of the last kEventRing launches (smmc_kernel_times)
   cudaEvent_t ev0[kEventRing] = {}, ev1[kEventRing] = {};
   uint64_t ev_head = 0;  // launches recorded so far
+  int ev_kind[kEventRing] = {};  // SMMC_KERNEL_* of each ring entry (smmc_kernel_kinds)
   cudaEvent_t red0 = nullptr, red1 = nullptr;  // around the reduce_mean kernel (smmc_reduce_mean_device)
   DevBuf returns, sorted, tbl, work, stats, finals, bmeans, bvars, scratch, sobol_full, sobol_shift, selhist, sincos, block_moments;
   bool sincos_ready = false;
@@ -802,6 +803,7 @@ smmc_status enqueue(const smmc_config *cfg, const smmc_result *out, Context *ctx
   CU(cudaEventRecord(ctx->ev0[slot], st));
   CU(smmc::launch_mc(cfg->mode, p, li, variant, st));
   CU(cudaEventRecord(ctx->ev1[slot], st));
+  ctx->ev_kind[slot] = SMMC_KERNEL_SIMULATION;
   ctx->ev_head++;
   pd->ev_slot = slot;
   pd->launches++;
@@ -1511,6 +1513,7 @@ smmc_status select_pass_enqueue(Context *ctx, const smmc_config *cfg, const smmc
                                         ctx->cand_capacity, sp.targets, sp.digit_shift, sp.digit_mask, sp.prefix_shift, sp.prefix, hd,
                                         ctx->n_sms, stream));
       CU(cudaEventRecord(ctx->ev1[slot], stream));
+      ctx->ev_kind[slot] = SMMC_KERNEL_SELECT_CANDIDATES;
       ctx->ev_head++;
       st = mark_last_use(ctx, stream);
       if (st != SMMC_OK) return st;
@@ -2327,6 +2330,20 @@ smmc_status smmc_debug_set_variant(const char *key, int32_t value) {
   else if (!strcmp(key, "host_merge")) g_variant.host_merge = value == 1 ? 1 : def.host_merge;
   else if (!strcmp(key, "finals_threads")) g_variant.finals_threads = (value > 0 && value <= 64) ? value : def.finals_threads;
   else return fail(SMMC_ERR_INVALID_ARG, "debug_set_variant: unknown key '%s'", key);
+  return SMMC_OK;
+}
+
+smmc_status smmc_kernel_kinds(int32_t device, int32_t *kinds_out, int32_t max_n, int32_t *n_out) {
+  DeviceGuard device_guard;  // the caller's current device is restored on every return path
+  if (!kinds_out || !n_out || max_n < 0) return fail(SMMC_ERR_INVALID_ARG, "kernel_kinds: bad arguments");
+  Context *ctx = nullptr;
+  smmc_status st = get_context(device, &ctx);
+  if (st != SMMC_OK) return st;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  uint64_t have = ctx->ev_head < (uint64_t)kEventRing ? ctx->ev_head : (uint64_t)kEventRing;
+  if (have > (uint64_t)max_n) have = (uint64_t)max_n;
+  for (uint64_t i = 0; i < have; i++) kinds_out[i] = ctx->ev_kind[(ctx->ev_head - have + i) % kEventRing];  // oldest first
+  *n_out = (int32_t)have;
   return SMMC_OK;
 }
 

@@ -212,6 +212,15 @@ def kernel_times(device=0, max_n=256):
     return out[:int(n.value)].copy()
 
 
+def kernel_kinds(device=0, max_n=256):
+    """Which kernel each entry of kernel_times() was (oldest first): N.KERNEL_SIMULATION or N.KERNEL_SELECT_CANDIDATES."""
+    lib = N.load()
+    out = np.zeros(int(max_n), dtype=np.int32)
+    n = C.c_int32()
+    N.check(lib.smmc_kernel_kinds(int(device), out.ctypes.data, int(max_n), C.byref(n)))
+    return [int(k) for k in out[:int(n.value)]]
+
+
 def finalize_stats(stats, hist_bins, initial_capital) -> Result:
     """Turn a (possibly all-reduced) host statistics vector into count / mean / M2 / below / histogram."""
     lib = N.load()

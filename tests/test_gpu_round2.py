@@ -230,20 +230,22 @@ def test_run_multi_merges_on_the_devices(S, table):
 @pytest.mark.parametrize("mode", ALL_MODES)
 def test_third_select_pass_reads_candidates_not_a_replay(S, table, mode):
     kw = mode_kwargs(mode, table)
-    N, P = 4_000_000, 240  # replays of ~0.6 ms: the timing relations below have a wide margin (they are structural, not a benchmark)
+    N, P = 1_000_000, 120
+    SIM, CAND = 1, 2  # SMMC_KERNEL_SIMULATION, SMMC_KERNEL_SELECT_CANDIDATES (include/smmc.h)
     fin = np.sort(S.simulate(mode, N, P, want_finals=True, **kw).finals)
     ranks = [0, 1, N // 4, N // 2, N // 2 + 1, 3 * (N // 4), N - 2, N - 1]
     q, ms = S.quantiles(mode, N, P, ranks=ranks, return_ms=True, **kw)
     assert np.array_equal(q, fin[ranks])
-    t = S.kernel_times(0, 3)  # the three passes of that call
-    assert t[2] < 0.5 * t[1], t  # pass 3 is an HBM pass over the candidates, not a third simulation
+    # the three passes of that call: pass 3 is the pass over the candidates, not a third simulation (what was launched is
+    # reported by the library; no duration is compared)
+    assert S.kernel_kinds(0, 3) == [SIM, SIM, CAND] and len(S.kernel_times(0, 3)) == 3 and ms > 0.0
     try:
         S.set_variant("select_candidates", 0)
-        q0, ms0 = S.quantiles(mode, N, P, ranks=ranks, return_ms=True, **kw)
-        t0 = S.kernel_times(0, 3)
+        q0 = S.quantiles(mode, N, P, ranks=ranks, **kw)
+        assert S.kernel_kinds(0, 3) == [SIM, SIM, SIM]
     finally:
         S.set_variant()
-    assert np.array_equal(q0, q) and t0[2] > 0.5 * t0[1] and ms < 0.95 * ms0
+    assert np.array_equal(q0, q)
 
 
 def test_candidate_buffer_is_never_reused_for_another_run(S, table):
