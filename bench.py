@@ -702,16 +702,19 @@ def main():
         for s in range(3):
             host_step(10_000 + s)
         barrier()
+        ar0 = comm.allreduce_count() if comm is not None else 0
         t0 = time.perf_counter()
         for s in range(k_e2e):
             host_step(20_000 + s)
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        ar_per_step = (comm.allreduce_count() - ar0) / k_e2e if comm is not None else 0
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": job_paths * P * k_e2e / float(dt.item()), "unit": UNIT,
                "h2d_bytes_per_step": int(table.nbytes) if table is not None else 0,
                "d2h_bytes_per_step": int(slen * 8 + (2 * nb * 4 if wl["block_partials"] else 0)),
+               "allreduces_per_step": ar_per_step,
                "steps": k_e2e, "api": ("stock_market_monte_carlo_b200.simulate -> smmc_run (host buffers, blocking)" if comm is None else
                                        "Comm.simulate -> smmc_run_rank (host buffers, blocking; ncclAllReduce inside the C ABI)"),
                "inputs": ("return table copied host->device every step" if table is not None else
@@ -898,7 +901,8 @@ def main():
         "config": {"workload": wl["desc"], "mode": mode, "paths_per_gpu_per_step": B, "periods": P, "seed": seed,
                    "hist_bins": HIST_BINS, "block_partials": wl["block_partials"], "parallelism": f"paths sharded by RNG offset x{world}",
                    "collective": ("1 ncclAllReduce(ncclFloat64, ncclSum) of %d doubles per step, enqueued by smmc_run_rank (C ABI) "
-                                  "on the kernel's stream" % slen) if world > 1 else "none",
+                                  "on the kernel's stream; the host-buffer e2e leg (two launches per step) also issues one" % slen)
+                   if world > 1 else "none",
                    "l2": "flushed between timed steps (256 MiB memset outside the event pairs); the path has no HBM input larger than 4.8 KB"},
         "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,

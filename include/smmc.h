@@ -165,6 +165,8 @@ smmc_status smmc_comm_init_rank(const void *id, int32_t n_ranks, int32_t rank, i
 smmc_status smmc_comm_adopt(void *nccl_comm, int32_t device, smmc_comm **comm);
 smmc_status smmc_comm_destroy(smmc_comm *comm);
 smmc_status smmc_comm_info(const smmc_comm *comm, int32_t *n_ranks, int32_t *rank, int32_t *device, int32_t *nccl_version);
+/* how many ncclAllReduce calls smmc_run_rank has issued through `comm` so far (one per call, on every path) */
+smmc_status smmc_comm_allreduce_count(const smmc_comm *comm, uint64_t *count);
 /* This rank's part of the GLOBAL run `cfg` (cfg->n_simulations, cfg->stream_offset describe the whole run; cfg->device
  * is ignored in favour of the communicator's device): rank r simulates the r-th of n_ranks contiguous ranges of whole
  * 256-path blocks (the partition of smmc_run_multi; smmc_rank_range reports it), then
@@ -174,7 +176,8 @@ smmc_status smmc_comm_info(const smmc_comm *comm, int32_t *n_ranks, int32_t *ran
  * pointers (blocking) by default; DEVICE_POINTERS [+ NO_SYNC] runs on cfg->stream, fully asynchronously with NO_SYNC
  * (read the merged vector from out->stats_dev).  Collective: every rank must call it.  Host-pointer runs that return block
  * partials of >= 16 Mi paths per rank are launched in two parts (the first part's download hides behind the second
- * kernel) and issue two such all-reduces, on every rank alike. */
+ * kernel); the first part's statistics are added into the second part's on the device, so this path too issues exactly ONE
+ * all-reduce per call (smmc_comm_allreduce_count lets a caller check). */
 smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *comm);
 /* first path (relative to cfg->stream_offset) and number of paths of rank `rank` of `n_ranks` for a run of n paths */
 smmc_status smmc_rank_range(int64_t n_simulations, int32_t n_ranks, int32_t rank, int64_t *first, int64_t *count);

@@ -116,7 +116,7 @@ C_ABI_SYMBOLS = [
     "smmc_debug_draws", "smmc_debug_philox", "smmc_debug_philox_rounds", "smmc_debug_set_variant", "smmc_kernel_times", "smmc_kernel_kinds", "smmc_last_error", "smmc_version", "smmc_device_count", "smmc_shutdown",
     "smmc_select_begin", "smmc_select_pass", "smmc_select_advance", "smmc_select_values", "smmc_quantiles",
     "smmc_trajectories", "smmc_read_returns_csv", "smmc_write_data_file", "smmc_plan_launch",
-    "smmc_comm_unique_id", "smmc_comm_init_rank", "smmc_comm_adopt", "smmc_comm_destroy", "smmc_comm_info", "smmc_run_rank",
+    "smmc_comm_unique_id", "smmc_comm_init_rank", "smmc_comm_adopt", "smmc_comm_destroy", "smmc_comm_info", "smmc_comm_allreduce_count", "smmc_run_rank",
     "smmc_rank_range", "smmc_quantiles_rank",
 ]
 COMM_ID_BYTES = 128
@@ -196,6 +196,8 @@ def load():
     lib.smmc_comm_destroy.restype = C.c_int
     lib.smmc_comm_info.argtypes = [C.c_void_p, P(C.c_int32), P(C.c_int32), P(C.c_int32), P(C.c_int32)]
     lib.smmc_comm_info.restype = C.c_int
+    lib.smmc_comm_allreduce_count.argtypes = [C.c_void_p, P(C.c_uint64)]
+    lib.smmc_comm_allreduce_count.restype = C.c_int
     lib.smmc_run_rank.argtypes = [P(SmmcConfig), P(SmmcResult), C.c_void_p]
     lib.smmc_run_rank.restype = C.c_int
     lib.smmc_rank_range.argtypes = [C.c_int64, C.c_int32, C.c_int32, P(C.c_int64), P(C.c_int64)]

@@ -28,6 +28,7 @@ struct smmc_comm {
   smmc::NcclComm nccl = nullptr;
   int n_ranks = 1, rank = 0, device = 0;
   bool owned = false;
+  unsigned long long allreduces = 0;  // ncclAllReduce calls issued through this communicator (smmc_comm_allreduce_count)
 };
 
 namespace smmc {
@@ -1192,10 +1193,12 @@ smmc_status run_finals_pipelined(std::vector<Shard> &shards, const smmc_config *
 // do -- and only the last eighth is exposed.  Statistics: the two allreduce-ready vectors are added on the host.
 constexpr int64_t kSplitMinPaths = (int64_t)16 << 20;
 
-// api / nccl (smmc_run_rank): every part's vector is all-reduced over the ranks on the kernel's stream before it is downloaded
-// (two collectives per call, on every rank alike).
+// api / nccl (smmc_run_rank): the first part's vector is added into the second part's on the device (108 doubles, one tiny
+// kernel behind the second launch) and that ONE vector is all-reduced over the ranks on the kernel's stream before it is
+// downloaded -- one collective per call on this path as on every other; the early download of the first part's partials is kept.
 smmc_status run_partials_split(std::vector<Shard> &shards, const smmc_config *cfg, std::vector<double> *total, float *device_ms,
-                               int *launches, const smmc::NcclApi *api = nullptr, smmc::NcclComm nccl = nullptr) {
+                               int *launches, const smmc::NcclApi *api = nullptr, smmc::NcclComm nccl = nullptr,
+                               unsigned long long *allreduces = nullptr) {
   const int slen = smmc_stats_len(cfg->hist_bins);
   const size_t S = shards.size();
   std::vector<int64_t> n_first(S, 0);
@@ -1247,8 +1250,14 @@ smmc_status run_partials_split(std::vector<Shard> &shards, const smmc_config *cf
       }
       if (part == 0) CU(cudaEventRecord(ctx->kdone[0], ctx->stream));
       if (api) {
+        if (part == 0) {  // folded into part 1 below: nothing of part 0 is reduced or downloaded by itself
+          memset(ctx->chunk_stats_host, 0, (size_t)slen * sizeof(double));
+          continue;
+        }
+        CU(smmc::launch_add_f64(stats_dev, (const double *)ctx->chunk_stats.p, slen, ctx->stream));
         const int r = api->AllReduce(stats_dev, stats_dev, (size_t)slen, smmc::kNcclFloat64, smmc::kNcclSum, nccl, ctx->stream);
         if (r != 0) return fail(SMMC_ERR_CUDA, "ncclAllReduce failed: %s", api->GetErrorString(r));
+        if (allreduces) ++*allreduces;
       }
       CU(cudaMemcpyAsync(ctx->chunk_stats_host + (size_t)part * slen, stats_dev, (size_t)slen * sizeof(double), cudaMemcpyDeviceToHost,
                          ctx->stream));
@@ -1708,6 +1717,12 @@ smmc_status smmc_comm_adopt(void *nccl_comm, int32_t device, smmc_comm **comm) {
   return SMMC_OK;
 }
 
+smmc_status smmc_comm_allreduce_count(const smmc_comm *comm, uint64_t *count) {
+  if (!comm || !count) return fail(SMMC_ERR_INVALID_ARG, "comm_allreduce_count: null argument");
+  *count = comm->allreduces;
+  return SMMC_OK;
+}
+
 smmc_status smmc_comm_destroy(smmc_comm *comm) {
   if (!comm) return SMMC_OK;
   if (comm->owned && comm->nccl) {
@@ -1762,8 +1777,8 @@ smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *c
   const bool host_ptrs = (cfg->flags & SMMC_FLAG_DEVICE_POINTERS) == 0;
   if (host_ptrs && !out->finals && (out->block_means || out->block_vars) && current_variant().finals_chunks != 1 &&
       cfg->n_simulations / comm->n_ranks >= kSplitMinPaths) {
-    // block partials into host memory: two launches (and two collectives) so that most of the download hides behind the
-    // second kernel; the criterion is a function of the job, not of the shard, so every rank takes the same branch
+    // block partials into host memory: two launches (ONE collective, after the second) so that most of the download hides
+    // behind the second kernel; the criterion is a function of the job, not of the shard, so every rank takes the same branch
     std::vector<Shard> one(1);
     one[0].ctx = ctx;
     one[0].cfg = c2;
@@ -1772,7 +1787,7 @@ smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *c
     std::vector<double> total;
     float ms = 0.0f;
     int launches = 0;
-    st = run_partials_split(one, cfg, &total, &ms, &launches, api, comm->nccl);
+    st = run_partials_split(one, cfg, &total, &ms, &launches, api, comm->nccl, &comm->allreduces);
     if (st != SMMC_OK) return st;
     out->device_ms = ms;
     out->gpu_launches = launches;
@@ -1785,6 +1800,7 @@ smmc_status smmc_run_rank(const smmc_config *cfg, smmc_result *out, smmc_comm *c
   out->gpu_launches = pd.launches;
   // the ONE collective of the path: O(KB), on the kernel's stream (stream order = data dependency)
   NCCL_CALL(api, api->AllReduce(pd.stats_dev, pd.stats_dev, (size_t)pd.stats_len, smmc::kNcclFloat64, smmc::kNcclSum, comm->nccl, pd.stream));
+  comm->allreduces++;
   st = mark_last_use(ctx, pd.stream);
   if (st != SMMC_OK) return st;
   if (cfg->flags & SMMC_FLAG_NO_SYNC) return SMMC_OK;

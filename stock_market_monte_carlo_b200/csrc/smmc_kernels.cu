@@ -546,6 +546,17 @@ cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_de
   return cudaGetLastError();
 }
 
+// dst[i] += src[i] over a statistics vector (a few hundred doubles): folds the first part of a split run into the second on
+// the device so that the rank path all-reduces ONE vector
+__global__ void add_f64_kernel(double *__restrict__ dst, const double *__restrict__ src, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] += src[i];
+}
+cudaError_t launch_add_f64(double *dst, const double *src, int n, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  add_f64_kernel<<<(n + 255) / 256, 256, 0, s>>>(dst, src, n);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, int n_sms, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const int vec = ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15u) == 0;

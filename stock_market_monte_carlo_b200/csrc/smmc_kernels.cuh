@@ -186,5 +186,6 @@ cudaError_t launch_reduce_sum(const float *v_dev, int64_t n, double *partials_de
 // name of the kernel launch_reduce_sum dispatches for (n, which) -- reported by the bench
 const char *reduce_sum_kernel_name(int64_t n, int n_sms, int which);
 cudaError_t launch_vector_add(float *out, const float *a, const float *b, int64_t n, int n_sms, cudaStream_t s);
+cudaError_t launch_add_f64(double *dst, const double *src, int n, cudaStream_t s);  // dst[i] += src[i], statistics vectors
 
 }  // namespace smmc

@@ -513,6 +513,12 @@ class Comm:
         N.check(self.lib.smmc_comm_info(self.handle, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return dict(n_ranks=a.value, rank=b.value, device=c.value, nccl_version=d.value)
 
+    def allreduce_count(self):
+        """ncclAllReduce calls smmc_run_rank has issued through this communicator (exactly one per call)"""
+        n = C.c_uint64()
+        N.check(self.lib.smmc_comm_allreduce_count(self.handle, C.byref(n)))
+        return int(n.value)
+
     def destroy(self):
         if self.handle:
             self.lib.smmc_comm_destroy(self.handle)

@@ -419,13 +419,15 @@ def test_split_launch_for_block_partials_changes_nothing(S, table, mode):
 
 
 def test_run_rank_split_launch_two_gpus(S, table):
-    """the same through smmc_run_rank on two ranks (two launches and two collectives per rank): block partials of the ranks
+    """the same through smmc_run_rank on two ranks (two launches, ONE collective per rank and call): block partials of the ranks
     concatenate to those of one GPU, merged statistics equal the single-GPU run's"""
     if _n_gpus(S) < 2:
         pytest.skip("needs 2 GPUs")
     N, P = 2 * ((16 << 20) + 148 * 32 * 256 * 2) + 1000, 4
     one = S.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True)
-    res = _two_rank_job(S, lambda c: c.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True))
+    res = _two_rank_job(S, lambda c: (c.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True), c.allreduce_count()))
+    assert [n for _, n in res] == [1, 1]
+    res = [r for r, _ in res]
     for r in res:
         assert r.gpu_launches >= 2
         assert r.count == N and r.below_count == one.below_count and np.array_equal(r.hist, one.hist)

@@ -50,3 +50,32 @@ def test_multi_gpu_host_merge_equals_device_merge(S, table):
             assert stats_only.count == 600_001 and abs(stats_only.mean - dev.mean) <= 1e-12 * abs(dev.mean)
     finally:
         S.set_variant()
+
+
+def test_run_rank_issues_one_allreduce_per_call_on_every_path(S, table):
+    """smmc_run_rank on a one-rank communicator (runs on a 1-GPU box): the plain path, the device-pointer path and the
+    split-launch path (block partials of >= 16 Mi paths into host memory: two kernels) each issue exactly one ncclAllReduce,
+    and the split path's statistics equal the monolithic launch's"""
+    import torch
+    comm = S.Comm(S.Comm.unique_id(), 1, 0, 0)
+    try:
+        assert comm.allreduce_count() == 0
+        comm.simulate("bootstrap", 100_003, 12, returns=table, seed=3, hist_bins=16, want_finals=True)
+        assert comm.allreduce_count() == 1
+        stats = torch.zeros(S.stats_len(16), dtype=torch.float64, device="cuda")
+        comm.simulate_device("gaussian", 300_000, 36, stats.data_ptr(), stream=torch.cuda.current_stream().cuda_stream, seed=5, hist_bins=16)
+        torch.cuda.synchronize()
+        assert comm.allreduce_count() == 2
+        N, P = (16 << 20) + 148 * 32 * 256 * 2 + 1000, 4
+        split = comm.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True)
+        assert split.gpu_launches >= 2 and comm.allreduce_count() == 3
+        try:
+            S.set_variant("finals_chunks", 1)  # one monolithic launch
+            mono = S.simulate("gaussian", N, P, hist_bins=32, want_block_partials=True)
+        finally:
+            S.set_variant()
+        assert np.array_equal(split.block_means, mono.block_means) and np.array_equal(split.block_vars, mono.block_vars)
+        assert np.array_equal(split.hist, mono.hist) and (split.count, split.below_count) == (mono.count, mono.below_count)
+        assert abs(split.mean - mono.mean) <= 1e-12 * abs(mono.mean) and abs(split.m2 - mono.m2) <= 1e-9 * abs(mono.m2)
+    finally:
+        comm.destroy()
