@@ -31,6 +31,7 @@ oracle/ is only ever the checker / the CPU baseline here, never the thing measur
 import argparse
 import json
 import os
+import re
 import statistics
 import subprocess
 import sys
@@ -536,6 +537,9 @@ def make_summary(extras):
                           r4(rg["this_build_compat_block_partials"]["wall_ms"]), r4(rg["this_build_compat_all_finals"]["wall_ms"])]
         if rg.get("reference_kernel_event_ms"):
             out["ref_kernel_event_ms"] = r4(rg["reference_kernel_event_ms"])
+    cp = (extras or {}).get("cold_process") or {}
+    if "call_s_min" in (cp.get("this_build") or {}) and "call_s_min" in (cp.get("reference") or {}):
+        out["cold_call_s"] = [cp["this_build"]["call_s_min"], cp["reference"]["call_s_min"]]
     se = (extras or {}).get("sharded_equals_single")
     if se:
         out["all_modes_identical"] = se["all_modes_identical"]
@@ -544,7 +548,52 @@ def make_summary(extras):
         out["quartiles_ms"] = [r4(extras["quartiles_device_ms"]), r4(extras.get("quartiles_riding_along_extra_ms"))]
     out["keys"] = ("legs [G path-months/s (G elements/s: reduce_mean, vector_add), kernel_ms, roofline frac]; c3_e2e [G/s, h2d bytes]; "
                    "c5 [ms_per_step, sha256[:12], mean_rel_err, std_rel_err]; cpu_v2 [G/s, threads]; "
-                   "ref_gpu wall ms [ref reduceBlock, ref finals, ours partials, ours finals]")
+                   "ref_gpu wall ms [ref reduceBlock, ref finals, ours partials, ours finals]; cold_call_s [ours, reference]: benchmark_mc_gpu 1 360 1e8, fresh process")
+    return out
+
+
+def cold_process(S, reps=3):
+    """The way every reference program uses the library: ONE call in a fresh process.  The reference's own benchmark_mc_gpu
+    (examples/benchmark_mc_gpu.cpp, unmodified) at `1 360 100000000`, three fresh processes each of (i) the example relinked
+    against libsmmc.so and (ii) the example built with the reference's own src/simulations.cu for sm_100a; the figure is the
+    wall clock the example itself prints around mc_simulations_gpu (:68-71), i.e. context creation, module load, allocation,
+    kernel, 400 MB download.  Also the whole process by this script's clock."""
+    import pathlib
+    import shutil
+    import subprocess
+    import tempfile
+    root = os.path.dirname(os.path.abspath(__file__))
+    exes = {"this_build": os.path.join(root, "oracle", "_ref", "benchmark_mc_gpu"),
+            "reference": os.path.join(root, "oracle", "_ref", "benchmark_mc_gpu_ref")}
+    out = {"args": "1 360 100000000", "n_returns": 1127, "how": "seconds printed by the example around its one mc_simulations_gpu call; fresh process each"}
+    table = S.synthetic_sp500_table(1127, seed=7)
+    with tempfile.TemporaryDirectory() as d:
+        d = pathlib.Path(d)
+        (d / "data").mkdir()
+        with open(d / "data" / "SP500_monthly_returns.csv", "w") as f:
+            f.write("Date,returns\n")
+            for x in table:
+                f.write(f"1900-01-01,{float(x)!r}\n")
+        env = dict(os.environ)
+        if os.path.isdir("/usr/lib/locale/C.utf8"):  # the example asks for en_US.UTF-8, which this image does not ship
+            shutil.copytree("/usr/lib/locale/C.utf8", d / "locale" / "en_US.UTF-8")
+            env["LOCPATH"] = str(d / "locale")
+        for name, exe in exes.items():
+            if not os.path.exists(exe):
+                out[name] = {"unavailable": f"{os.path.relpath(exe, root)} did not travel with the snapshot"}
+                continue
+            call_s, proc_s = [], []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                p = subprocess.run([exe, "1", "360", "100000000"], cwd=d, env=env, capture_output=True, text=True)
+                proc_s.append(time.perf_counter() - t0)
+                m = re.search(r"simulation done in ([\d.]+) s", p.stdout)
+                if p.returncode != 0 or not m:
+                    out[name] = {"unavailable": f"rc={p.returncode}: {(p.stderr or p.stdout)[-200:]}"}
+                    break
+                call_s.append(float(m.group(1)))
+            else:
+                out[name] = {"call_s": call_s, "call_s_min": min(call_s), "process_s": [round(x, 3) for x in proc_s]}
     return out
 
 
@@ -876,6 +925,10 @@ def main():
         legs["reduce_mean"] = hbm_leg(torch, S, "reduce_mean", dev, local)
         legs["vector_add"] = hbm_leg(torch, S, "vector_add", dev, local)
         extras["workloads"] = legs
+        try:
+            extras["cold_process"] = cold_process(S)
+        except Exception as e:
+            extras["cold_process"] = {"unavailable": f"{type(e).__name__}: {e}"}
         try:
             extras["cpu_v2"] = cpu_v2_leg()
         except Exception as e:
