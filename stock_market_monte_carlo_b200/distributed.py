@@ -5,7 +5,8 @@ The reference's multi-GPU launcher re-runs the same paths on every device and ga
 range `shard_range(N, r, G)`; the path id IS the RNG stream offset, so the union over ranks is exactly the
 1-GPU run.  Each rank's kernel emits the allreduce-ready statistics vector of include/smmc.h
 (count, below, S1, S2, histogram -- all sum-reducible, integer fields exact in fp64), and a single
-`all_reduce(SUM)` (NCCL over NVLink on GPUs, gloo in the CPU tests) merges them.
+all-reduce merges them: on GPUs `ncclAllReduce` enqueued by `smmc_run_rank` inside libsmmc.so (simulate_sharded and
+quantiles_sharded go through `simulations.Comm`), in the gloo CPU tests of this host logic `torch.distributed.all_reduce`.
 
 Nothing here touches per-path data, and nothing here computes paths: the simulation itself is `simulate_device`
 (CUDA only).
@@ -25,14 +26,37 @@ def shard_range(n_simulations, rank, world_size, stream_offset=0):
     return int(stream_offset) + first, count
 
 
+_comms = {}  # (device, id(group)) -> simulations.Comm: the communicators behind simulate_sharded / quantiles_sharded on GPUs
+
+
+def _uses_nccl(group=None):
+    """True when this is a multi-rank job on GPUs: the collective then runs inside libsmmc.so (smmc_run_rank /
+    smmc_quantiles_rank), never through torch.distributed -- the package has ONE GPU data plane."""
+    import torch.distributed as dist
+    return (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+            and "nccl" in str(dist.get_backend(group)).lower())
+
+
+def _comm_for(device, group=None):
+    key = (int(device), id(group))
+    if key not in _comms:
+        _comms[key] = init_comm(device, group)  # collective: every rank gets here on its first sharded call
+    return _comms[key]
+
+
 def allreduce_stats(stats, group=None):
-    """In-place SUM all-reduce of a statistics vector (torch float64 tensor; CUDA for NCCL, CPU for gloo).
-    This is the only collective of the path: O(KB), latency-bound."""
+    """In-place SUM all-reduce of a statistics vector through torch.distributed: the stand-in for the NCCL call of
+    smmc_run_rank in the gloo CPU tests of the host logic (CPU float64 tensor).  GPU jobs do not come through here."""
     import torch.distributed as dist
 
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
     return stats
+
+
+def _first(n_simulations, rank, world):
+    from . import simulations as _S
+    return _S.rank_range(int(n_simulations), world, rank)[0]
 
 
 def simulate_sharded(mode, n_simulations, n_periods, *, device, stream=None, group=None, hist_bins=0, **kw):
@@ -50,9 +74,13 @@ def simulate_sharded(mode, n_simulations, n_periods, *, device, stream=None, gro
     stats = torch.empty(stats_len(hist_bins), dtype=torch.float64, device=dev)
     st = stream if stream is not None else torch.cuda.current_stream(dev)
     with torch.cuda.stream(st):
-        launches = simulate_device(mode, n_local, n_periods, stats.data_ptr(), stream_offset=off,
-                                   hist_bins=hist_bins, device=device, stream=st.cuda_stream, **kw)
-        allreduce_stats(stats, group)
+        if _uses_nccl(group):  # kernel -> ncclAllReduce on the same stream, both enqueued by smmc_run_rank
+            launches = _comm_for(device, group).simulate_device(mode, n_simulations, n_periods, stats.data_ptr(), stream_offset=off - _first(n_simulations, rank, world),
+                                                                hist_bins=hist_bins, stream=st.cuda_stream, **kw)
+        else:
+            launches = simulate_device(mode, n_local, n_periods, stats.data_ptr(), stream_offset=off,
+                                       hist_bins=hist_bins, device=device, stream=st.cuda_stream, **kw)
+            allreduce_stats(stats, group)  # one rank, or a non-NCCL group
         host = stats.cpu()
     return finalize_stats(host.numpy(), hist_bins, kw.get("initial_capital", 1000.0)), launches
 
@@ -69,6 +97,8 @@ def quantiles_sharded(mode, n_simulations, n_periods, ranks=None, *, device, str
 
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if _uses_nccl(group):  # smmc_quantiles_rank: replays + ncclAllReduce(ncclUint64) of the digit histograms inside the C ABI
+        return _comm_for(device, group).quantiles(mode, n_simulations, n_periods, ranks=ranks, **kw)
     off, n_local = shard_range(n_simulations, rank, world, kw.pop("stream_offset", 0))
     dev = torch.device("cuda", device)
     st = stream if stream is not None else torch.cuda.current_stream(dev)
